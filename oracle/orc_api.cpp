@@ -1,0 +1,158 @@
+// oracle/orc_api.cpp -- TEST INFRASTRUCTURE ONLY.  C entry points over the CPU
+// oracle for ctypes (tests/, bench.py cpu_baseline / --impl reference, smoke()).
+// PARITY UNPINNED (see orc_common.h).
+#include "orc_common.h"
+#include "orc_raytracer.h"
+#include "orc_models.h"
+#ifdef ORC_HAVE_GRID
+#include "orc_grid.h"
+#endif
+
+using namespace orc;
+
+extern "C" {
+
+// row layout shared with the product (include/srt.h): 20 doubles
+//   t, pos[3], vprel[3], vgrel[3], n[3], B0[3], Ns[4]
+#define ORC_ROW 20
+
+void* orc_model_ngo(const char* cfg, int yearday, int msec, int use_igrf, int faithful_cost) {
+  NgoModel* m = new NgoModel();
+  if (m->st.readinput(cfg) != 0) { delete m; return nullptr; }
+  m->del = 1.0e-4;  // delSP, driver:251
+  m->field.tilt.init(yearday, msec);
+  m->field.tilt.cache = !faithful_cost;
+  m->field.use_igrf = use_igrf;
+#ifdef ORC_HAVE_GRID
+  if (!orc_attach_igrf(m->field, yearday, msec, faithful_cost)) { delete m; return nullptr; }
+#else
+  if (use_igrf) { delete m; return nullptr; }
+#endif
+  return (Model*)m;
+}
+
+#ifdef ORC_HAVE_GRID
+void* orc_model_grid(const char* gridfile, int yearday, int msec, int use_igrf, int faithful_cost) {
+  GridModel* m = new GridModel();
+  if (m->setup(gridfile) != 0) { delete m; return nullptr; }
+  m->del = 1.0e-6;  // delDP, driver:252
+  m->dense_matmul = faithful_cost != 0;
+  m->field.tilt.init(yearday, msec);
+  m->field.tilt.cache = !faithful_cost;
+  m->field.use_igrf = use_igrf;
+  if (!orc_attach_igrf(m->field, yearday, msec, faithful_cost)) { delete m; return nullptr; }
+  return (Model*)m;
+}
+#endif
+
+void orc_model_free(void* m) { delete (Model*)m; }
+
+double orc_model_del(void* m) { return ((Model*)m)->del; }
+
+// funcPlasmaParams at n points: out[n][19] = qs4, Ns4, ms4, nus4, B03
+void orc_plasma(void* mv, long n, const double* x, double* out) {
+  Model* m = (Model*)mv;
+  for (long i = 0; i < n; ++i) {
+    Plasma p;
+    m->plasma(x + 3 * i, p);
+    double* o = out + 19 * i;
+    for (int s = 0; s < 4; ++s) { o[s] = p.qs[s]; o[4 + s] = p.Ns[s]; o[8 + s] = p.ms[s]; o[12 + s] = p.nus[s]; }
+    for (int c = 0; c < 3; ++c) o[16 + c] = p.B0[c];
+  }
+}
+
+double orc_dispersion_relation(void* mv, const double* n, double w, const double* x) {
+  Plasma p;
+  ((Model*)mv)->plasma(x, p);
+  return dispersion_relation(n, w, p);
+}
+void orc_stix(void* mv, double w, const double* x, double* out5) {
+  Plasma p;
+  ((Model*)mv)->plasma(x, p);
+  stix_parameters(w, p, m_sqrt(dot3(p.B0, p.B0)), out5[0], out5[1], out5[2], out5[3], out5[4]);
+}
+void orc_evalrhs(void* mv, const double* args7, double* rhs7) {
+  Model* m = (Model*)mv;
+  raytracer_evalrhs(args7, m->del, *m, rhs7);
+}
+void orc_solve(void* mv, const double* k, double w, const double* x, double* k1k2 /*re,im,re,im*/) {
+  cplx k1, k2;
+  solve_dispersion_relation(k, w, x, k1, k2, *(Model*)mv);
+  k1k2[0] = k1.re; k1k2[1] = k1.im; k1k2[2] = k2.re; k1k2[3] = k2.im;
+}
+int orc_is_right_handed(double n2, double phi, double S, double D, double P) { return is_right_handed(n2, phi, S, D, P) ? 1 : 0; }
+// the float-rounded matrix of form_dispersion_matrix, for the numpy SVD cross-check: out[3][3][2]
+void orc_form_dispersion_matrix(double n2, double phi, double S, double D, double P, double* out) {
+  cplx M[3][3];
+  form_dispersion_matrix(M, n2, phi, S, D, P);
+  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) { out[(i * 3 + j) * 2] = M[i][j].re; out[(i * 3 + j) * 2 + 1] = M[i][j].im; }
+}
+
+struct OrcTrace {
+  RunResult r;
+  double dir0[3];
+  long plasma_calls;
+};
+
+// one raytracer_run; returns an opaque handle
+void* orc_trace(void* mv, const double* pos0, const double* dir0, double w0, double dt0, double dtmax, double maxerr, int maxsteps,
+                double minalt, int root, double tmax, int fixedstep) {
+  Model* m = (Model*)mv;
+  OrcTrace* t = new OrcTrace();
+  for (int i = 0; i < 3; ++i) t->dir0[i] = dir0[i];
+  long before = m->n_plasma_calls;
+  raytracer_run(t->r, pos0, t->dir0, w0, dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep, m->del, *m);
+  t->plasma_calls = m->n_plasma_calls - before;
+  return t;
+}
+long orc_trace_nrows(void* tv) { return (long)((OrcTrace*)tv)->r.rows.size(); }
+int orc_trace_stopcond(void* tv) { return ((OrcTrace*)tv)->r.stopcond; }
+long orc_trace_nrejected(void* tv) { return ((OrcTrace*)tv)->r.n_rejected; }
+long orc_trace_ncone(void* tv) { return ((OrcTrace*)tv)->r.n_cone; }
+long orc_trace_plasma_calls(void* tv) { return ((OrcTrace*)tv)->plasma_calls; }
+int orc_trace_fixed_cone_exit(void* tv) { return ((OrcTrace*)tv)->r.fixed_cone_exit; }
+void orc_trace_dir0(void* tv, double* d) { for (int i = 0; i < 3; ++i) d[i] = ((OrcTrace*)tv)->dir0[i]; }
+void orc_trace_rows(void* tv, double* out) {
+  OrcTrace* t = (OrcTrace*)tv;
+  for (size_t i = 0; i < t->r.rows.size(); ++i) {
+    const Row& r = t->r.rows[i];
+    double* o = out + ORC_ROW * i;
+    o[0] = r.t;
+    for (int c = 0; c < 3; ++c) { o[1 + c] = r.pos[c]; o[4 + c] = r.vprel[c]; o[7 + c] = r.vgrel[c]; o[10 + c] = r.n[c]; o[13 + c] = r.B0[c]; }
+    for (int s = 0; s < 4; ++s) o[16 + s] = r.Ns[s];
+  }
+}
+// species constants of row 0 (qs4, ms4, nus4)
+void orc_trace_species(void* tv, double* out12) {
+  const Row& r = ((OrcTrace*)tv)->r.rows[0];
+  for (int s = 0; s < 4; ++s) { out12[s] = r.qs[s]; out12[4 + s] = r.ms[s]; out12[8 + s] = r.nus[s]; }
+}
+void orc_trace_free(void* tv) { delete (OrcTrace*)tv; }
+
+// batch over rays for the timed CPU baseline: returns total accepted steps (rows-1) and
+// writes the last row + counts per ray.  Rays [first, first+count) of the arrays.
+long orc_trace_batch_summary(void* mv, long nrays, const double* pos0, const double* dir0, const double* w0, double dt0, double dtmax,
+                             double maxerr, int maxsteps, double minalt, int root, double tmax, int fixedstep, double* last_row,
+                             long* nrows, int* stopcond, long* nrejected) {
+  Model* m = (Model*)mv;
+  long acc = 0;
+  for (long i = 0; i < nrays; ++i) {
+    RunResult r;
+    double d[3] = {dir0[3 * i], dir0[3 * i + 1], dir0[3 * i + 2]};
+    raytracer_run(r, pos0 + 3 * i, d, w0[i], dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep, m->del, *m);
+    acc += (long)r.rows.size() - 1;
+    if (nrows) nrows[i] = (long)r.rows.size();
+    if (stopcond) stopcond[i] = r.stopcond;
+    if (nrejected) nrejected[i] = r.n_rejected + r.n_cone;
+    if (last_row) {
+      const Row& q = r.rows.back();
+      double* o = last_row + ORC_ROW * i;
+      o[0] = q.t;
+      for (int c = 0; c < 3; ++c) { o[1 + c] = q.pos[c]; o[4 + c] = q.vprel[c]; o[7 + c] = q.vgrel[c]; o[10 + c] = q.n[c]; o[13 + c] = q.B0[c]; }
+      for (int s = 0; s < 4; ++s) o[16 + s] = q.Ns[s];
+    }
+  }
+  return acc;
+}
+
+}  // extern "C"

@@ -1,0 +1,99 @@
+// tests/csrc/hostemu.cpp -- TEST-ONLY CPU build of the device physics
+// (stanford_raytracer_b200/csrc/srt_physics.h).  It lets the CPU suite check, without a
+// GPU, that the de-duplicated evaluation order of the kernels reproduces the oracle's
+// faithful call structure bit for bit.  Not shipped, not a fallback: libsrt.so has no
+// CPU path.
+#include "../../stanford_raytracer_b200/csrc/srt_physics.h"
+#include "../../stanford_raytracer_b200/csrc/srt_igrf.h"
+#include "../../stanford_raytracer_b200/csrc/srt_tricubic.h"
+#include "../../stanford_raytracer_b200/csrc/srt_host_setup.h"
+#ifdef EMU_HAVE_GRID
+#include "../../stanford_raytracer_b200/csrc/srt_grid_setup.h"
+#include "../../stanford_raytracer_b200/csrc/srt_igrf_setup.h"
+#endif
+
+template <int D, int I>
+static long run_one(const SrtModel& M, const SrtRunParams& P, const double* pos0, double* dir0, double w0, double* rows, long max_rows,
+                    int* stopcond, long* nrej, long* ncone, int* cone_exit) {
+  SrtRayState st;
+  double row[SRT_ROW_DOUBLES];
+  srt_ray_init<D, I>(M, P, pos0, dir0, w0, st, row);
+  long n = 0;
+  if (n < max_rows) memcpy(rows + SRT_ROW_DOUBLES * n, row, sizeof row);
+  ++n;
+  for (;;) {
+    int r = srt_ray_attempt<D, I>(M, P, st, row);
+    if (r == SRT_ATTEMPT_DONE) break;
+    if (r == SRT_ATTEMPT_ACCEPTED) {
+      if (n < max_rows) memcpy(rows + SRT_ROW_DOUBLES * n, row, sizeof row);
+      ++n;
+    }
+  }
+  *stopcond = st.stopcond;
+  *nrej = st.nrej;
+  *ncone = st.ncone;
+  *cone_exit = st.fixed_cone_exit;
+  return n;
+}
+
+template <int D, int I>
+static void plasma_n(const SrtModel& M, long n, const double* x, double* out) {
+  for (long i = 0; i < n; ++i) {
+    SrtPlasma p;
+    srt_plasma<D, I>(M, x + 3 * i, p);
+    double* o = out + 19 * i;
+    for (int s = 0; s < 4; ++s) { o[s] = M.qs[s]; o[4 + s] = p.Ns[s]; o[8 + s] = M.ms[s]; o[12 + s] = 0.0; }
+    for (int c = 0; c < 3; ++c) o[16 + c] = p.B0[c];
+  }
+}
+extern "C" {
+void* emu_model_ngo(const char* cfg, int yearday, int msec, int use_igrf) {
+  SrtModel* M = new SrtModel();
+  memset(M, 0, sizeof *M);
+  if (srt_host::load_ngo_config(cfg, *M) != 0) { delete M; return nullptr; }
+  srt_host::set_time(*M, yearday, msec);
+  M->use_igrf = use_igrf;
+#ifdef EMU_HAVE_GRID
+  srt_host::igrf_recalc(yearday, msec, M->igrf);
+#endif
+  return M;
+}
+#ifdef EMU_HAVE_GRID
+void* emu_model_grid(const char* path, int yearday, int msec, int use_igrf) {
+  SrtModel* M = new SrtModel();
+  memset(M, 0, sizeof *M);
+  srt_host::HostGrid* hg = new srt_host::HostGrid();
+  if (srt_host::load_grid(path, *M, *hg) != 0) { delete M; delete hg; return nullptr; }
+  M->grid.nodes = hg->nodes.data();
+  M->grid.xs = hg->xs.data(); M->grid.ys = hg->ys.data(); M->grid.zs = hg->zs.data();
+  srt_host::set_time(*M, yearday, msec);
+  M->use_igrf = use_igrf;
+  srt_host::igrf_recalc(yearday, msec, M->igrf);
+  return M;  // hg leaks with the model: test-only
+}
+#endif
+void emu_model_free(void* m) { delete (SrtModel*)m; }
+void emu_model_get(void* m, double* out /* ane0, cos_mu, sin_mu, del */) {
+  SrtModel* M = (SrtModel*)m;
+  out[0] = M->ngo.ane0; out[1] = M->cos_mu; out[2] = M->sin_mu; out[3] = M->del;
+}
+
+void emu_plasma(void* m, long n, const double* x, double* out) {
+  const SrtModel& M = *(SrtModel*)m;
+  if (M.density == SRT_DENS_NGO) { if (M.use_igrf) plasma_n<0, 1>(M, n, x, out); else plasma_n<0, 0>(M, n, x, out); }
+  else { if (M.use_igrf) plasma_n<1, 1>(M, n, x, out); else plasma_n<1, 0>(M, n, x, out); }
+}
+int emu_is_right_handed(double n2, double phi, double S, double D, double P) { return srt_is_right_handed(n2, phi, S, D, P) ? 1 : 0; }
+
+long emu_trace(void* m, const double* pos0, double* dir0, double w0, double dt0, double dtmax, double maxerr, int maxsteps, double minalt,
+               int root, double tmax, int fixedstep, double* rows, long max_rows, int* stopcond, long* nrej, long* ncone, int* cone_exit) {
+  const SrtModel& M = *(SrtModel*)m;
+  SrtRunParams P = {dt0, dtmax, maxerr, minalt, tmax, maxsteps, root, fixedstep, 1};
+  if (M.density == SRT_DENS_NGO) {
+    if (M.use_igrf) return run_one<0, 1>(M, P, pos0, dir0, w0, rows, max_rows, stopcond, nrej, ncone, cone_exit);
+    return run_one<0, 0>(M, P, pos0, dir0, w0, rows, max_rows, stopcond, nrej, ncone, cone_exit);
+  }
+  if (M.use_igrf) return run_one<1, 1>(M, P, pos0, dir0, w0, rows, max_rows, stopcond, nrej, ncone, cone_exit);
+  return run_one<1, 0>(M, P, pos0, dir0, w0, rows, max_rows, stopcond, nrej, ncone, cone_exit);
+}
+}

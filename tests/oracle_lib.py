@@ -1,0 +1,152 @@
+"""ctypes wrapper over the CPU oracle (oracle/_build/libsrt_oracle*.so).
+
+Test infrastructure only: imported by tests/, bench.py's cpu_baseline / --impl reference
+legs and __graft_entry__.smoke().  Never imported by the product package.
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORC_DIR = os.path.join(ROOT, "oracle")
+ROW = 20
+R_E = 6371.2e3
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", ORC_DIR])
+
+
+_libs = {}
+
+
+def lib(libm=False):
+    name = "libsrt_oracle_libm.so" if libm else "libsrt_oracle.so"
+    if name in _libs:
+        return _libs[name]
+    path = os.path.join(ORC_DIR, "_build", name)
+    if not os.path.exists(path):
+        build()
+    L = C.CDLL(path)
+    vp, d, i, l = C.c_void_p, C.c_double, C.c_int, C.c_long
+    L.orc_model_ngo.restype = vp
+    L.orc_model_ngo.argtypes = [C.c_char_p, i, i, i, i]
+    if hasattr(L, "orc_model_grid"):
+        L.orc_model_grid.restype = vp
+        L.orc_model_grid.argtypes = [C.c_char_p, i, i, i, i]
+    L.orc_model_free.argtypes = [vp]
+    L.orc_model_del.restype = d
+    L.orc_model_del.argtypes = [vp]
+    L.orc_plasma.argtypes = [vp, l, vp, vp]
+    L.orc_dispersion_relation.restype = d
+    L.orc_dispersion_relation.argtypes = [vp, vp, d, vp]
+    L.orc_stix.argtypes = [vp, d, vp, vp]
+    L.orc_evalrhs.argtypes = [vp, vp, vp]
+    L.orc_solve.argtypes = [vp, vp, d, vp, vp]
+    L.orc_is_right_handed.restype = i
+    L.orc_is_right_handed.argtypes = [d, d, d, d, d]
+    L.orc_form_dispersion_matrix.argtypes = [d, d, d, d, d, vp]
+    L.orc_trace.restype = vp
+    L.orc_trace.argtypes = [vp, vp, vp, d, d, d, d, i, d, i, d, i]
+    for f in ("nrows", "nrejected", "ncone", "plasma_calls"):
+        getattr(L, "orc_trace_" + f).restype = l
+        getattr(L, "orc_trace_" + f).argtypes = [vp]
+    L.orc_trace_stopcond.restype = i
+    L.orc_trace_stopcond.argtypes = [vp]
+    L.orc_trace_fixed_cone_exit.restype = i
+    L.orc_trace_fixed_cone_exit.argtypes = [vp]
+    L.orc_trace_dir0.argtypes = [vp, vp]
+    L.orc_trace_rows.argtypes = [vp, vp]
+    L.orc_trace_species.argtypes = [vp, vp]
+    L.orc_trace_free.argtypes = [vp]
+    L.orc_trace_batch_summary.restype = l
+    L.orc_trace_batch_summary.argtypes = [vp, l, vp, vp, vp, d, d, d, i, d, i, d, i, vp, vp, vp, vp]
+    _libs[name] = L
+    return L
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class OracleModel:
+    def __init__(self, kind, path, yearday=2010001, msec=0, use_igrf=0, libm=False, faithful_cost=False):
+        self.L = lib(libm)
+        fn = self.L.orc_model_ngo if kind == "ngo" else self.L.orc_model_grid
+        self.h = fn(path.encode(), yearday, msec, use_igrf, int(faithful_cost))
+        if not self.h:
+            raise RuntimeError("oracle model setup failed: %s" % path)
+        self.del_ = self.L.orc_model_del(self.h)
+
+    def close(self):
+        if self.h:
+            self.L.orc_model_free(self.h)
+            self.h = None
+
+    def plasma(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64).reshape(-1, 3)
+        out = np.empty((len(x), 19))
+        self.L.orc_plasma(self.h, len(x), _p(x), _p(out))
+        return out
+
+    def dispersion_relation(self, n, w, x):
+        n = np.ascontiguousarray(n, dtype=np.float64)
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        return self.L.orc_dispersion_relation(self.h, _p(n), w, _p(x))
+
+    def stix(self, w, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        o = np.empty(5)
+        self.L.orc_stix(self.h, w, _p(x), _p(o))
+        return dict(zip("SDPRL", o))
+
+    def evalrhs(self, args7):
+        a = np.ascontiguousarray(args7, dtype=np.float64)
+        o = np.empty(7)
+        self.L.orc_evalrhs(self.h, _p(a), _p(o))
+        return o
+
+    def solve(self, k, w, x):
+        k = np.ascontiguousarray(k, dtype=np.float64)
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        o = np.empty(4)
+        self.L.orc_solve(self.h, _p(k), w, _p(x), _p(o))
+        return complex(o[0], o[1]), complex(o[2], o[3])
+
+    def trace(self, pos0, dir0, w0, dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep):
+        pos0 = np.ascontiguousarray(pos0, dtype=np.float64)
+        dir0 = np.ascontiguousarray(dir0, dtype=np.float64)
+        t = self.L.orc_trace(self.h, _p(pos0), _p(dir0), w0, dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep)
+        n = self.L.orc_trace_nrows(t)
+        rows = np.empty((n, ROW))
+        self.L.orc_trace_rows(t, _p(rows))
+        d = np.empty(3)
+        self.L.orc_trace_dir0(t, _p(d))
+        sp = np.empty(12)
+        self.L.orc_trace_species(t, _p(sp))
+        res = dict(rows=rows, stopcond=self.L.orc_trace_stopcond(t), nrejected=self.L.orc_trace_nrejected(t),
+                   ncone=self.L.orc_trace_ncone(t), plasma_calls=self.L.orc_trace_plasma_calls(t),
+                   fixed_cone_exit=self.L.orc_trace_fixed_cone_exit(t), dir0=d, qs=sp[0:4], ms=sp[4:8], nus=sp[8:12])
+        self.L.orc_trace_free(t)
+        return res
+
+    def trace_batch_summary(self, pos0, dir0, w0, dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep):
+        pos0 = np.ascontiguousarray(pos0, dtype=np.float64).reshape(-1, 3)
+        dir0 = np.ascontiguousarray(dir0, dtype=np.float64).reshape(-1, 3)
+        w0 = np.ascontiguousarray(w0, dtype=np.float64)
+        n = len(w0)
+        last = np.empty((n, ROW))
+        nrows = np.empty(n, dtype=np.int64)
+        stop = np.empty(n, dtype=np.int32)
+        nrej = np.empty(n, dtype=np.int64)
+        acc = self.L.orc_trace_batch_summary(self.h, n, _p(pos0), _p(dir0), _p(w0), dt0, dtmax, maxerr, maxsteps, minalt, root,
+                                             tmax, fixedstep, _p(last), _p(nrows), _p(stop), _p(nrej))
+        return dict(accepted=acc, last_row=last, nrows=nrows, stopcond=stop, nrejected=nrej)
+
+
+def launch_point(lat_deg, lon_deg=0.0, alt_km=1000.0):
+    """SM position of a launch point (radius R_E + alt)."""
+    r = R_E + alt_km * 1e3
+    la, lo = np.deg2rad(lat_deg), np.deg2rad(lon_deg)
+    return np.array([r * np.cos(la) * np.cos(lo), r * np.cos(la) * np.sin(lo), r * np.sin(la)])
