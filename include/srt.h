@@ -1,0 +1,120 @@
+/* srt.h -- C ABI of libsrt.so: batched Haselgrove ray integration on one B200.
+ *
+ * The reference has no C ABI; what this library replaces is the Fortran call
+ *   call raytracer_run(pos,time,vprel,vgrel,n,B0,qs,ms,Ns,nus,stopcond, pos0,dir0,w,
+ *        dt0,dtmax,maxerr,maxsteps,minalt,root,tmax,fixedstep,del,funcPlasmaParams,data,
+ *        raytracer_stopconditions)
+ * made once per input ray by fortran/raytracer_driver.f95:1154-1194 (signature
+ * fortran/raytracer.f95:609-642), together with the model set-up that precedes it
+ * (ngosetup, driver:256-369; interpsetup, driver:497-615).  The per-ray call becomes
+ * one srt_trace_batch() over all rays of the input file.  `funcPlasmaParams` cannot
+ * cross to the device as a callback: the two adapters on the hot path are built-in
+ * models (srt_model_ngo = modelnum 1, srt_model_grid = modelnum 3), and `del` is
+ * implied by the model (delSP = 1e-4 / delDP = 1e-6, driver:251-252,1158,1170).
+ *
+ * Conventions: plain C types; every call returns 0 or a negative SRT_E_* code (never
+ * exits); input arrays are caller-owned; the result object is library-owned until
+ * srt_result_free().  A call uses the CUDA device selected by srt_init() for the
+ * calling process (one process per GPU; rays shard across processes by index, no
+ * collective).  There is no CPU fallback: without a CUDA device every compute call
+ * fails with SRT_E_NODEVICE.
+ *
+ * INTEGRATION.md shows the ISO_C_BINDING interface block and the patched driver loop.
+ */
+#ifndef SRT_H
+#define SRT_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SRT_OK 0
+#define SRT_E_NODEVICE -1   /* no usable CUDA device */
+#define SRT_E_IO -2         /* cannot open / parse a model file */
+#define SRT_E_ARG -3        /* invalid argument */
+#define SRT_E_UNSUPPORTED -4 /* e.g. use_tsyganenko != 0 */
+#define SRT_E_CUDA -5       /* CUDA runtime error (srt_last_cuda_error()) */
+#define SRT_E_NOMEM -6      /* trajectory log cannot hold even one ray */
+
+/* one recorded trajectory row: the non-constant columns that driver:1197-1217 writes */
+#define SRT_ROW_DOUBLES 20
+#define SRT_ROW_T 0      /* time            */
+#define SRT_ROW_POS 1    /* pos(3)          */
+#define SRT_ROW_VPREL 4  /* vprel(3)        */
+#define SRT_ROW_VGREL 7  /* vgrel(3)        */
+#define SRT_ROW_N 10     /* n(3)            */
+#define SRT_ROW_B0 13    /* B0(3)           */
+#define SRT_ROW_NS 16    /* Ns(nspec<=4)    */
+
+/* per-ray flag bits (srt_result_flags) */
+#define SRT_FLAG_FIXED_CONE_EXIT 1 /* fixed-step run left the resonance cone and returned with
+                                      stopcond 0 (raytracer.f95:900-905) */
+
+typedef struct srt_model srt_model;
+typedef struct srt_result srt_result;
+
+/* the scalar arguments of raytracer_run (raytracer.f95:620-623) + the driver's outputper (driver:223-228) */
+typedef struct srt_run_params {
+  double dt0, dtmax, maxerr, minalt, tmax;
+  int32_t maxsteps, root, fixedstep, outputper;
+} srt_run_params;
+
+/* Selects the CUDA device of this process.  device < 0: keep the current one. */
+int srt_init(int device);
+const char* srt_strerror(int code);
+const char* srt_last_cuda_error(void);
+
+/* modelnum 1 -- ngosetup + ngoStateData (driver:256-369; ngo_dens_model_adapter.f95:15-29,42-51) */
+int srt_model_ngo(srt_model** m, const char* ngo_configfile, int yearday, int milliseconds_day, int use_igrf, int use_tsyganenko);
+/* modelnum 3 -- interpsetup + interpStateData (driver:497-615; interp_dens_model_adapter.f95:16-39,52-134) */
+int srt_model_grid(srt_model** m, const char* interp_interpfile, int yearday, int milliseconds_day, int use_igrf, int use_tsyganenko);
+void srt_model_free(srt_model* m);
+/* qs, ms, nus as the adapter returns them on every call (constant per model) */
+int srt_model_species(const srt_model* m, int* nspec, double* qs, double* ms, double* nus);
+/* funcPlasmaParams at n points (host arrays): out[n][19] = qs4, Ns4, ms4, nus4, B0(3).
+ * The parity surface of fortran/dumpmodel.f95:374-378,649-653. */
+int srt_model_eval(const srt_model* m, int64_t n, const double* x /*[n][3]*/, double* out /*[n][19]*/);
+
+/* raytracer_run for nrays rays, host buffers.  pos0[nrays][3], dir0[nrays][3] (inout: an all-zero
+ * direction is replaced by the field-aligned one, raytracer.f95:661-674), w0[nrays]. */
+int srt_trace_batch(const srt_model* m, int64_t nrays, const double* pos0, double* dir0, const double* w0, const srt_run_params* p,
+                    srt_result** out);
+
+int64_t srt_result_nrays(const srt_result* r);
+int64_t srt_result_total_rows(const srt_result* r);     /* rows held (after outputper decimation) */
+int64_t srt_result_accepted_steps(const srt_result* r); /* sum over rays of (rows the reference would hold - 1) */
+int64_t srt_result_attempts(const srt_result* r);       /* accepted + rejected + cone-refined attempts */
+/* per ray */
+int64_t srt_result_nrows(const srt_result* r, int64_t ray);       /* rows held for this ray = ceil(nsteps/outputper) */
+int64_t srt_result_nsteps(const srt_result* r, int64_t ray);      /* size(time) in the reference */
+int srt_result_stopcond(const srt_result* r, int64_t ray);
+int srt_result_flags(const srt_result* r, int64_t ray);
+int srt_result_copy_ray(const srt_result* r, int64_t ray, double* rows /*[nrows][SRT_ROW_DOUBLES]*/);
+/* zero-copy view: *rows points at the rows of `ray` (row-major [nrows][20]) */
+int srt_result_ray_view(const srt_result* r, int64_t ray, const double** rows, int64_t* nrows);
+/* endpoint summary for all rays (any pointer may be NULL) */
+int srt_result_summary(const srt_result* r, double* last_row /*[nrays][20]*/, int64_t* nsteps, int64_t* nrejected, int32_t* stopcond);
+void srt_result_free(srt_result* r);
+
+/* Device-resident variant (pipelines, bench `value`): inputs already in HBM, outputs stay there.
+ *   d_rays      [7][nrays] structure-of-arrays: pos0 x,y,z; dir0 x,y,z; w0   (dir0 rows are updated in place)
+ *   d_log       [log_capacity][21] append log: word 0 = (ray | row_index << 32) bit pattern, words 1..20 = the row
+ *   d_summary   [nrays][24]: words 0..19 last row, 20 nsteps, 21 stopcond, 22 rejected+cone attempts, 23 flags
+ *               (integers stored as doubles)
+ *   d_counters  [8] uint64: log rows used, accepted steps, attempts, rays dropped because the log was full,
+ *               ray-queue head, 3 spare (zeroed by the call)
+ * stream: a cudaStream_t (NULL = default stream).  Asynchronous: returns after the launch. */
+int srt_trace_batch_device(const srt_model* m, int64_t nrays, double* d_rays, const srt_run_params* p, double* d_log, int64_t log_capacity,
+                           double* d_summary, uint64_t* d_counters, void* stream);
+/* kernels launched by this library since srt_init (for bench.py's gpu_launches) */
+int64_t srt_launch_count(void);
+/* name, registers/thread, local bytes/thread, blocks/SM and grid of the trace kernel chosen for this model */
+int srt_kernel_info(const srt_model* m, int* regs, int* local_bytes, int* blocks_per_sm, int* grid, int* block);
+/* FP64 pipe micro-benchmark used as the roofline denominator: runs `iters` dependent-free DFMA (fma=1)
+ * or DMUL+DADD pairs (fma=0) per thread on a full grid; returns achieved GFLOP/s in *gflops. */
+int srt_fp64_peak(int fma, int iters, double* gflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

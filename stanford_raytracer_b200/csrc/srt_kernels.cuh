@@ -1,0 +1,195 @@
+// srt_kernels.cuh -- sm_100a kernels of the hot path.
+//
+//   srt_trace_kernel    persistent one-thread-per-ray integrator (raytracer_run,
+//                       fortran/raytracer.f95:609-995) with a warp-aggregated ray queue:
+//                       a lane whose ray terminated pulls the next ray index at the top
+//                       of the loop, so a finished ray never idles its lane while the
+//                       rest of the warp keeps stepping; a rejected attempt keeps its
+//                       lane (it retries with the smaller dt, :790-798).
+//   srt_scatter_kernel  orders the append log by (ray, row) for the host gather.
+//   srt_eval_kernel     funcPlasmaParams at n points (the dumpmodel parity surface).
+//   srt_fp64_peak_kernel  FP64 pipe micro-benchmark: the roofline denominator.
+//
+// Bound: FP64 (non-tensor) pipe; nothing here is a dense contraction, so no tensor
+// cores, no TMA.  HBM traffic = 168 B per recorded row + 56 B per ray in, 192 B per ray
+// out; the model lives in __constant__ memory (c_srt_model).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "srt_physics.h"
+#include "srt_igrf.h"
+#include "srt_tricubic.h"
+
+#define SRT_LOG_WORDS 21      // header word + SRT_ROW_DOUBLES
+#define SRT_SUMMARY_WORDS 24  // last row + nsteps, stopcond, rejected, flags
+#define SRT_FLAG_CONE_EXIT 1
+#define SRT_FLAG_DROPPED 2    // log full: the ray was abandoned and must be re-run
+
+struct SrtBatch {
+  long long nrays;
+  double* rays;                     // SoA [7][nrays]
+  double* log;                      // [capacity][SRT_LOG_WORDS]
+  unsigned long long log_capacity;
+  double* summary;                  // [nrays][SRT_SUMMARY_WORDS]
+  unsigned long long* counters;     // [0] log rows, [1] accepted steps, [2] attempts, [3] dropped rays, [4] ray queue head
+  unsigned* nlogged;                // optional [nrays]: rows this ray put in the log
+};
+
+__device__ __forceinline__ void srt_log_row(const SrtBatch& B, long long ray, int rowidx, const double row[SRT_ROW_DOUBLES], bool& dropped) {
+  if (!B.log) return;  // summary-only run: nothing is recorded, nothing is dropped
+  unsigned long long slot = atomicAdd(&B.counters[0], 1ull);
+  if (slot >= B.log_capacity) { dropped = true; return; }
+  double* dst = B.log + slot * SRT_LOG_WORDS;
+  unsigned long long hdr = (unsigned long long)(unsigned)ray | ((unsigned long long)(unsigned)rowidx << 32);
+  dst[0] = __longlong_as_double((long long)hdr);
+#pragma unroll
+  for (int i = 0; i < SRT_ROW_DOUBLES; ++i) dst[1 + i] = row[i];
+}
+
+template <int DENS, int USE_IGRF>
+__global__ void __launch_bounds__(SRT_BLOCK_THREADS) srt_trace_kernel(const __grid_constant__ SrtRunParams P, const __grid_constant__ SrtBatch B) {
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const SrtModelRef MR = SrtModelRef();
+  SrtRayState st;
+  double row[SRT_ROW_DOUBLES];
+  bool active = false, exhausted = false, dropped = false;
+  long long slot = -1, ray = -1;
+  unsigned nlog = 0;
+  unsigned long long my_accepted = 0, my_attempts = 0;
+  const int outputper = P.outputper < 1 ? 1 : P.outputper;
+
+  for (;;) {
+    // ---- refill: every idle lane of the warp takes the next ray with ONE atomic per warp
+    const unsigned need = __ballot_sync(full, !active && !exhausted);
+    if (need) {
+      const int leader = __ffs(need) - 1;
+      unsigned long long base = 0;
+      if (lane == leader) base = atomicAdd(&B.counters[4], (unsigned long long)__popc(need));
+      base = __shfl_sync(full, base, leader);
+      if (!active && !exhausted) {
+        slot = (long long)(base + __popc(need & ((1u << lane) - 1u)));
+        if (slot >= B.nrays) {
+          exhausted = true;
+        } else {
+          ray = slot;
+          // coalesced SoA loads: neighbouring lanes hold neighbouring rays
+          double pos0[3] = {B.rays[0 * B.nrays + slot], B.rays[1 * B.nrays + slot], B.rays[2 * B.nrays + slot]};
+          double dir0[3] = {B.rays[3 * B.nrays + slot], B.rays[4 * B.nrays + slot], B.rays[5 * B.nrays + slot]};
+          double w0 = B.rays[6 * B.nrays + slot];
+          srt_ray_init<DENS, USE_IGRF>(MR, P, pos0, dir0, w0, st, row);
+          B.rays[3 * B.nrays + slot] = dir0[0];
+          B.rays[4 * B.nrays + slot] = dir0[1];
+          B.rays[5 * B.nrays + slot] = dir0[2];
+          active = true;
+          dropped = false;
+          nlog = 0;
+          srt_log_row(B, ray, 0, row, dropped);
+          if (!dropped) nlog = 1;
+        }
+      }
+    }
+    if (__ballot_sync(full, active) == 0u) break;  // queue empty and every lane finished
+
+    if (active) {
+      int r = SRT_ATTEMPT_DONE;
+      if (!dropped) {
+        double newrow[SRT_ROW_DOUBLES];
+        r = srt_ray_attempt<DENS, USE_IGRF>(MR, P, st, newrow);
+        if (r != SRT_ATTEMPT_DONE) ++my_attempts;
+        if (r == SRT_ATTEMPT_ACCEPTED) {
+          ++my_accepted;
+#pragma unroll
+          for (int i = 0; i < SRT_ROW_DOUBLES; ++i) row[i] = newrow[i];
+          const int rowidx = st.nstep - 1;  // 0-based index of the row just recorded
+          if (rowidx % outputper == 0) {
+            srt_log_row(B, ray, rowidx / outputper, row, dropped);
+            if (!dropped) ++nlog;
+          }
+        }
+      }
+      if (r == SRT_ATTEMPT_DONE) {
+        double* s = B.summary + slot * SRT_SUMMARY_WORDS;
+#pragma unroll
+        for (int i = 0; i < SRT_ROW_DOUBLES; ++i) s[i] = row[i];
+        s[20] = (double)st.nstep;
+        s[21] = (double)st.stopcond;
+        s[22] = (double)(st.nrej + st.ncone);
+        s[23] = (double)((st.fixed_cone_exit ? SRT_FLAG_CONE_EXIT : 0) | (dropped ? SRT_FLAG_DROPPED : 0));
+        if (B.nlogged) B.nlogged[slot] = dropped ? 0u : nlog;
+        if (dropped) atomicAdd(&B.counters[3], 1ull);
+        active = false;
+      }
+    }
+  }
+  // per-warp totals -> two atomics per warp
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    my_accepted += __shfl_down_sync(full, my_accepted, o);
+    my_attempts += __shfl_down_sync(full, my_attempts, o);
+  }
+  if (lane == 0) {
+    atomicAdd(&B.counters[1], my_accepted);
+    atomicAdd(&B.counters[2], my_attempts);
+  }
+}
+
+// log[slot] -> sorted[offsets[ray] + row]; entries of dropped rays are skipped
+__global__ void srt_scatter_kernel(const double* __restrict__ log, unsigned long long nlog, const unsigned long long* __restrict__ offsets,
+                                   const unsigned* __restrict__ nlogged, double* __restrict__ sorted) {
+  // one warp per log entry: 21 words in, 20 words out, coalesced both ways
+  const unsigned long long warp = (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+  for (unsigned long long e = warp; e < nlog; e += nwarps) {
+    const double* src = log + e * SRT_LOG_WORDS;
+    unsigned long long hdr = (unsigned long long)__double_as_longlong(src[0]);
+    unsigned ray = (unsigned)(hdr & 0xffffffffull), rowidx = (unsigned)(hdr >> 32);
+    long long slot = (long long)ray;
+    if (nlogged[slot] == 0u) continue;
+    double* dst = sorted + (offsets[slot] + rowidx) * SRT_ROW_DOUBLES;
+    if (lane < SRT_ROW_DOUBLES) dst[lane] = src[1 + lane];
+  }
+}
+
+template <int DENS, int USE_IGRF>
+__global__ void srt_eval_kernel(long long n, const double* __restrict__ x, double* __restrict__ out) {
+  const SrtModelRef MR = SrtModelRef();
+  const SrtModel& M = MR.get();
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    double xx[3] = {x[3 * i], x[3 * i + 1], x[3 * i + 2]};
+    SrtPlasma p;
+    srt_plasma<DENS, USE_IGRF>(MR, xx, p);
+    double* o = out + 19 * i;
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      o[s] = M.qs[s];
+      o[4 + s] = p.Ns[s];
+      o[8 + s] = M.ms[s];
+      o[12 + s] = 0.0;
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) o[16 + c] = p.B0[c];
+  }
+}
+
+// FP64 pipe peak: 8 independent accumulator chains per thread
+template <int FMA>
+__global__ void srt_fp64_peak_kernel(int iters, double seed, double* out) {
+  double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const double m = 0.999999999, c = 1e-9;
+  for (int i = 0; i < iters; ++i) {
+    if (FMA) {
+      a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+      a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+    } else {
+      a0 = __dadd_rn(__dmul_rn(a0, m), c); a1 = __dadd_rn(__dmul_rn(a1, m), c);
+      a2 = __dadd_rn(__dmul_rn(a2, m), c); a3 = __dadd_rn(__dmul_rn(a3, m), c);
+      a4 = __dadd_rn(__dmul_rn(a4, m), c); a5 = __dadd_rn(__dmul_rn(a5, m), c);
+      a6 = __dadd_rn(__dmul_rn(a6, m), c); a7 = __dadd_rn(__dmul_rn(a7, m), c);
+    }
+  }
+  double s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+  if (s == 123.456) out[0] = s;  // keeps the loop alive; never true
+}

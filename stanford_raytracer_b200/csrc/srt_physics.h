@@ -31,6 +31,21 @@
 SRT_HD double srt_c_light() { return srt_sqrt(1.0 / SRT_EPS0 / (SRT_PI * 4e-7)); }
 #define SRT_R2D (180.0 / SRT_PI)
 
+
+// How device code reaches the model: the kernels read it from __constant__ memory
+// (operands fold into FP64 instructions as c[bank][offset]); host builds carry a pointer.
+#if defined(__CUDACC__)
+__constant__ SrtModel c_srt_model;
+#endif
+struct SrtModelRef {
+#if defined(__CUDA_ARCH__)
+  SRT_HD const SrtModel& get() const { return c_srt_model; }
+#else
+  const SrtModel* p;
+  SRT_HD const SrtModel& get() const { return *p; }
+#endif
+};
+
 struct SrtPlasma {
   double Ns[SRT_NSPEC];
   double B0[3];
@@ -226,8 +241,9 @@ SRT_HD void srt_igrf_gsw(const SrtIgrf& ig, float xgsw, float ygsw, float zgsw, 
 // base field in GSM [nT] rounded to real*4 (Q3), + 0.0 (fp32), *1e-9, rotated to SM.
 // For the dipole the caller passes the spherical coordinates of x it already has.
 template <int USE_IGRF>
-SRT_HD void srt_field_sm(const SrtModel& M, const double x[3], const double p[3], double sph, double cph, double sth, double cth,
+SRT_HD void srt_field_sm(SrtModelRef MR, const double x[3], const double p[3], double sph, double cph, double sth, double cth,
                          double B0[3]) {
+  const SrtModel& M = MR.get();
   float bx, by, bz;
   if (USE_IGRF) {
     double xg[3];
@@ -256,7 +272,8 @@ SRT_HD void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT_
 //   Ngo:  fortran/ngo_dens_model_adapter.f95:63-207
 //   grid: fortran/interp_dens_model_adapter.f95:148-269
 template <int DENS, int USE_IGRF>
-SRT_HD void srt_plasma(const SrtModel& M, const double x[3], SrtPlasma& o) {
+SRT_HD void srt_plasma(SrtModelRef MR, const double x[3], SrtPlasma& o) {
+  const SrtModel& M = MR.get();
   double p[3] = {0.0, 0.0, 0.0};
   double sph = 0.0, cph = 0.0, sth = 0.0, cth = 0.0;
   if (DENS == SRT_DENS_NGO || !USE_IGRF) {
@@ -282,13 +299,14 @@ SRT_HD void srt_plasma(const SrtModel& M, const double x[3], SrtPlasma& o) {
     srt_grid_density(M.grid, x, o.Ns);
   }
   if (!USE_IGRF) srt_sincos(p[1], sth, cth);
-  srt_field_sm<USE_IGRF>(M, x, p, sph, cph, sth, cth, o.B0);
+  srt_field_sm<USE_IGRF>(MR, x, p, sph, cph, sth, cth, o.B0);
 }
 
 // ------------------------------------------------------------------ Stix / dispersion
 // plasma-only parts of stix_parameters (raytracer.f95:92-93) and of the free-space
 // test (raytracer.f95:65)
-SRT_HD void srt_plasma_derive(const SrtModel& M, const SrtPlasma& pl, SrtPlasmaDerived& d) {
+SRT_HD void srt_plasma_derive(SrtModelRef MR, const SrtPlasma& pl, SrtPlasmaDerived& d) {
+  const SrtModel& M = MR.get();
   d.B0[0] = pl.B0[0]; d.B0[1] = pl.B0[1]; d.B0[2] = pl.B0[2];
   d.B0sq = srt_dot3(pl.B0, pl.B0);
   double B0mag = srt_sqrt(d.B0sq);
@@ -376,19 +394,21 @@ SRT_HD double srt_dFdw(const double k[3], double w, const SrtPlasmaDerived& d) {
 
 // one side of a dF/dx difference: plasma at xs, Stix at w, F(n)
 template <int DENS, int USE_IGRF>
-SRT_HDN double srt_F_at(const SrtModel& M, const double xs[3], const double n[3], double w) {
+SRT_HDN double srt_F_at(SrtModelRef MR, const double xs[3], const double n[3], double w) {
+  const SrtModel& M = MR.get();
   SrtPlasma pl;
   SrtPlasmaDerived d;
   SrtStix s;
-  srt_plasma<DENS, USE_IGRF>(M, xs, pl);
-  srt_plasma_derive(M, pl, d);
+  srt_plasma<DENS, USE_IGRF>(MR, xs, pl);
+  srt_plasma_derive(MR, pl, d);
   srt_stix(d, w, s);
   return srt_F(n, w, d, s);
 }
 
 // dispersion_relation_dFdx (raytracer.f95:215-263)
 template <int DENS, int USE_IGRF>
-SRT_HD void srt_dFdx(const SrtModel& M, const double k[3], double w, const double x[3], double out[3]) {
+SRT_HD void srt_dFdx(SrtModelRef MR, const double k[3], double w, const double x[3], double out[3]) {
+  const SrtModel& M = MR.get();
   const double C = srt_c_light();
   double n[3];
 #pragma unroll
@@ -399,8 +419,8 @@ SRT_HD void srt_dFdx(const SrtModel& M, const double k[3], double w, const doubl
     double xp[3] = {x[0], x[1], x[2]}, xn[3] = {x[0], x[1], x[2]};
     xp[i] = x[i] + dd;
     xn[i] = x[i] - dd;
-    double Fp = srt_F_at<DENS, USE_IGRF>(M, xp, n, w);
-    double Fn = srt_F_at<DENS, USE_IGRF>(M, xn, n, w);
+    double Fp = srt_F_at<DENS, USE_IGRF>(MR, xp, n, w);
+    double Fn = srt_F_at<DENS, USE_IGRF>(MR, xn, n, w);
     out[i] = (Fp - Fn) / dd / 2.0;
   }
 }
@@ -412,22 +432,24 @@ struct SrtCentre {
   SrtStix s;  // Stix set at (x, w)
 };
 template <int DENS, int USE_IGRF>
-SRT_HDN void srt_centre(const SrtModel& M, const double x[3], double w, SrtCentre& c) {
-  srt_plasma<DENS, USE_IGRF>(M, x, c.pl);
-  srt_plasma_derive(M, c.pl, c.d);
+SRT_HDN void srt_centre(SrtModelRef MR, const double x[3], double w, SrtCentre& c) {
+  const SrtModel& M = MR.get();
+  srt_plasma<DENS, USE_IGRF>(MR, x, c.pl);
+  srt_plasma_derive(MR, c.pl, c.d);
   srt_stix(c.d, w, c.s);
 }
 
 // raytracer_evalrhs (raytracer.f95:282-314): rhs[0:3] = -(dfdk/dfdw), rhs[3:6] = dfdx/dfdw
 // (rhs(7) = 0 is implicit).
 template <int DENS, int USE_IGRF>
-SRT_HD void srt_evalrhs(const SrtModel& M, const double x[3], const double k[3], double w, double rhs[6]) {
+SRT_HDN void srt_evalrhs(SrtModelRef MR, const double x[3], const double k[3], double w, double rhs[6]) {
+  const SrtModel& M = MR.get();
   SrtCentre c;
-  srt_centre<DENS, USE_IGRF>(M, x, w, c);
+  srt_centre<DENS, USE_IGRF>(MR, x, w, c);
   double dfdk[3], dfdx[3];
   srt_dFdk(k, w, c.d, c.s, dfdk);
   double dfdw = srt_dFdw(k, w, c.d);
-  srt_dFdx<DENS, USE_IGRF>(M, k, w, x, dfdx);
+  srt_dFdx<DENS, USE_IGRF>(MR, k, w, x, dfdx);
 #pragma unroll
   for (int i = 0; i < 3; ++i) rhs[i] = -(dfdk[i] / dfdw);
 #pragma unroll
@@ -617,10 +639,11 @@ SRT_HD void srt_fill_row(const SrtRayState& st, const SrtPlasma& pl, bool propag
 
 // raytracer.f95:661-742.  dir0 is inout (field-aligned convention when all zero).
 template <int DENS, int USE_IGRF>
-SRT_HD void srt_ray_init(const SrtModel& M, const SrtRunParams& P, const double pos0[3], double dir0[3], double w0, SrtRayState& st,
+SRT_HD void srt_ray_init(SrtModelRef MR, const SrtRunParams& P, const double pos0[3], double dir0[3], double w0, SrtRayState& st,
                          double row[SRT_ROW_DOUBLES]) {
+  const SrtModel& M = MR.get();
   SrtCentre c;
-  srt_centre<DENS, USE_IGRF>(M, pos0, w0, c);
+  srt_centre<DENS, USE_IGRF>(MR, pos0, w0, c);
   if (dir0[0] == 0 && dir0[1] == 0 && dir0[2] == 0) {
     double p[3], sth, cth, sph, cph;
     srt_cart_to_sph(pos0, p);
@@ -716,7 +739,8 @@ SRT_HD int srt_stopconditions(const SrtRayState& st, const SrtRunParams& P) {
 
 // One pass through the loop body of raytracer_run (:748-993).
 template <int DENS, int USE_IGRF>
-SRT_HD int srt_ray_attempt(const SrtModel& M, const SrtRunParams& P, SrtRayState& st, double row[SRT_ROW_DOUBLES]) {
+SRT_HD int srt_ray_attempt(SrtModelRef MR, const SrtRunParams& P, SrtRayState& st, double row[SRT_ROW_DOUBLES]) {
+  const SrtModel& M = MR.get();
   if (st.t >= P.tmax) { st.stopcond = 0; return SRT_ATTEMPT_DONE; }  // :749
   st.stopcond = srt_stopconditions(st, P);                           // :756
   if (st.stopcond != 0) return SRT_ATTEMPT_DONE;
@@ -725,7 +749,7 @@ SRT_HD int srt_ray_attempt(const SrtModel& M, const SrtRunParams& P, SrtRayState
   // ones recorded at the end of the previous step (same k, w, x); only dF/dx is new.
   if (!st.have_rhs1) {
     double dfdx[3];
-    srt_dFdx<DENS, USE_IGRF>(M, st.k, st.w, st.x, dfdx);
+    srt_dFdx<DENS, USE_IGRF>(MR, st.k, st.w, st.x, dfdx);
 #pragma unroll
     for (int i = 0; i < 3; ++i) st.rhs1[i] = -(st.dfdk[i] / st.dfdw);
 #pragma unroll
@@ -743,28 +767,28 @@ SRT_HD int srt_ray_attempt(const SrtModel& M, const SrtRunParams& P, SrtRayState
     double k2[6], k3[6], k4[6], k5[6], k6[6], tmp[6], r[6];
 #pragma unroll
     for (int i = 0; i < 6; ++i) tmp[i] = xs[i] + (SRT_A21 * k1[i]);
-    srt_evalrhs<DENS, USE_IGRF>(M, tmp, tmp + 3, st.w, r);
+    srt_evalrhs<DENS, USE_IGRF>(MR, tmp, tmp + 3, st.w, r);
 #pragma unroll
     for (int i = 0; i < 6; ++i) k2[i] = dt * r[i];
 #pragma unroll
     for (int i = 0; i < 6; ++i) tmp[i] = xs[i] + (SRT_A31 * k1[i] + SRT_A32 * k2[i]);
-    srt_evalrhs<DENS, USE_IGRF>(M, tmp, tmp + 3, st.w, r);
+    srt_evalrhs<DENS, USE_IGRF>(MR, tmp, tmp + 3, st.w, r);
 #pragma unroll
     for (int i = 0; i < 6; ++i) k3[i] = dt * r[i];
 #pragma unroll
     for (int i = 0; i < 6; ++i) tmp[i] = xs[i] + (SRT_A41 * k1[i] + SRT_A42 * k2[i] + SRT_A43 * k3[i]);
-    srt_evalrhs<DENS, USE_IGRF>(M, tmp, tmp + 3, st.w, r);
+    srt_evalrhs<DENS, USE_IGRF>(MR, tmp, tmp + 3, st.w, r);
 #pragma unroll
     for (int i = 0; i < 6; ++i) k4[i] = dt * r[i];
 #pragma unroll
     for (int i = 0; i < 6; ++i) tmp[i] = xs[i] + (SRT_A51 * k1[i] + SRT_A52 * k2[i] + SRT_A53 * k3[i] + SRT_A54 * k4[i]);
-    srt_evalrhs<DENS, USE_IGRF>(M, tmp, tmp + 3, st.w, r);
+    srt_evalrhs<DENS, USE_IGRF>(MR, tmp, tmp + 3, st.w, r);
 #pragma unroll
     for (int i = 0; i < 6; ++i) k5[i] = dt * r[i];
 #pragma unroll
     for (int i = 0; i < 6; ++i)
       tmp[i] = xs[i] + (SRT_A61 * k1[i] + SRT_A62 * k2[i] + SRT_A63 * k3[i] + SRT_A64 * k4[i] + SRT_A65 * k5[i]);
-    srt_evalrhs<DENS, USE_IGRF>(M, tmp, tmp + 3, st.w, r);
+    srt_evalrhs<DENS, USE_IGRF>(MR, tmp, tmp + 3, st.w, r);
 #pragma unroll
     for (int i = 0; i < 6; ++i) k6[i] = dt * r[i];
     double e1x[6];
@@ -785,9 +809,9 @@ SRT_HD int srt_ray_attempt(const SrtModel& M, const SrtRunParams& P, SrtRayState
       // dFdk at est1 and est2 with the local w (== x(7) after the first acceptance)
       SrtCentre c1;
       double g1[3], g2[3];
-      srt_centre<DENS, USE_IGRF>(M, e1x, st.wl, c1);
+      srt_centre<DENS, USE_IGRF>(MR, e1x, st.wl, c1);
       srt_dFdk(e1x + 3, st.wl, c1.d, c1.s, g1);
-      srt_centre<DENS, USE_IGRF>(M, e2x, st.wl, c1);
+      srt_centre<DENS, USE_IGRF>(MR, e2x, st.wl, c1);
       srt_dFdk(e2x + 3, st.wl, c1.d, c1.s, g2);
       double sc = 0.0, sd = 0.0;
 #pragma unroll
@@ -815,17 +839,17 @@ SRT_HD int srt_ray_attempt(const SrtModel& M, const SrtRunParams& P, SrtRayState
     double k2[6], k3[6], k4[6], tmp[6], r[6];
 #pragma unroll
     for (int i = 0; i < 6; ++i) tmp[i] = xs[i] + 1.0 / 2.0 * k1[i];
-    srt_evalrhs<DENS, USE_IGRF>(M, tmp, tmp + 3, st.w, r);
+    srt_evalrhs<DENS, USE_IGRF>(MR, tmp, tmp + 3, st.w, r);
 #pragma unroll
     for (int i = 0; i < 6; ++i) k2[i] = dt * r[i];
 #pragma unroll
     for (int i = 0; i < 6; ++i) tmp[i] = xs[i] + 1.0 / 2.0 * k2[i];
-    srt_evalrhs<DENS, USE_IGRF>(M, tmp, tmp + 3, st.w, r);
+    srt_evalrhs<DENS, USE_IGRF>(MR, tmp, tmp + 3, st.w, r);
 #pragma unroll
     for (int i = 0; i < 6; ++i) k3[i] = dt * r[i];
 #pragma unroll
     for (int i = 0; i < 6; ++i) tmp[i] = xs[i] + k3[i];
-    srt_evalrhs<DENS, USE_IGRF>(M, tmp, tmp + 3, st.w, r);
+    srt_evalrhs<DENS, USE_IGRF>(MR, tmp, tmp + 3, st.w, r);
 #pragma unroll
     for (int i = 0; i < 6; ++i) k4[i] = dt * r[i];
 #pragma unroll
@@ -834,7 +858,7 @@ SRT_HD int srt_ray_attempt(const SrtModel& M, const SrtRunParams& P, SrtRayState
   const double dtincr = dt;
   // re-project |k| onto the dispersion surface at the new point (:819-836)
   SrtCentre c2;
-  srt_centre<DENS, USE_IGRF>(M, e2x, st.w, c2);
+  srt_centre<DENS, USE_IGRF>(MR, e2x, st.w, c2);
   SrtCplx ksel = srt_solve_root(e2x + 3, st.w, c2.d, c2.s, P.root);
   // k = kmag*(k/sqrt(dot_product(k,k))) in complex arithmetic (Q18)
   double kk = 0.0;

@@ -1,0 +1,109 @@
+"""Shared helpers of the test-suite: builds, synthetic launch sets, ctypes
+wrapper of the test-only host emulation of the device physics."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+import oracle_lib as ol
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+DATA = os.path.join(ROOT, "tests", "data")
+NGO_CFG = os.path.join(DATA, "newray_default.in")
+BUILD = os.path.join(ROOT, "tests", "_build")
+R_E = 6371.2e3
+MINALT = R_E + 100e3
+
+C1 = dict(dt0=5e-4, dtmax=0.1, maxerr=5e-4, maxsteps=2000, minalt=MINALT, root=2, tmax=0.5, fixedstep=1)
+C2 = dict(dt0=1e-3, dtmax=0.1, maxerr=5e-4, maxsteps=20000, minalt=MINALT, root=2, tmax=10.0, fixedstep=0)
+
+
+def _newer(target, srcs):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in srcs)
+
+
+def build_hostemu():
+    os.makedirs(BUILD, exist_ok=True)
+    csrc = os.path.join(ROOT, "stanford_raytracer_b200", "csrc")
+    srcs = [os.path.join(csrc, f) for f in os.listdir(csrc)] + [os.path.join(ROOT, "tests", "csrc", "hostemu.cpp")]
+    out = os.path.join(BUILD, "libsrt_hostemu.so")
+    if _newer(out, srcs):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-fno-fast-math", "-DEMU_HAVE_GRID", "-shared", "-o", out,
+                               os.path.join(ROOT, "tests", "csrc", "hostemu.cpp")])
+    out2 = os.path.join(BUILD, "math_probe.so")
+    src2 = os.path.join(ROOT, "tests", "csrc", "math_probe.cpp")
+    if _newer(out2, [src2, os.path.join(csrc, "srt_math.h")]):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-shared", "-o", out2, src2])
+    return out
+
+
+def build_all():
+    ol.build()
+    build_hostemu()
+    from stanford_raytracer_b200 import build as b
+    b.build()
+
+
+def launch_grid(freqs_hz, lats_deg, lons_deg=(0.0,), alt_km=1000.0):
+    """Lattice of launch points: frequency slowest, then latitude, then longitude.
+    dir0 = 0 (field-aligned convention)."""
+    pos, w = [], []
+    for f in freqs_hz:
+        for la in lats_deg:
+            for lo in lons_deg:
+                pos.append(ol.launch_point(la, lo, alt_km))
+                w.append(2 * np.pi * f)
+    pos = np.array(pos)
+    return pos, np.zeros_like(pos), np.array(w)
+
+
+def c2_grid(nf=100, nlat=100, nlon=1):
+    freqs = np.logspace(np.log10(200.0), np.log10(30000.0), nf)
+    lats = np.linspace(10.0, 60.0, nlat)
+    lons = np.arange(nlon) * 36.0
+    return launch_grid(freqs, lats, lons)
+
+
+class HostEmu:
+    """tests/csrc/hostemu.cpp: the device physics compiled for the CPU (test-only)."""
+
+    def __init__(self, kind, path, yearday=2010001, msec=0, use_igrf=0):
+        build_hostemu()
+        E = C.CDLL(os.path.join(BUILD, "libsrt_hostemu.so"))
+        d, i, vp, l = C.c_double, C.c_int, C.c_void_p, C.c_long
+        E.emu_model_ngo.restype = vp
+        E.emu_model_ngo.argtypes = [C.c_char_p, i, i, i]
+        E.emu_model_grid.restype = vp
+        E.emu_model_grid.argtypes = [C.c_char_p, i, i, i]
+        E.emu_plasma.argtypes = [vp, l, vp, vp]
+        E.emu_is_right_handed.restype = i
+        E.emu_is_right_handed.argtypes = [d] * 5
+        E.emu_trace.restype = l
+        E.emu_trace.argtypes = [vp, vp, vp, d, d, d, d, i, d, i, d, i, vp, l, vp, vp, vp, vp]
+        self.E = E
+        fn = E.emu_model_ngo if kind == "ngo" else E.emu_model_grid
+        self.h = fn(path.encode(), yearday, msec, use_igrf)
+        if not self.h:
+            raise RuntimeError("hostemu model setup failed")
+
+    def plasma(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64).reshape(-1, 3)
+        out = np.empty((len(x), 19))
+        self.E.emu_plasma(self.h, len(x), x.ctypes.data, out.ctypes.data)
+        return out
+
+    def is_right_handed(self, n2, phi, S, D, P):
+        return bool(self.E.emu_is_right_handed(n2, phi, S, D, P))
+
+    def trace(self, pos0, dir0, w0, dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep):
+        pos0 = np.ascontiguousarray(pos0, dtype=np.float64)
+        dir0 = np.array(dir0, dtype=np.float64)
+        rows = np.empty((maxsteps + 1, 20))
+        sc, nr, nc, ce = C.c_int(), C.c_long(), C.c_long(), C.c_int()
+        n = self.E.emu_trace(self.h, pos0.ctypes.data, dir0.ctypes.data, w0, dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep,
+                             rows.ctypes.data, len(rows), C.byref(sc), C.byref(nr), C.byref(nc), C.byref(ce))
+        return dict(rows=rows[:n].copy(), stopcond=sc.value, nrejected=nr.value, ncone=nc.value, fixed_cone_exit=ce.value, dir0=dir0)

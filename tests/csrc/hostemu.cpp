@@ -17,12 +17,12 @@ static long run_one(const SrtModel& M, const SrtRunParams& P, const double* pos0
                     int* stopcond, long* nrej, long* ncone, int* cone_exit) {
   SrtRayState st;
   double row[SRT_ROW_DOUBLES];
-  srt_ray_init<D, I>(M, P, pos0, dir0, w0, st, row);
+  srt_ray_init<D, I>(SrtModelRef{&M}, P, pos0, dir0, w0, st, row);
   long n = 0;
   if (n < max_rows) memcpy(rows + SRT_ROW_DOUBLES * n, row, sizeof row);
   ++n;
   for (;;) {
-    int r = srt_ray_attempt<D, I>(M, P, st, row);
+    int r = srt_ray_attempt<D, I>(SrtModelRef{&M}, P, st, row);
     if (r == SRT_ATTEMPT_DONE) break;
     if (r == SRT_ATTEMPT_ACCEPTED) {
       if (n < max_rows) memcpy(rows + SRT_ROW_DOUBLES * n, row, sizeof row);
@@ -40,7 +40,7 @@ template <int D, int I>
 static void plasma_n(const SrtModel& M, long n, const double* x, double* out) {
   for (long i = 0; i < n; ++i) {
     SrtPlasma p;
-    srt_plasma<D, I>(M, x + 3 * i, p);
+    srt_plasma<D, I>(SrtModelRef{&M}, x + 3 * i, p);
     double* o = out + 19 * i;
     for (int s = 0; s < 4; ++s) { o[s] = M.qs[s]; o[4 + s] = p.Ns[s]; o[8 + s] = M.ms[s]; o[12 + s] = 0.0; }
     for (int c = 0; c < 3; ++c) o[16 + c] = p.B0[c];
