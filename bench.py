@@ -277,7 +277,7 @@ def main():
                 "attempted_steps_per_sec": total_attempts / (kernel_ms_max * 1e-3),
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": int(launches), "clocks": sampler.result(), "roofline": roofline, "cpu_baseline": cpu,
-                "kernel": model.kernel_info()}
+                "kernel": model.kernel_info(nrays)}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -108,8 +108,9 @@ int srt_trace_batch_device(const srt_model* m, int64_t nrays, double* d_rays, co
                            double* d_summary, uint64_t* d_counters, void* stream);
 /* kernels launched by this library since srt_init (for bench.py's gpu_launches) */
 int64_t srt_launch_count(void);
-/* name, registers/thread, local bytes/thread, blocks/SM and grid of the trace kernel chosen for this model */
-int srt_kernel_info(const srt_model* m, int* regs, int* local_bytes, int* blocks_per_sm, int* grid, int* block);
+/* which trace kernel a batch of nrays rays runs (mode 0: one thread per ray, 1: team of 8 lanes per ray;
+ * SRT_KERNEL=thread|team overrides), its registers/thread, local bytes/thread, blocks/SM, persistent grid, block */
+int srt_kernel_info(const srt_model* m, int64_t nrays, int* mode, int* regs, int* local_bytes, int* blocks_per_sm, int* grid, int* block);
 /* FP64 pipe micro-benchmark used as the roofline denominator: runs `iters` dependent-free DFMA (fma=1)
  * or DMUL+DADD pairs (fma=0) per thread on a full grid; returns achieved GFLOP/s in *gflops. */
 int srt_fp64_peak(int fma, int iters, double* gflops);

@@ -72,7 +72,7 @@ def lib():
     L.srt_result_free.restype = None
     L.srt_trace_batch_device.argtypes = [vp, i64, vp, C.POINTER(RunParams), vp, i64, vp, vp, vp]
     L.srt_launch_count.restype = i64
-    L.srt_kernel_info.argtypes = [vp] + [C.POINTER(i)] * 5
+    L.srt_kernel_info.argtypes = [vp, i64] + [C.POINTER(i)] * 6
     L.srt_fp64_peak.argtypes = [i, i, C.POINTER(d)]
     _lib = L
     return L
@@ -124,10 +124,12 @@ class Model:
         _check(lib().srt_model_eval(self._h, len(x), _ptr(x), _ptr(out)), "srt_model_eval")
         return dict(qs=out[:, 0:4], Ns=out[:, 4:8], ms=out[:, 8:12], nus=out[:, 12:16], B0=out[:, 16:19], raw=out)
 
-    def kernel_info(self):
-        v = [C.c_int() for _ in range(5)]
-        _check(lib().srt_kernel_info(self._h, *[C.byref(t) for t in v]), "srt_kernel_info")
-        return dict(zip(("regs", "local_bytes", "blocks_per_sm", "grid", "block"), [t.value for t in v]))
+    def kernel_info(self, nrays):
+        v = [C.c_int() for _ in range(6)]
+        _check(lib().srt_kernel_info(self._h, int(nrays), *[C.byref(t) for t in v]), "srt_kernel_info")
+        d = dict(zip(("mode", "regs", "local_bytes", "blocks_per_sm", "grid", "block"), [t.value for t in v]))
+        d["mode"] = "team8" if d["mode"] else "thread"
+        return d
 
 
 def ngosetup(ngo_configfile, yearday=0, milliseconds_day=0, use_igrf=0, use_tsyganenko=0):

@@ -2,6 +2,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo (build.py).
 #define SRT_BLOCK_THREADS 64
 #include "srt_kernels.cuh"
+#include "srt_team.cuh"
 #include "srt_host_setup.h"
 #include "srt_grid_setup.h"
 #include "srt_igrf_setup.h"
@@ -53,6 +54,10 @@ int ensure_device() {
 typedef void (*trace_kernel_t)(const SrtRunParams, const SrtBatch);
 typedef void (*eval_kernel_t)(long long, const double*, double*);
 
+trace_kernel_t pick_team(const SrtModel& M) {
+  if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_NGO, 1> : srt_trace_team_kernel<SRT_DENS_NGO, 0>;
+  return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_GRID, 1> : srt_trace_team_kernel<SRT_DENS_GRID, 0>;
+}
 trace_kernel_t pick_trace(const SrtModel& M) {
   if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_trace_kernel<SRT_DENS_NGO, 1> : srt_trace_kernel<SRT_DENS_NGO, 0>;
   return M.use_igrf ? srt_trace_kernel<SRT_DENS_GRID, 1> : srt_trace_kernel<SRT_DENS_GRID, 0>;
@@ -70,8 +75,8 @@ struct srt_model {
   // device copies of the grid (modelnum 3)
   double* d_nodes = nullptr;
   double* d_axes = nullptr;
-  int blocks_per_sm = 0;
-  int grid = 0;
+  int blocks_per_sm[2] = {0, 0};  // [thread-per-ray, team-of-8]
+  int grid[2] = {0, 0};
 };
 
 struct srt_result {
@@ -88,13 +93,24 @@ struct srt_result {
 
 namespace {
 
+// 0 = one thread per ray, 1 = team of 8 lanes per ray.  SRT_KERNEL=thread|team overrides; by default
+// the team form is used while the batch cannot fill the machine with one thread per ray.
+int pick_mode(const srt_model* m, long long nrays) {
+  const char* env = getenv("SRT_KERNEL");
+  if (env && !strcmp(env, "thread")) return 0;
+  if (env && !strcmp(env, "team")) return 1;
+  return nrays < (long long)m->grid[0] * SRT_BLOCK_THREADS * 4 ? 1 : 0;
+}
+
 int launch_config(srt_model* m) {
-  if (m->grid) return SRT_OK;
-  int nb = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pick_trace(m->M), SRT_BLOCK_THREADS, 0));
-  if (nb < 1) nb = 1;
-  m->blocks_per_sm = nb;
-  m->grid = nb * g_num_sms;  // persistent: exactly one resident wave
+  if (m->grid[0]) return SRT_OK;
+  for (int mode = 0; mode < 2; ++mode) {
+    int nb = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, mode ? pick_team(m->M) : pick_trace(m->M), SRT_BLOCK_THREADS, 0));
+    if (nb < 1) nb = 1;
+    m->blocks_per_sm[mode] = nb;
+    m->grid[mode] = nb * g_num_sms;  // persistent: exactly one resident wave
+  }
   return SRT_OK;
 }
 
@@ -104,11 +120,12 @@ int launch_trace(srt_model* m, const SrtRunParams& P, const SrtBatch& B, cudaStr
   if (rc) return rc;
   CK(cudaMemcpyToSymbolAsync(c_srt_model, &m->M, sizeof(SrtModel), 0, cudaMemcpyHostToDevice, stream));
   CK(cudaMemsetAsync(B.counters, 0, 8 * sizeof(unsigned long long), stream));
-  long long warps_needed = (B.nrays + 31) / 32;
-  long long blocks_needed = (warps_needed * 32 + SRT_BLOCK_THREADS - 1) / SRT_BLOCK_THREADS;
-  int grid = (int)(blocks_needed < m->grid ? blocks_needed : m->grid);
+  const int mode = pick_mode(m, B.nrays);
+  const long long lanes_per_ray = mode ? 8 : 1;
+  long long blocks_needed = (B.nrays * lanes_per_ray + SRT_BLOCK_THREADS - 1) / SRT_BLOCK_THREADS;
+  int grid = (int)(blocks_needed < m->grid[mode] ? blocks_needed : m->grid[mode]);
   if (grid < 1) grid = 1;
-  pick_trace(m->M)<<<grid, SRT_BLOCK_THREADS, 0, stream>>>(P, B);
+  (mode ? pick_team(m->M) : pick_trace(m->M))<<<grid, SRT_BLOCK_THREADS, 0, stream>>>(P, B);
   g_launches++;
   CK(cudaGetLastError());
   return SRT_OK;
@@ -245,19 +262,21 @@ int srt_model_eval(const srt_model* m, int64_t n, const double* x, double* out) 
   return SRT_OK;
 }
 
-int srt_kernel_info(const srt_model* m, int* regs, int* local_bytes, int* blocks_per_sm, int* grid, int* block) {
+int srt_kernel_info(const srt_model* m, int64_t nrays, int* mode, int* regs, int* local_bytes, int* blocks_per_sm, int* grid, int* block) {
   if (!m) return SRT_E_ARG;
   int rc = ensure_device();
   if (rc) return rc;
   srt_model* mm = const_cast<srt_model*>(m);
   rc = launch_config(mm);
   if (rc) return rc;
+  const int md = pick_mode(mm, nrays);
   cudaFuncAttributes fa;
-  CK(cudaFuncGetAttributes(&fa, pick_trace(m->M)));
+  CK(cudaFuncGetAttributes(&fa, md ? pick_team(m->M) : pick_trace(m->M)));
+  if (mode) *mode = md;
   if (regs) *regs = fa.numRegs;
   if (local_bytes) *local_bytes = (int)fa.localSizeBytes;
-  if (blocks_per_sm) *blocks_per_sm = mm->blocks_per_sm;
-  if (grid) *grid = mm->grid;
+  if (blocks_per_sm) *blocks_per_sm = mm->blocks_per_sm[md];
+  if (grid) *grid = mm->grid[md];
   if (block) *block = SRT_BLOCK_THREADS;
   return SRT_OK;
 }

@@ -122,8 +122,15 @@ int srt_trace_batch(const srt_model* m, int64_t nrays, const double* pos0, doubl
   std::vector<Chunk> chunks;  // (pinned buffer, rows, capacity)
   std::vector<uint32_t> chunk_of((size_t)nrays, 0);
 
-  while (!todo.empty()) {
-    const size_t n = todo.size();
+  // A full log drops every ray still in flight, so after a wave that dropped rays the next waves are
+  // limited to what is guaranteed to fit (or to what just completed, if that is more).
+  size_t wave_limit = (size_t)nrays;
+  std::vector<int64_t> pending;  // rays not yet launched in any wave + rays to re-run
+  pending.swap(todo);
+  while (!pending.empty()) {
+    const size_t n = pending.size() < wave_limit ? pending.size() : wave_limit;
+    todo.assign(pending.begin(), pending.begin() + n);
+    pending.erase(pending.begin(), pending.begin() + n);
     if ((rc = g_rays.reserve(n * 7 * sizeof(double)))) FAIL(rc);
     if ((rc = g_rays_h.reserve(n * 7 * sizeof(double)))) FAIL(rc);
     if ((rc = g_summary.reserve(n * SRT_SUMMARY_WORDS * sizeof(double)))) FAIL(rc);
@@ -181,7 +188,12 @@ int srt_trace_batch(const srt_model* m, int64_t nrays, const double* pos0, doubl
       if (flags & SRT_FLAG_DROPPED) { again.push_back(todo[s]); continue; }
       kept_rows += nlogged_h[s];
     }
-    if (again.size() == n) FAIL(SRT_E_NOMEM);  // no ray fitted: the log cannot make progress
+    if (!again.empty()) {
+      const size_t guaranteed = cap_rows / max_rows_per_ray > 0 ? cap_rows / max_rows_per_ray : 1;
+      if (again.size() == n && n <= guaranteed) FAIL(SRT_E_NOMEM);  // even a guaranteed-size wave made no progress
+      const size_t completed = n - again.size();
+      wave_limit = completed > guaranteed ? completed : guaranteed;
+    }
     double* chunk = nullptr;
     if (kept_rows) {
       if ((rc = g_sorted.reserve(kept_rows * SRT_ROW_DOUBLES * sizeof(double)))) FAIL(rc);
@@ -209,7 +221,7 @@ int srt_trace_batch(const srt_model* m, int64_t nrays, const double* pos0, doubl
       res->accepted += (uint64_t)sh[s * SRT_SUMMARY_WORDS + 20] - 1;
       dir0[3 * r + 0] = hr[3 * n + s]; dir0[3 * r + 1] = hr[4 * n + s]; dir0[3 * r + 2] = hr[5 * n + s];
     }
-    todo.swap(again);
+    pending.insert(pending.end(), again.begin(), again.end());
   }
   // one contiguous pinned buffer when there was a single wave; otherwise concatenate
   if (chunks.size() == 1) {

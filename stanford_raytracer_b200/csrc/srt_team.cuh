@@ -1,0 +1,291 @@
+// srt_team.cuh -- the cooperative ("team") form of the per-ray integrator: 8 lanes per ray.
+//
+// Why: a ray is a serial ODE, and one thread per ray leaves the FP64 pipe idle whenever
+// the batch is small or a few long rays are left (config 2: 10^4 rays, a third of which
+// run 2*10^4 steps): one accepted RK45 step is a chain of 43 plasma evaluations.  The
+// 7-point stencil of raytracer_evalrhs (x, x+-dx, x+-dy, x+-dz; raytracer.f95:137,190,
+// 241-261) is embarrassingly parallel, so a team of 8 lanes evaluates it in ONE plasma-
+// evaluation latency: lanes 0-5 take the six displaced points, lanes 6 and 7 the centre
+// (for the w+d and w-d Stix sets).  An accepted step becomes 7 rounds (stage-1 dF/dx,
+// stages 2-6, error estimate + re-projection) instead of 43 sequential evaluations.
+//
+// Layout of a team: lane r < 6 OWNS component r of the state vector (x,y,z,kx,ky,kz): its
+// stage increments k1..k6, est1/est2 and the RK algebra for that component live only
+// there (6x fewer registers than the replicated form); scalars (t, dt, w, counters) are
+// replicated.  Every round is "plasma at my point -> derived -> Stix at my w", which is
+// the same instruction stream for all lanes of the warp whatever phase their team is in;
+// only the short tails differ per phase.  All arithmetic is the arithmetic of
+// srt_physics.h in the same order, so results are bit-identical to the thread-per-ray
+// kernel and to the oracle (checked by tests/test_gpu_parity.py).
+#pragma once
+#include "srt_kernels.cuh"
+
+enum { SRT_PH_IDLE = 0, SRT_PH_S1DX = 1, SRT_PH_STAGE = 2, SRT_PH_EST = 3 };
+
+struct SrtTeamCtx {
+  unsigned tmask;  // lanes of my team
+  int tbase;       // first lane of my team
+  int r;           // my role 0..7
+};
+
+__device__ __forceinline__ double team_get(const SrtTeamCtx& T, double v, int src_role) { return __shfl_sync(T.tmask, v, T.tbase + src_role); }
+
+// gathers the 6 owned components into a full vector on every lane
+__device__ __forceinline__ void team_gather6(const SrtTeamCtx& T, double mine, double out[6]) {
+#pragma unroll
+  for (int j = 0; j < 6; ++j) out[j] = team_get(T, mine, j);
+}
+
+__device__ __forceinline__ void team_bcast_derived(const SrtTeamCtx& T, const SrtPlasmaDerived& in, int src_role, SrtPlasmaDerived& out) {
+#pragma unroll
+  for (int i = 0; i < SRT_NSPEC; ++i) {
+    out.wps2[i] = team_get(T, in.wps2[i], src_role);
+    out.wcs[i] = team_get(T, in.wcs[i], src_role);
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) out.B0[i] = team_get(T, in.B0[i], src_role);
+  out.B0sq = team_get(T, in.B0sq, src_role);
+  out.fs_thr = team_get(T, in.fs_thr, src_role);
+}
+
+// the (i, sign) perturbed refractive-index vector of dispersion_relation_dFdk (raytracer.f95:139-153)
+__device__ __forceinline__ void team_dfdk_n(const double k[3], double w, int axis, int minus, double n[3], double& dk_axis) {
+  const double C = srt_c_light();
+#pragma unroll
+  for (int j = 0; j < 3; ++j) n[j] = k[j] * C / w;
+  double dk = srt_fd_step(1.0e-8, axis == 0 ? k[0] : (axis == 1 ? k[1] : k[2]));
+  double kc = axis == 0 ? k[0] : (axis == 1 ? k[1] : k[2]);
+  double v = (minus ? (kc - dk) : (kc + dk)) * C / w;
+  if (axis == 0) n[0] = v;
+  else if (axis == 1) n[1] = v;
+  else n[2] = v;
+  dk_axis = dk;
+}
+
+template <int DENS, int USE_IGRF>
+__global__ void __launch_bounds__(SRT_BLOCK_THREADS) srt_trace_team_kernel(const __grid_constant__ SrtRunParams P, const __grid_constant__ SrtBatch B) {
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const SrtModelRef MR = SrtModelRef();
+  const SrtModel& M = MR.get();
+  SrtTeamCtx T;
+  T.r = lane & 7;
+  T.tbase = lane & ~7;
+  T.tmask = 0xffu << T.tbase;
+  const int r = T.r;
+  const int axis = (r < 6) ? (r >> 1) : 0;  // stencil axis of lanes 0-5
+  const int minus = r & 1;                  // + side on even lanes, - side on odd lanes
+  const double C = srt_c_light();
+  const int outputper = P.outputper < 1 ? 1 : P.outputper;
+  const bool adaptive = (P.fixedstep == 0);
+
+  // ---- replicated scalars
+  int phase = SRT_PH_IDLE, stage = 0;
+  bool exhausted = false, dropped = false, attempt_start = false, finish_now = false;
+  long long slot = -1;
+  double w = 0.0, wl = 0.0, t = 0.0, dt = 0.0, dfdw_rec = 0.0;
+  double vg[3] = {0.0, 0.0, 0.0};
+  int nstep = 0, lastrefinedown = 0, stopcond = 0, cone_exit = 0;
+  unsigned nrej = 0, ncone = 0, nlog = 0;
+  unsigned long long my_accepted = 0, my_attempts = 0;
+  // ---- owned component (meaningful on lanes 0-5; lanes 6,7 mirror component r-6 harmlessly)
+  const int comp = (r < 6) ? r : (r - 6);
+  double xc = 0.0;          // state component
+  double dfdk_c = 0.0;      // recorded dF/dk component (lanes 0-2)
+  double rhs1c = 0.0;       // stage-1 rhs component, kept across rejections
+  double kk1 = 0.0, kk2 = 0.0, kk3 = 0.0, kk4 = 0.0, kk5 = 0.0, kk6 = 0.0;
+  double tmpc = 0.0;        // my component of the current evaluation point
+  double e1c = 0.0, e2c = 0.0;
+
+  for (;;) {
+    // ================= refill: idle teams take the next ray; one atomic per warp
+    const bool want = (phase == SRT_PH_IDLE) && !exhausted;
+    const unsigned need = __ballot_sync(full, want && r == 0);
+    if (need) {
+      const int leader = __ffs(need) - 1;
+      unsigned long long base = 0;
+      if (lane == leader) base = atomicAdd(&B.counters[4], (unsigned long long)__popc(need));
+      base = __shfl_sync(full, base, leader);
+      // every lane of a wanting team computes its team's rank from the leader-lane bits
+      if (want) {
+        slot = (long long)(base + __popc(need & ((1u << T.tbase) - 1u)));
+        if (slot >= B.nrays) {
+          exhausted = true;
+        } else {
+          double pos0[3] = {B.rays[0 * B.nrays + slot], B.rays[1 * B.nrays + slot], B.rays[2 * B.nrays + slot]};
+          double dir0[3] = {B.rays[3 * B.nrays + slot], B.rays[4 * B.nrays + slot], B.rays[5 * B.nrays + slot]};
+          double w0 = B.rays[6 * B.nrays + slot];
+          SrtRayState st;
+          double row0[SRT_ROW_DOUBLES];
+          srt_ray_init<DENS, USE_IGRF>(MR, P, pos0, dir0, w0, st, row0);  // replicated on the 8 lanes (once per ray)
+          xc = (comp == 0) ? st.x[0] : (comp == 1) ? st.x[1] : (comp == 2) ? st.x[2] : (comp == 3) ? st.k[0] : (comp == 4) ? st.k[1] : st.k[2];
+          dfdk_c = (comp == 0) ? st.dfdk[0] : (comp == 1) ? st.dfdk[1] : st.dfdk[2];
+          dfdw_rec = st.dfdw;
+          w = st.w; wl = 0.0; t = 0.0; dt = st.dt;
+          vg[0] = st.vg[0]; vg[1] = st.vg[1]; vg[2] = st.vg[2];
+          nstep = 1; lastrefinedown = 0; stopcond = 0; cone_exit = 0; nrej = 0; ncone = 0;
+          dropped = false; nlog = 0; finish_now = false;
+          if (r == 0) {
+            B.rays[3 * B.nrays + slot] = dir0[0];
+            B.rays[4 * B.nrays + slot] = dir0[1];
+            B.rays[5 * B.nrays + slot] = dir0[2];
+            srt_log_row(B, slot, 0, row0, dropped);
+            double* sm = B.summary + slot * SRT_SUMMARY_WORDS;  // the last recorded row lives in the summary
+#pragma unroll
+            for (int i = 0; i < SRT_ROW_DOUBLES; ++i) sm[i] = row0[i];
+          }
+          dropped = __shfl_sync(T.tmask, (int)dropped, T.tbase) != 0;
+          if (!dropped) nlog = 1;
+          phase = SRT_PH_S1DX;
+          attempt_start = true;
+        }
+      }
+    }
+    if (__ballot_sync(full, phase != SRT_PH_IDLE) == 0u) break;
+
+    if (phase != SRT_PH_IDLE) {
+      // ================= top of an attempt: raytracer.f95:749-763
+      if (attempt_start) {
+        attempt_start = false;
+        double xs[6];
+        team_gather6(T, xc, xs);
+        int done = 0;
+        if (dropped || finish_now) { done = 1; }
+        else if (t >= P.tmax) { stopcond = 0; done = 1; }
+        else {
+          int sc = 0;
+          if (srt_sqrt(srt_dot3(xs, xs)) < P.minalt) sc = 1;
+          else if (srt_sqrt(srt_dot3(xs + 3, xs + 3)) == 0.0) sc = 2;
+          else if (srt_sqrt(srt_dot3(vg, vg)) > 1.0 + 1e-2) sc = 3;
+          else if (dt < (double)1e-14f) sc = 5;
+          else if (nstep >= P.maxsteps) sc = 6;
+          stopcond = sc;
+          if (sc != 0) done = 1;
+        }
+        if (done) {
+          if (r == 0) {
+            double* s = B.summary + slot * SRT_SUMMARY_WORDS;
+            s[20] = (double)nstep;
+            s[21] = (double)stopcond;
+            s[22] = (double)(nrej + ncone);
+            s[23] = (double)((cone_exit ? SRT_FLAG_CONE_EXIT : 0) | (dropped ? SRT_FLAG_DROPPED : 0));
+            if (B.nlogged) B.nlogged[slot] = dropped ? 0u : nlog;
+            if (dropped) atomicAdd(&B.counters[3], 1ull);
+          }
+          phase = SRT_PH_IDLE;
+        } else if (phase == SRT_PH_STAGE) {
+          // retry after a rejection: stage 1 is unchanged, only dt differs
+          kk1 = dt * rhs1c;
+          tmpc = adaptive ? xc + (SRT_A21 * kk1) : xc + 1.0 / 2.0 * kk1;
+          stage = 2;
+        }
+      }
+    }
+
+    if (phase != SRT_PH_IDLE) {
+      // ================= the round: plasma at my point, derived quantities, Stix at my w
+      double y[6];  // the point this round differentiates at (x,k)
+      double e1[6], e2[6];
+      if (phase == SRT_PH_S1DX) team_gather6(T, xc, y);
+      else if (phase == SRT_PH_STAGE) team_gather6(T, tmpc, y);
+      else {
+        team_gather6(T, e1c, e1);
+        team_gather6(T, e2c, e2);
+#pragma unroll
+        for (int j = 0; j < 6; ++j) y[j] = (r < 4 && adaptive) ? e1[j] : e2[j];
+      }
+      double pt[3] = {y[0], y[1], y[2]};
+      double dx_axis = 0.0;
+      if (phase != SRT_PH_EST && r < 6) {
+        const double xi = axis == 0 ? y[0] : (axis == 1 ? y[1] : y[2]);
+        dx_axis = srt_fd_step(M.del, xi);
+        const double v = minus ? xi - dx_axis : xi + dx_axis;
+        if (axis == 0) pt[0] = v;
+        else if (axis == 1) pt[1] = v;
+        else pt[2] = v;
+      }
+      const double dw = srt_fd_step(1.0e-8, w);
+      double wr = w;  // the frequency my Stix set is evaluated at
+      if (phase == SRT_PH_STAGE) wr = (r == 6) ? w + dw : (r == 7 ? w - dw : w);
+      else if (phase == SRT_PH_EST) wr = (wl != 0.0) ? wl : w;
+      SrtPlasma pl;
+      SrtPlasmaDerived pd;
+      SrtStix sx;
+      srt_plasma<DENS, USE_IGRF>(MR, pt, pl);
+      srt_plasma_derive(MR, pl, pd);
+      srt_stix(pd, wr, sx);
+
+      if (phase == SRT_PH_S1DX) {
+        // ---- stage 1: dF/dx at the current point; dF/dk, dF/dw are the recorded ones
+        double n[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) n[j] = y[3 + j] * C / w;
+        const double FA = srt_F(n, w, pd, sx);
+        const int j2 = 2 * (comp % 3);
+        const double Fp = team_get(T, FA, j2), Fn = team_get(T, FA, j2 + 1);
+        const double ddx = team_get(T, dx_axis, j2);
+        if (comp < 3) rhs1c = -(dfdk_c / dfdw_rec);
+        else rhs1c = ((Fp - Fn) / ddx / 2.0) / dfdw_rec;
+        kk1 = dt * rhs1c;
+        tmpc = adaptive ? xc + (SRT_A21 * kk1) : xc + 1.0 / 2.0 * kk1;
+        stage = 2;
+        phase = SRT_PH_STAGE;
+      } else if (phase == SRT_PH_STAGE) {
+        // ---- raytracer_evalrhs at y (raytracer.f95:282-314)
+        double nA[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) nA[j] = y[3 + j] * C / wr;  // lanes 0-5: k*C/w; 6,7: k*c/(w+-d)
+        const double FA = srt_F(nA, wr, pd, sx);
+        SrtPlasmaDerived pc;
+        team_bcast_derived(T, pd, 6, pc);
+        SrtStix sc;
+        srt_stix(pc, w, sc);
+        double nB[3], dk_axis;
+        team_dfdk_n(y + 3, w, axis, minus, nB, dk_axis);
+        const double FB = srt_F(nB, w, pc, sc);
+        const double dfdw = (team_get(T, FA, 6) - team_get(T, FA, 7)) / dw / 2.0;
+        const int j2 = 2 * (comp % 3);
+        const double FAp = team_get(T, FA, j2), FAn = team_get(T, FA, j2 + 1);
+        const double FBp = team_get(T, FB, j2), FBn = team_get(T, FB, j2 + 1);
+        const double ddx = team_get(T, dx_axis, j2), ddk = team_get(T, dk_axis, j2);
+        double rhsc;
+        if (comp < 3) rhsc = -(((FBp - FBn) / ddk / 2.0) / dfdw);
+        else rhsc = ((FAp - FAn) / ddx / 2.0) / dfdw;
+        const double kk = dt * rhsc;
+        if (adaptive) {
+          if (stage == 2) { kk2 = kk; tmpc = xc + (SRT_A31 * kk1 + SRT_A32 * kk2); }
+          else if (stage == 3) { kk3 = kk; tmpc = xc + (SRT_A41 * kk1 + SRT_A42 * kk2 + SRT_A43 * kk3); }
+          else if (stage == 4) { kk4 = kk; tmpc = xc + (SRT_A51 * kk1 + SRT_A52 * kk2 + SRT_A53 * kk3 + SRT_A54 * kk4); }
+          else if (stage == 5) { kk5 = kk; tmpc = xc + (SRT_A61 * kk1 + SRT_A62 * kk2 + SRT_A63 * kk3 + SRT_A64 * kk4 + SRT_A65 * kk5); }
+          else {
+            kk6 = kk;
+            e1c = xc + (SRT_B41 * kk1 + SRT_B42 * kk2 + SRT_B43 * kk3 + SRT_B44 * kk4 + SRT_B45 * kk5 + SRT_B46 * kk6);
+            e2c = xc + (SRT_B51 * kk1 + SRT_B52 * kk2 + SRT_B53 * kk3 + SRT_B54 * kk4 + SRT_B55 * kk5 + SRT_B56 * kk6);
+            phase = SRT_PH_EST;
+          }
+        } else {
+          if (stage == 2) { kk2 = kk; tmpc = xc + 1.0 / 2.0 * kk2; }
+          else if (stage == 3) { kk3 = kk; tmpc = xc + kk3; }
+          else {
+            kk4 = kk;
+            e2c = xc + 1.0 / 6.0 * (kk1 + 2.0 * kk2 + 2.0 * kk3 + kk4);
+            e1c = e2c;
+            phase = SRT_PH_EST;
+          }
+        }
+        ++stage;
+      } else {
+#include "srt_team_est.inl"
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    my_accepted += __shfl_down_sync(full, my_accepted, o);
+    my_attempts += __shfl_down_sync(full, my_attempts, o);
+  }
+  if (lane == 0) {
+    atomicAdd(&B.counters[1], my_accepted);
+    atomicAdd(&B.counters[2], my_attempts);
+  }
+}

@@ -1,0 +1,145 @@
+        // ---- srt_team_est.inl: error estimate, re-projection, accept/reject (raytracer.f95:775-922).
+        // Included inside srt_trace_team_kernel; lanes 0-3 hold the plasma at est1, lanes 4-7 at est2
+        // (fixed step: all at est2).
+        const double dt_used = dt;
+        bool retry = false;
+        if (adaptive) {
+          double sa = 0.0, sb = 0.0;
+#pragma unroll
+          for (int i = 0; i < 3; ++i) sa = sa + srt_fabs(e1[3 + i] - e2[3 + i]);
+#pragma unroll
+          for (int i = 0; i < 3; ++i) sb = sb + srt_fabs(e2[3 + i]);
+          double err = sa / sb;
+          if (wl != 0.0) {
+            const int set = r >> 2, q = r & 3;
+            const double* kset = set ? (e2 + 3) : (e1 + 3);
+            double n1[3], n2[3], dk1, dk2;
+            team_dfdk_n(kset, wl, q >> 1, q & 1, n1, dk1);  // axes 0 and 1 on the four lanes of the set
+            const double F1 = srt_F(n1, wl, pd, sx);
+            team_dfdk_n(kset, wl, 2, q & 1, n2, dk2);       // axis 2 on the first two lanes of the set
+            const double F2 = srt_F(n2, wl, pd, sx);
+            double g[2][3];
+#pragma unroll
+            for (int s2 = 0; s2 < 2; ++s2) {
+              const double* ks = s2 ? (e2 + 3) : (e1 + 3);
+              g[s2][0] = (team_get(T, F1, s2 * 4 + 0) - team_get(T, F1, s2 * 4 + 1)) / srt_fd_step(1.0e-8, ks[0]) / 2.0;
+              g[s2][1] = (team_get(T, F1, s2 * 4 + 2) - team_get(T, F1, s2 * 4 + 3)) / srt_fd_step(1.0e-8, ks[1]) / 2.0;
+              g[s2][2] = (team_get(T, F2, s2 * 4 + 0) - team_get(T, F2, s2 * 4 + 1)) / srt_fd_step(1.0e-8, ks[2]) / 2.0;
+            }
+            double sc2 = 0.0, sd2 = 0.0;
+#pragma unroll
+            for (int i = 0; i < 3; ++i) sc2 = sc2 + srt_fabs(g[0][i] - g[1][i]);
+#pragma unroll
+            for (int i = 0; i < 3; ++i) sd2 = sd2 + srt_fabs(g[1][i]);
+            const double eg = sc2 / sd2;
+            if (eg > err || err != err) err = eg;  // MAX() as gfortran <= 8 expands it
+          } else {
+            if (err != err) err = srt_nan();  // Q1
+          }
+          if (err > P.maxerr) {
+            dt = 0.8 * dt;
+            lastrefinedown = 1;
+            nrej++;
+            retry = true;
+          } else if (lastrefinedown == 0 && err < P.maxerr / 100.0 && dt * 1.25 < P.dtmax) {
+            dt = dt * 1.25;
+            lastrefinedown = 0;
+          }
+        }
+        if (!retry) {
+          // re-project |k| at est2 (lane 4 holds the plasma there and its Stix set at w)
+          SrtCplx ksel = srt_solve_root(e2 + 3, w, pd, sx, P.root);
+          ksel.re = team_get(T, ksel.re, 4);
+          ksel.im = team_get(T, ksel.im, 4);
+          double kk = 0.0;
+#pragma unroll
+          for (int i = 0; i < 3; ++i) kk = kk + (e2[3 + i] * e2[3 + i] - (-0.0) * 0.0);
+          SrtCplx nrm;
+          srt_csqrt(kk, 0.0, nrm.re, nrm.im);
+          double knew[3];
+          double imsum = 0.0;
+#pragma unroll
+          for (int i = 0; i < 3; ++i) {
+            SrtCplx ki = {e2[3 + i], 0.0};
+            SrtCplx kn = srt_cmul(ksel, srt_cdiv(ki, nrm));
+            knew[i] = kn.re;
+            imsum = imsum + kn.im * kn.im;
+          }
+          if (imsum > 0.0) {
+            if (adaptive) {
+              dt = dt / 2.0;
+              lastrefinedown = 1;
+              ncone++;
+              retry = true;
+            } else {
+              cone_exit = 1;
+              stopcond = 0;
+              finish_now = true;
+              phase = SRT_PH_STAGE;
+              attempt_start = true;
+            }
+          } else {
+            // ---- accept (raytracer.f95:909-922)
+            xc = (comp == 0) ? e2[0] : (comp == 1) ? e2[1] : (comp == 2) ? e2[2] : (comp == 3) ? knew[0] : (comp == 4) ? knew[1] : knew[2];
+            wl = w;
+            lastrefinedown = 0;
+            t = t + dt_used;
+            nstep = nstep + 1;
+            // dF/dk and dF/dw at the new point: est2's plasma, spread over the 8 lanes
+            SrtPlasmaDerived pc;
+            team_bcast_derived(T, pd, 4, pc);
+            const double wr2 = (r == 6) ? w + dw : (r == 7 ? w - dw : w);
+            SrtStix s2;
+            srt_stix(pc, wr2, s2);
+            double nT[3], dkT;
+            team_dfdk_n(knew, w, axis, minus, nT, dkT);
+            if (r >= 6) {
+#pragma unroll
+              for (int j = 0; j < 3; ++j) nT[j] = knew[j] * C / wr2;
+            }
+            const double FT = srt_F(nT, wr2, pc, s2);
+            dfdw_rec = (team_get(T, FT, 6) - team_get(T, FT, 7)) / dw / 2.0;
+            double dfdk_new[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) dfdk_new[i] = (team_get(T, FT, 2 * i) - team_get(T, FT, 2 * i + 1)) / srt_fd_step(1.0e-8, knew[i]) / 2.0;
+            dfdk_c = (comp % 3 == 0) ? dfdk_new[0] : (comp % 3 == 1) ? dfdk_new[1] : dfdk_new[2];
+            // the recorded row (raytracer.f95:937-986)
+            double row[SRT_ROW_DOUBLES];
+            double nn[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) nn[i] = knew[i] * C / w;
+            const double n2 = srt_dot3(nn, nn);
+            row[0] = t;
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+              row[1 + i] = e2[i];
+              row[4 + i] = nn[i] / n2;
+              row[7 + i] = -(dfdk_new[i] / dfdw_rec) / C;
+              row[10 + i] = nn[i];
+              row[13 + i] = team_get(T, pl.B0[i], 4);
+            }
+#pragma unroll
+            for (int i = 0; i < SRT_NSPEC; ++i) row[16 + i] = team_get(T, pl.Ns[i], 4);
+            vg[0] = row[7]; vg[1] = row[8]; vg[2] = row[9];
+            if (r == 0) {
+              ++my_accepted;
+              ++my_attempts;
+              double* sm = B.summary + slot * SRT_SUMMARY_WORDS;
+#pragma unroll
+              for (int i = 0; i < SRT_ROW_DOUBLES; ++i) sm[i] = row[i];
+              const int rowidx = nstep - 1;
+              if (rowidx % outputper == 0) {
+                srt_log_row(B, slot, rowidx / outputper, row, dropped);
+                if (!dropped) ++nlog;
+              }
+            }
+            dropped = __shfl_sync(T.tmask, (int)dropped, T.tbase) != 0;
+            phase = SRT_PH_S1DX;
+            attempt_start = true;
+          }
+        }
+        if (retry) {
+          if (r == 0) ++my_attempts;
+          phase = SRT_PH_STAGE;
+          attempt_start = true;
+        }
