@@ -161,7 +161,7 @@ def main():
     P = srt.RunParams(params["dt0"], params["dtmax"], params["maxerr"], params["minalt"], params["tmax"], params["maxsteps"], params["root"],
                       params["fixedstep"], 1)
     # device-resident inputs (SoA) and outputs
-    rays_h = np.concatenate([pos0.T, dir0.T, w0[None, :]], axis=0)  # [7][nrays]
+    rays_h = np.ascontiguousarray(np.concatenate([pos0.T, dir0.T, w0[None, :]], axis=0))  # [7][nrays], C order (concatenate keeps F order)
     rays0 = torch.from_numpy(rays_h).to(dev)
     rays = rays0.clone()
     summary = torch.empty((nrays, srt.SUMMARY_WORDS), dtype=torch.float64, device=dev)

@@ -1,6 +1,13 @@
 // srt_api.cu -- the C ABI of include/srt.h over the sm_100a kernels.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo (build.py).
 #define SRT_BLOCK_THREADS 64
+// resident 64-thread blocks per SM the trace kernels are compiled for (register budget = 65536 / (64 * blocks))
+#ifndef SRT_THREAD_MIN_BLOCKS
+#define SRT_THREAD_MIN_BLOCKS 4
+#endif
+#ifndef SRT_TEAM_MIN_BLOCKS
+#define SRT_TEAM_MIN_BLOCKS 4
+#endif
 #include "srt_kernels.cuh"
 #include "srt_team.cuh"
 #include "srt_host_setup.h"

@@ -48,7 +48,7 @@ __device__ __forceinline__ void srt_log_row(const SrtBatch& B, long long ray, in
 }
 
 template <int DENS, int USE_IGRF>
-__global__ void __launch_bounds__(SRT_BLOCK_THREADS) srt_trace_kernel(const __grid_constant__ SrtRunParams P, const __grid_constant__ SrtBatch B) {
+__global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_THREAD_MIN_BLOCKS) srt_trace_kernel(const __grid_constant__ SrtRunParams P, const __grid_constant__ SrtBatch B) {
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const SrtModelRef MR = SrtModelRef();

@@ -63,7 +63,7 @@ __device__ __forceinline__ void team_dfdk_n(const double k[3], double w, int axi
 }
 
 template <int DENS, int USE_IGRF>
-__global__ void __launch_bounds__(SRT_BLOCK_THREADS) srt_trace_team_kernel(const __grid_constant__ SrtRunParams P, const __grid_constant__ SrtBatch B) {
+__global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_TEAM_MIN_BLOCKS) srt_trace_team_kernel(const __grid_constant__ SrtRunParams P, const __grid_constant__ SrtBatch B) {
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const SrtModelRef MR = SrtModelRef();

@@ -10,7 +10,7 @@ for nf, nl, tmax in ((10, 16, 10.0), (100, 100, 10.0), (100, 1000, 0.5)):
     n = len(w0)
     p = dict(common.C2, tmax=tmax)
     P = srt.RunParams(p["dt0"], p["dtmax"], p["maxerr"], p["minalt"], p["tmax"], p["maxsteps"], p["root"], p["fixedstep"], 1)
-    rays0 = torch.from_numpy(np.concatenate([pos0.T, dir0.T, w0[None, :]], axis=0)).cuda()
+    rays0 = torch.from_numpy(np.ascontiguousarray(np.concatenate([pos0.T, dir0.T, w0[None, :]], axis=0))).cuda()
     summary = torch.zeros((n, 24), dtype=torch.float64, device="cuda")
     counters = torch.zeros(8, dtype=torch.int64, device="cuda")
     for mode in ("thread", "team"):
