@@ -82,6 +82,7 @@ struct srt_model {
   // device copies of the grid (modelnum 3)
   double* d_nodes = nullptr;
   double* d_axes = nullptr;
+  double* d_coef = nullptr;  // per-cell tricubic coefficients
   int blocks_per_sm[2] = {0, 0};  // [thread-per-ray, team-of-8]
   int grid[2] = {0, 0};
 };
@@ -202,23 +203,41 @@ int srt_model_grid(srt_model** m, const char* path, int yearday, int msec, int u
   if (!mm) return SRT_E_NOMEM;
   memset(&mm->M, 0, sizeof mm->M);
   srt_host::HostGrid hg;
-  if (srt_host::load_grid(path, mm->M, hg) != 0) { delete mm; return SRT_E_IO; }
+  rc = srt_host::load_grid(path, mm->M, hg);
+  if (rc != 0) { delete mm; return rc == -3 ? SRT_E_UNSUPPORTED : SRT_E_IO; }
   rc = finish_model(mm, yearday, msec, use_igrf, use_tsyganenko);
   if (rc) { delete mm; return rc; }
   size_t nb = hg.nodes.size() * sizeof(double);
   size_t ax = (hg.xs.size() + hg.ys.size() + hg.zs.size()) * sizeof(double);
-  if (cudaMalloc(&mm->d_nodes, nb) != cudaSuccess || cudaMalloc(&mm->d_axes, ax) != cudaSuccess) {
+  const SrtGrid& hgd = mm->M.grid;
+  const size_t ncells = (size_t)(hgd.nx > 1 ? hgd.nx - 1 : 0) * (size_t)(hgd.ny > 1 ? hgd.ny - 1 : 0) * (size_t)(hgd.nz > 1 ? hgd.nz - 1 : 0);
+  if (cudaMalloc(&mm->d_nodes, nb) != cudaSuccess || cudaMalloc(&mm->d_axes, ax) != cudaSuccess ||
+      (ncells && cudaMalloc(&mm->d_coef, ncells * 256 * sizeof(double)) != cudaSuccess)) {
+    rc = cuda_fail(cudaGetLastError(), "cudaMalloc(grid)");
     srt_model_free(mm);
-    return cuda_fail(cudaGetLastError(), "cudaMalloc(grid)");
+    return rc;
   }
   cudaMemcpy(mm->d_nodes, hg.nodes.data(), nb, cudaMemcpyHostToDevice);
   cudaMemcpy(mm->d_axes, hg.xs.data(), hg.xs.size() * 8, cudaMemcpyHostToDevice);
   cudaMemcpy(mm->d_axes + hg.xs.size(), hg.ys.data(), hg.ys.size() * 8, cudaMemcpyHostToDevice);
   cudaMemcpy(mm->d_axes + hg.xs.size() + hg.ys.size(), hg.zs.data(), hg.zs.size() * 8, cudaMemcpyHostToDevice);
   mm->M.grid.nodes = mm->d_nodes;
+  mm->M.grid.coef = nullptr;
   mm->M.grid.xs = mm->d_axes;
   mm->M.grid.ys = mm->d_axes + hg.xs.size();
   mm->M.grid.zs = mm->d_axes + hg.xs.size() + hg.ys.size();
+  if (ncells) {
+    // per-cell tricubic coefficients, once (SRT_GRID_COEF=0 keeps the on-the-fly path: test hook)
+    const char* env = getenv("SRT_GRID_COEF");
+    if (!(env && !strcmp(env, "0"))) {
+      long long threads = (long long)ncells * 4;
+      int blocks = (int)((threads + 127) / 128 < (long long)g_num_sms * 16 ? (threads + 127) / 128 : (long long)g_num_sms * 16);
+      srt_coef_kernel<<<blocks, 128>>>(mm->M.grid, mm->d_coef);
+      g_launches++;
+      cudaDeviceSynchronize();
+      mm->M.grid.coef = mm->d_coef;
+    }
+  }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { srt_model_free(mm); return cuda_fail(e, "grid upload"); }
   *m = mm;
@@ -229,6 +248,7 @@ void srt_model_free(srt_model* m) {
   if (!m) return;
   if (m->d_nodes) cudaFree(m->d_nodes);
   if (m->d_axes) cudaFree(m->d_axes);
+  if (m->d_coef) cudaFree(m->d_coef);
   delete m;
 }
 

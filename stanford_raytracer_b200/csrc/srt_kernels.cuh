@@ -13,6 +13,7 @@
 // Bound: FP64 (non-tensor) pipe; nothing here is a dense contraction, so no tensor
 // cores, no TMA.  HBM traffic = 168 B per recorded row + 56 B per ray in, 192 B per ray
 // out; the model lives in __constant__ memory (c_srt_model).
+// Gridded model: + one 2 KiB coefficient record per distinct cell a query lands in (L2-resident gathers).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -171,6 +172,28 @@ __global__ void srt_eval_kernel(long long n, const double* __restrict__ x, doubl
     }
 #pragma unroll
     for (int c = 0; c < 3; ++c) o[16 + c] = p.B0[c];
+  }
+}
+
+// One-shot set-up of the gridded model: tricubic coefficients of every interior cell
+// (tricubic_get_coeff, libtricubic.f95:638-656,715-720) -> coef[cell][64 terms][4 species].
+// One thread per (cell, species); the 64 x 64 int8 Amat sits in __constant__ memory and every
+// thread of a warp reads the same entry (broadcast).
+__global__ void srt_coef_kernel(const __grid_constant__ SrtGrid g, double* __restrict__ coef) {
+  const long long ncx = g.nx - 1, ncy = g.ny - 1, ncz = g.nz - 1;
+  const long long total = ncx * ncy * ncz * 4;
+  for (long long id = blockIdx.x * (long long)blockDim.x + threadIdx.x; id < total; id += (long long)gridDim.x * blockDim.x) {
+    const int s = (int)(id & 3);
+    const long long cell = id >> 2;
+    double* dst = coef + cell * 256 + s;
+    if (s >= g.nspec) {
+      for (int t = 0; t < 64; ++t) dst[4 * t] = 0.0;
+      continue;
+    }
+    const int i0 = (int)(cell % ncx), j0 = (int)((cell / ncx) % ncy), k0 = (int)(cell / (ncx * ncy));
+    double a[64];
+    srt_tricubic_cell_coef(g, i0, j0, k0, s, a);
+    for (int t = 0; t < 64; ++t) dst[4 * t] = a[t];
   }
 }
 

@@ -40,13 +40,18 @@ struct SrtGrid {
   int nx, ny, nz, nspec;
   double minx, miny, minz;
   double delx, dely, delz;
-  // corner-value scale factors, hoisted products in the reference's order
-  // (libtricubic.f95:892-899): dx*dy, dx*dz, dy*dz, (dx*dy)*dz
-  double dxdy, dxdz, dydz, dxdydz;
-  // device pointers.  nodes: [nz][ny][nx][8 arrays][4 species] doubles, i.e. the 32
-  // values one corner contributes are contiguous (256 B);  xs/ys/zs: node coordinates
-  // as the reference regenerates them (interp_dens_model_adapter.f95:90-95)
+  // device (or, in the CPU test build, host) pointers.
+  // nodes: [nz][ny][nx][8 arrays][4 species] doubles -- the 32 values one cube corner contributes
+  //        (f, dfdx, dfdy, dfdz, d2fdxdy, d2fdxdz, d2fdydz, d3fdxdydz; species fastest) are one
+  //        contiguous 256-byte record.
+  // coef:  [nz-1][ny-1][nx-1][64 terms][4 species] doubles -- the tricubic coefficients of every
+  //        interior cell, a = Amat * (scaled corner data), precomputed once by srt_coef_kernel in
+  //        the reference's accumulation order; term t = 16*i + 4*j + k holds a(i + 4j + 16k), the
+  //        order tricubic_eval walks them (libtricubic.f95:677-693).  2 KiB per cell.  NULL: every
+  //        query takes the on-the-fly path (CPU test build).
+  // xs/ys/zs: node coordinates as the reference regenerates them (interp_dens_model_adapter.f95:90-95)
   const double* nodes;
+  const double* coef;
   const double* xs;
   const double* ys;
   const double* zs;

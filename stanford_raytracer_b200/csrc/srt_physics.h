@@ -265,7 +265,7 @@ SRT_HD void srt_field_sm(SrtModelRef MR, const double x[3], const double p[3], d
 }
 
 // gridded log-density (srt_tricubic.h)
-SRT_HD void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT_NSPEC]);
+SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT_NSPEC]);
 
 // ------------------------------------------------------------------ funcPlasmaParams
 // DENS = SrtDensityKind, USE_IGRF = 0/1.

@@ -1,11 +1,166 @@
-// srt_tricubic.h -- gridded log-density by Lekien-Marsden tricubic interpolation
-// (tricubic-for/libtricubic.f95:796-933 called from
-// fortran/interp_dens_model_adapter.f95:190-206).  PLACEHOLDER until the gridded
-// path lands: returns NaN densities so that a mis-dispatched model cannot pass.
+// srt_tricubic.h -- gridded log-density by Lekien-Marsden tricubic interpolation:
+// tricubic_interpolate_at (tricubic-for/libtricubic.f95:796-933) as called once per species from
+// fortran/interp_dens_model_adapter.f95:190-206, followed by Ns = exp(.) (:209).
+//
+// What the reference does per query and species: three O(n) maxloc scans for the cell, a gather of
+// 8 corners x 8 arrays, a dense 64x64 matmul with Amat, a 64-term polynomial.  What this does:
+//   * cell index from the regular axes (one division + a fix-up against the stored node
+//     coordinates, so the comparison `0 <= xi - x(ind)` is the reference's);
+//   * interior cells (every query of a ray inside the grid): the 64 coefficients x 4 species are
+//     PRECOMPUTED per cell (SrtGrid::coef, 2 KiB per cell, built once by srt_coef_kernel with
+//     srt_tricubic_cell_coef below, the same accumulation order as the reference's matmul), so a
+//     query is one 2 KiB gather served from L2 plus the polynomial;
+//   * cells touching or outside the grid edge take the on-the-fly path, which reproduces the sticky
+//     clamp flags statement by statement.
+// Both paths give the same bits where both apply (tests/test_grid_cpu.py).
 #pragma once
 #include "srt_physics.h"
+#include "srt_amat.h"
 
-SRT_HD void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT_NSPEC]) {
-  (void)g; (void)x;
-  for (int i = 0; i < SRT_NSPEC; ++i) Ns[i] = srt_nan();
+#if defined(__CUDA_ARCH__)
+__constant__ signed char c_srt_amat[64][64] = {SRT_AMAT_ROWS};
+#define SRT_AMAT(r, c) c_srt_amat[r][c]
+#else
+#if defined(__CUDACC__)
+__constant__ signed char c_srt_amat[64][64] = {SRT_AMAT_ROWS};
+#endif
+static const signed char h_srt_amat[64][64] = {SRT_AMAT_ROWS};
+#define SRT_AMAT(r, c) h_srt_amat[r][c]
+#endif
+
+// index (1-based, as maxloc returns it; 0 when the mask is all false) of the last node with
+// 0 <= xi - x(ind)   (libtricubic.f95:835-840).  xs ascending, n >= 1.
+SRT_HD int srt_grid_locate(const double* xs, int n, double minx, double delx, double xi) {
+  double g = (xi - minx) / delx;
+  int i;
+  if (!(g > -1.0)) i = -1;
+  else if (!(g < (double)n)) i = n - 1;
+  else i = (int)g;  // truncation; g in (-1, n)
+  if (i > n - 1) i = n - 1;
+  while (i + 1 < n && 0.0 <= (xi - xs[i + 1])) ++i;
+  while (i >= 0 && !(0.0 <= (xi - xs[i]))) --i;
+  return i + 1;
+}
+
+// a = matmul(Amat, x) for one species (libtricubic.f95:719): per row, accumulation from 0 in
+// ascending column order; exact zeros of Amat are skipped (adding +-0 to the running sum changes
+// nothing for finite data, Q13).  xv = the 64 stacked, scaled corner data of tricubic_get_coeff.
+SRT_HD double srt_amat_row(int r, const double xv[64]) {
+  double s = 0.0;
+  for (int c = 0; c < 64; ++c) {
+    const int a = SRT_AMAT(r, c);
+    if (a != 0) s = s + (double)a * xv[c];
+  }
+  return s;
+}
+
+// the scaled corner datum q (0..7: f, fx, fy, fz, fxy, fxz, fyz, fxyz) of libtricubic.f95:891-899
+SRT_HD double srt_corner_scale(int q, double v, double dx, double dy, double dz) {
+  switch (q) {
+    case 0: return v;
+    case 1: return v * dx;
+    case 2: return v * dy;
+    case 3: return v * dz;
+    case 4: return v * dx * dy;
+    case 5: return v * dx * dz;
+    case 6: return v * dy * dz;
+    default: return v * dx * dy * dz;
+  }
+}
+
+// Coefficients of the interior cell whose lower corner is node (i0, j0, k0) (0-based), species s:
+// out[t], t = 16*i + 4*j + k  <-  a(i + 4j + 16k).  No clamp can fire for an interior cell.
+SRT_HD void srt_tricubic_cell_coef(const SrtGrid& g, int i0, int j0, int k0, int s, double out[64]) {
+  double xv[64];
+  for (int l = 0; l < 8; ++l) {
+    const int ii = i0 + (l & 1), jj = j0 + ((l >> 1) & 1), kk = k0 + ((l >> 2) & 1);
+    const double* rec = g.nodes + ((((size_t)kk * g.ny + jj) * g.nx + ii) * 32);
+    for (int q = 0; q < 8; ++q) xv[8 * q + l] = srt_corner_scale(q, rec[4 * q + s], g.delx, g.dely, g.delz);
+  }
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j)
+      for (int k = 0; k < 4; ++k) out[16 * i + 4 * j + k] = srt_amat_row(i + 4 * j + 16 * k, xv);
+}
+
+// x**n for n = 0..3 as libgfortran's pow_r8_i4 evaluates it (square-and-multiply, Q24)
+SRT_HD void srt_powers3(double x, double p[4]) {
+  p[0] = 1.0;
+  p[1] = x;
+  p[2] = x * x;
+  p[3] = x * (x * x);
+}
+
+// the on-the-fly path: tricubic_interpolate_at for one species with the clamp logic of
+// libtricubic.f95:859-921 (flags are sticky across the 8 corners, Q12)
+SRT_HDN double srt_tricubic_slow(const SrtGrid& g, int is0, int js0, int ks0, double xil, double yil, double zil, int s) {
+  int flagi = 0, flagj = 0, flagk = 0;
+  double xv[64];
+  for (int l = 0; l < 8; ++l) {
+    int istmp = is0 + (l & 1), jstmp = js0 + ((l >> 1) & 1), kstmp = ks0 + ((l >> 2) & 1);  // 1-based
+    if (istmp < 1) { istmp = 1; flagi = 1; }
+    if (istmp > g.nx) { istmp = g.nx; flagi = 1; }
+    if (jstmp < 1) { jstmp = 1; flagj = 1; }
+    if (jstmp > g.ny) { jstmp = g.ny; flagj = 1; }
+    if (kstmp < 1) { kstmp = 1; flagk = 1; }
+    if (kstmp > g.nz) { kstmp = g.nz; flagk = 1; }
+    const double* rec = g.nodes + ((((size_t)(kstmp - 1) * g.ny + (jstmp - 1)) * g.nx + (istmp - 1)) * 32);
+    for (int q = 0; q < 8; ++q) xv[8 * q + l] = srt_corner_scale(q, rec[4 * q + s], g.delx, g.dely, g.delz);
+    if (flagi == 1) { xv[8 + l] = 0.0; xv[32 + l] = 0.0; xv[40 + l] = 0.0; xv[56 + l] = 0.0; }
+    if (flagj == 1) { xv[16 + l] = 0.0; xv[32 + l] = 0.0; xv[48 + l] = 0.0; xv[56 + l] = 0.0; }
+    if (flagk == 1) { xv[24 + l] = 0.0; xv[40 + l] = 0.0; xv[48 + l] = 0.0; xv[56 + l] = 0.0; }
+  }
+  double xp[4], yp[4], zp[4];
+  srt_powers3(xil, xp);
+  srt_powers3(yil, yp);
+  srt_powers3(zil, zp);
+  double v = 0.0;
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j)
+      for (int k = 0; k < 4; ++k) {
+        double cont = srt_amat_row(i + 4 * j + 16 * k, xv) * xp[i] * yp[j] * zp[k];
+        v = v + cont;
+      }
+  return v;
+}
+
+// Ns(1:4) = exp(tricubic(log-density)) at x (SM, metres)
+SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT_NSPEC]) {
+  const int is0 = srt_grid_locate(g.xs, g.nx, g.minx, g.delx, x[0]);
+  const int js0 = srt_grid_locate(g.ys, g.ny, g.miny, g.dely, x[1]);
+  const int ks0 = srt_grid_locate(g.zs, g.nz, g.minz, g.delz, x[2]);
+  const bool ini = is0 >= 1 && is0 < g.nx, inj = js0 >= 1 && js0 < g.ny, ink = ks0 >= 1 && ks0 < g.nz;
+  double xil = 0.0, yil = 0.0, zil = 0.0;
+  if (ini) xil = (x[0] - g.xs[is0 - 1]) / g.delx;
+  if (inj) yil = (x[1] - g.ys[js0 - 1]) / g.dely;
+  if (ink) zil = (x[2] - g.zs[ks0 - 1]) / g.delz;
+  double v[SRT_NSPEC] = {0.0, 0.0, 0.0, 0.0};
+  if (ini && inj && ink && g.coef) {
+    const double* a = g.coef + ((((size_t)(ks0 - 1) * (g.ny - 1) + (js0 - 1)) * (g.nx - 1) + (is0 - 1)) * 256);
+    double xp[4], yp[4], zp[4];
+    srt_powers3(xil, xp);
+    srt_powers3(yil, yp);
+    srt_powers3(zil, zp);
+#pragma unroll 1
+    for (int i = 0; i < 4; ++i) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int t = 16 * i + 4 * j + k;
+#if defined(__CUDA_ARCH__)
+          const double2 a01 = __ldg((const double2*)(a + 4 * t));
+          const double2 a23 = __ldg((const double2*)(a + 4 * t + 2));
+          const double as[4] = {a01.x, a01.y, a23.x, a23.y};
+#else
+          const double* as = a + 4 * t;
+#endif
+#pragma unroll
+          for (int s = 0; s < SRT_NSPEC; ++s) v[s] = v[s] + as[s] * xp[i] * yp[j] * zp[k];
+        }
+      }
+    }
+  } else {
+    for (int s = 0; s < g.nspec; ++s) v[s] = srt_tricubic_slow(g, is0, js0, ks0, xil, yil, zil, s);
+  }
+  for (int s = 0; s < SRT_NSPEC; ++s) Ns[s] = (s < g.nspec) ? srt_exp(v[s]) : 0.0;
 }

@@ -32,7 +32,7 @@ def build_hostemu():
     srcs = [os.path.join(csrc, f) for f in os.listdir(csrc)] + [os.path.join(ROOT, "tests", "csrc", "hostemu.cpp")]
     out = os.path.join(BUILD, "libsrt_hostemu.so")
     if _newer(out, srcs):
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-fno-fast-math", "-DEMU_HAVE_GRID", "-shared", "-o", out,
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-fno-fast-math", "-DEMU_HAVE_GRID", "-Wno-attributes", "-shared", "-o", out,
                                os.path.join(ROOT, "tests", "csrc", "hostemu.cpp")])
     out2 = os.path.join(BUILD, "math_probe.so")
     src2 = os.path.join(ROOT, "tests", "csrc", "math_probe.cpp")
@@ -71,7 +71,7 @@ def c2_grid(nf=100, nlat=100, nlon=1):
 class HostEmu:
     """tests/csrc/hostemu.cpp: the device physics compiled for the CPU (test-only)."""
 
-    def __init__(self, kind, path, yearday=2010001, msec=0, use_igrf=0):
+    def __init__(self, kind, path, yearday=2010001, msec=0, use_igrf=0, precomputed_coef=False):
         build_hostemu()
         E = C.CDLL(os.path.join(BUILD, "libsrt_hostemu.so"))
         d, i, vp, l = C.c_double, C.c_int, C.c_void_p, C.c_long
@@ -86,7 +86,7 @@ class HostEmu:
         E.emu_trace.argtypes = [vp, vp, vp, d, d, d, d, i, d, i, d, i, vp, l, vp, vp, vp, vp]
         self.E = E
         fn = E.emu_model_ngo if kind == "ngo" else E.emu_model_grid
-        self.h = fn(path.encode(), yearday, msec, use_igrf)
+        self.h = fn(path.encode(), yearday, msec, use_igrf | (2 if (precomputed_coef and kind != "ngo") else 0))
         if not self.h:
             raise RuntimeError("hostemu model setup failed")
 

@@ -66,6 +66,20 @@ void* emu_model_grid(const char* path, int yearday, int msec, int use_igrf) {
   if (srt_host::load_grid(path, *M, *hg) != 0) { delete M; delete hg; return nullptr; }
   M->grid.nodes = hg->nodes.data();
   M->grid.xs = hg->xs.data(); M->grid.ys = hg->ys.data(); M->grid.zs = hg->zs.data();
+  M->grid.coef = nullptr;
+  if (use_igrf & 2) {  // bit 1: precompute the per-cell coefficients the way srt_coef_kernel does
+    use_igrf &= 1;
+    const SrtGrid& g = M->grid;
+    const size_t ncx = g.nx - 1, ncy = g.ny - 1, ncz = g.nz - 1;
+    std::vector<double>* coef = new std::vector<double>(ncx * ncy * ncz * 256, 0.0);
+    for (size_t cell = 0; cell < ncx * ncy * ncz; ++cell)
+      for (int sp = 0; sp < g.nspec; ++sp) {
+        double a[64];
+        srt_tricubic_cell_coef(g, (int)(cell % ncx), (int)((cell / ncx) % ncy), (int)(cell / (ncx * ncy)), sp, a);
+        for (int t = 0; t < 64; ++t) (*coef)[cell * 256 + 4 * t + sp] = a[t];
+      }
+    M->grid.coef = coef->data();
+  }
   srt_host::set_time(*M, yearday, msec);
   M->use_igrf = use_igrf;
   srt_host::igrf_recalc(yearday, msec, M->igrf);

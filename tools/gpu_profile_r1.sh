@@ -1,0 +1,14 @@
+#!/bin/bash
+# round-1 profiling pass (run under gpurun): launch list of the bench + one full ncu capture per trace-kernel form
+mkdir -p gpurun_out
+B="python bench.py --steps 2 --warmup 1 --no-cpu-baseline"
+$B > gpurun_out/r1_plain_bench.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r1_launches.csv $B > gpurun_out/r1_ncu_bench.log 2>&1
+T="python tools/profile_case.py team 100 48 300"
+$T > gpurun_out/r1_plain_team.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:srt_trace -s 1 -c 1 -f -o gpurun_out/r1_team $T > gpurun_out/r1_ncu_team.log 2>&1
+T="python tools/profile_case.py thread 200 200 150"
+$T > gpurun_out/r1_plain_thread.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:srt_trace -s 1 -c 1 -f -o gpurun_out/r1_thread $T > gpurun_out/r1_ncu_thread.log 2>&1
+cat gpurun_out/r1_plain_team.log gpurun_out/r1_plain_thread.log
+tail -3 gpurun_out/r1_ncu_team.log gpurun_out/r1_ncu_thread.log
