@@ -167,7 +167,7 @@ __global__ void srt_eval_kernel(long long n, const double* __restrict__ x, doubl
     for (int s = 0; s < 4; ++s) {
       o[s] = M.qs[s];
       o[4 + s] = p.Ns[s];
-      o[8 + s] = M.ms[s];
+      o[8 + s] = s < M.nspec ? M.ms[s] : 0.0;
       o[12 + s] = 0.0;
     }
 #pragma unroll

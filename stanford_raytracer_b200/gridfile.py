@@ -50,9 +50,14 @@ def sample_grid(plasma_fn, nx, ny, nz, extent, min_radius=R_E):
     Pq[zero] = [min_radius, 0.0, 0.0]
     sel = inside & ~zero
     Pq[sel] = P[sel] * (min_radius / r[sel])[:, None]
+    # the analytic (Ngo) model is singular on the dipole axis (L = r / sin^2(colat)): nudge axis nodes off it
+    axis = (Pq[:, 0] == 0.0) & (Pq[:, 1] == 0.0)
+    Pq[axis, 0] = 1e-3 * np.abs(Pq[axis, 2])
     raw = plasma_fn(np.ascontiguousarray(Pq))
     Ns = raw[:, 4:8]
     f = np.log(Ns).reshape(nz, ny, nx, 4)
+    if not np.isfinite(f).all():
+        raise ValueError("sample_grid: %d non-finite log-densities" % int((~np.isfinite(f)).sum()))
     return f, raw[0, 0:4].copy(), raw[0, 8:12].copy()
 
 

@@ -42,7 +42,7 @@ static void plasma_n(const SrtModel& M, long n, const double* x, double* out) {
     SrtPlasma p;
     srt_plasma<D, I>(SrtModelRef{&M}, x + 3 * i, p);
     double* o = out + 19 * i;
-    for (int s = 0; s < 4; ++s) { o[s] = M.qs[s]; o[4 + s] = p.Ns[s]; o[8 + s] = M.ms[s]; o[12 + s] = 0.0; }
+    for (int s = 0; s < 4; ++s) { o[s] = M.qs[s]; o[4 + s] = p.Ns[s]; o[8 + s] = s < M.nspec ? M.ms[s] : 0.0; o[12 + s] = 0.0; }
     for (int c = 0; c < 3; ++c) o[16 + c] = p.B0[c];
   }
 }
