@@ -1,6 +1,8 @@
 // srt_api.cu -- the C ABI of include/srt.h over the sm_100a kernels.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo (build.py).
+#ifndef SRT_BLOCK_THREADS
 #define SRT_BLOCK_THREADS 64
+#endif
 // resident 64-thread blocks per SM the trace kernels are compiled for (register budget = 65536 / (64 * blocks))
 #ifndef SRT_THREAD_MIN_BLOCKS
 #define SRT_THREAD_MIN_BLOCKS 4

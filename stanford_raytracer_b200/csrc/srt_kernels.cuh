@@ -91,7 +91,13 @@ __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_THREAD_MIN_BLOCKS) srt_
         }
       }
     }
+#if defined(SRT_BLOCK_SYNC)
+    // block-synchronous attempts: every warp of the block starts its next attempt together, so the warps
+    // walk the (instruction-cache-sized) step code in phase and share the fetched lines
+    if (__syncthreads_or(active ? 1 : 0) == 0) break;
+#else
     if (__ballot_sync(full, active) == 0u) break;  // queue empty and every lane finished
+#endif
 
     if (active) {
       int r = SRT_ATTEMPT_DONE;

@@ -3,10 +3,10 @@ import ctypes as C, glob, os, sys
 sys.path.insert(0, "."); sys.path.insert(0, "tests")
 import numpy as np, torch
 import stanford_raytracer_b200 as srt, common
-nf, nl, tmax = int(sys.argv[1]), int(sys.argv[2]), float(sys.argv[3])
+nf, nl, maxsteps = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
 pos0, dir0, w0 = common.c2_grid(nf, nl)
 n = len(w0)
-p = dict(common.C2, tmax=tmax)
+p = dict(common.C2, maxsteps=maxsteps)
 P = srt.RunParams(p["dt0"], p["dtmax"], p["maxerr"], p["minalt"], p["tmax"], p["maxsteps"], p["root"], p["fixedstep"], 1)
 rays0 = torch.from_numpy(np.ascontiguousarray(np.concatenate([pos0.T, dir0.T, w0[None, :]], axis=0))).cuda()
 summary = torch.zeros((n, 24), dtype=torch.float64, device="cuda")
