@@ -17,7 +17,7 @@ LIB = os.path.join(HERE, "libsrt.so")
 CLI = os.path.join(HERE, "raytracer")
 
 NVCC_FLAGS = [
-    "-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-fmad=false", "-lineinfo",
+    "-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-fmad=false", "-lineinfo", "-w",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fno-fast-math",
 ]
 
@@ -41,8 +41,18 @@ def build(force=False, verbose=False):
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     srcs = sources()
     if force or _newer(LIB, srcs):
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", LIB, os.path.join(CSRC, "srt_api.cu")]
-        subprocess.check_call(cmd)
+        extra = (["-Xptxas", "-v"] if verbose else [])
+        # two translation units, compiled concurrently: the thread-per-ray kernel + C ABI (elementary functions
+        # inlined) and the team-of-8 kernel (elementary functions as calls); see srt_team_tu.cu
+        objs = [os.path.join(HERE, "srt_api.o"), os.path.join(HERE, "srt_team_tu.o")]
+        procs = [subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-DSRT_INLINE_MATH", "-c", "-o", objs[0], os.path.join(CSRC, "srt_api.cu")]),
+                 subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-c", "-o", objs[1], os.path.join(CSRC, "srt_team_tu.cu")])]
+        for pr in procs:
+            if pr.wait() != 0:
+                raise subprocess.CalledProcessError(pr.returncode, pr.args)
+        subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB] + objs)
+        for o in objs:
+            os.remove(o)
     cli_src = os.path.join(CSRC, "srt_cli.cpp")
     if os.path.exists(cli_src) and (force or _newer(CLI, srcs + [LIB])):
         gxx = shutil.which("g++") or "g++"

@@ -1,17 +1,19 @@
 // srt_api.cu -- the C ABI of include/srt.h over the sm_100a kernels.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo (build.py).
+// This unit holds the one-thread-per-ray trace kernel: 256-thread blocks (one per SM, <= 255 registers)
+// that start every attempt together (SRT_BLOCK_SYNC), elementary functions inlined (SRT_INLINE_MATH in
+// build.py).  The team-of-8 kernel is compiled separately (srt_team_tu.cu).
 #ifndef SRT_BLOCK_THREADS
-#define SRT_BLOCK_THREADS 64
+#define SRT_BLOCK_THREADS 256
 #endif
-// resident 64-thread blocks per SM the trace kernels are compiled for (register budget = 65536 / (64 * blocks))
 #ifndef SRT_THREAD_MIN_BLOCKS
-#define SRT_THREAD_MIN_BLOCKS 4
+#define SRT_THREAD_MIN_BLOCKS 1
 #endif
-#ifndef SRT_TEAM_MIN_BLOCKS
-#define SRT_TEAM_MIN_BLOCKS 4
+#ifndef SRT_BLOCK_SYNC
+#define SRT_BLOCK_SYNC 1
 #endif
 #include "srt_kernels.cuh"
-#include "srt_team.cuh"
+#include "srt_team_tu.h"
 #include "srt_host_setup.h"
 #include "srt_grid_setup.h"
 #include "srt_igrf_setup.h"
@@ -63,10 +65,6 @@ int ensure_device() {
 typedef void (*trace_kernel_t)(const SrtRunParams, const SrtBatch);
 typedef void (*eval_kernel_t)(long long, const double*, double*);
 
-trace_kernel_t pick_team(const SrtModel& M) {
-  if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_NGO, 1> : srt_trace_team_kernel<SRT_DENS_NGO, 0>;
-  return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_GRID, 1> : srt_trace_team_kernel<SRT_DENS_GRID, 0>;
-}
 trace_kernel_t pick_trace(const SrtModel& M) {
   if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_trace_kernel<SRT_DENS_NGO, 1> : srt_trace_kernel<SRT_DENS_NGO, 0>;
   return M.use_igrf ? srt_trace_kernel<SRT_DENS_GRID, 1> : srt_trace_kernel<SRT_DENS_GRID, 0>;
@@ -109,33 +107,47 @@ int pick_mode(const srt_model* m, long long nrays) {
   const char* env = getenv("SRT_KERNEL");
   if (env && !strcmp(env, "thread")) return 0;
   if (env && !strcmp(env, "team")) return 1;
-  return nrays < (long long)m->grid[0] * SRT_BLOCK_THREADS * 4 ? 1 : 0;
+  return nrays < (long long)m->grid[0] * SRT_BLOCK_THREADS ? 1 : 0;
 }
 
-int launch_config(srt_model* m) {
-  if (m->grid[0]) return SRT_OK;
-  for (int mode = 0; mode < 2; ++mode) {
+// persistent launch geometry of a batch: mode (0 thread / 1 team), block, grid = one resident wave at most
+int launch_config(srt_model* m, long long nrays, int* mode_out, int* block_out, int* grid_out, int* blocks_per_sm_out) {
+  if (!m->grid[0]) {
     int nb = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, mode ? pick_team(m->M) : pick_trace(m->M), SRT_BLOCK_THREADS, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pick_trace(m->M), SRT_BLOCK_THREADS, 0));
     if (nb < 1) nb = 1;
-    m->blocks_per_sm[mode] = nb;
-    m->grid[mode] = nb * g_num_sms;  // persistent: exactly one resident wave
+    m->blocks_per_sm[0] = nb;
+    m->grid[0] = nb * g_num_sms;
   }
+  const int mode = pick_mode(m, nrays);
+  int block = SRT_BLOCK_THREADS, nb = m->blocks_per_sm[0];
+  if (mode) {
+    block = srt_team_block_threads(nrays, g_num_sms);
+    CK(srt_team_occupancy(m->M, block, &nb));
+    if (nb < 1) nb = 1;
+  }
+  const long long lanes_per_ray = mode ? 8 : 1;
+  long long blocks_needed = (nrays * lanes_per_ray + block - 1) / block;
+  long long resident = (long long)nb * g_num_sms;
+  int grid = (int)(blocks_needed < resident ? blocks_needed : resident);
+  if (grid < 1) grid = 1;
+  *mode_out = mode; *block_out = block; *grid_out = grid;
+  if (blocks_per_sm_out) *blocks_per_sm_out = nb;
   return SRT_OK;
 }
 
 // upload the model and launch the persistent trace kernel on `stream`; caller holds g_model_mutex
 int launch_trace(srt_model* m, const SrtRunParams& P, const SrtBatch& B, cudaStream_t stream) {
-  int rc = launch_config(m);
+  int mode, block, grid;
+  int rc = launch_config(m, B.nrays, &mode, &block, &grid, nullptr);
   if (rc) return rc;
-  CK(cudaMemcpyToSymbolAsync(c_srt_model, &m->M, sizeof(SrtModel), 0, cudaMemcpyHostToDevice, stream));
   CK(cudaMemsetAsync(B.counters, 0, 8 * sizeof(unsigned long long), stream));
-  const int mode = pick_mode(m, B.nrays);
-  const long long lanes_per_ray = mode ? 8 : 1;
-  long long blocks_needed = (B.nrays * lanes_per_ray + SRT_BLOCK_THREADS - 1) / SRT_BLOCK_THREADS;
-  int grid = (int)(blocks_needed < m->grid[mode] ? blocks_needed : m->grid[mode]);
-  if (grid < 1) grid = 1;
-  (mode ? pick_team(m->M) : pick_trace(m->M))<<<grid, SRT_BLOCK_THREADS, 0, stream>>>(P, B);
+  if (mode) {
+    CK(srt_team_launch(m->M, P, B, block, grid, stream));
+  } else {
+    CK(cudaMemcpyToSymbolAsync(c_srt_model, &m->M, sizeof(SrtModel), 0, cudaMemcpyHostToDevice, stream));
+    pick_trace(m->M)<<<grid, block, 0, stream>>>(P, B);
+  }
   g_launches++;
   CK(cudaGetLastError());
   return SRT_OK;
@@ -296,17 +308,18 @@ int srt_kernel_info(const srt_model* m, int64_t nrays, int* mode, int* regs, int
   int rc = ensure_device();
   if (rc) return rc;
   srt_model* mm = const_cast<srt_model*>(m);
-  rc = launch_config(mm);
+  int md, blk, grd, nb;
+  rc = launch_config(mm, nrays, &md, &blk, &grd, &nb);
   if (rc) return rc;
-  const int md = pick_mode(mm, nrays);
   cudaFuncAttributes fa;
-  CK(cudaFuncGetAttributes(&fa, md ? pick_team(m->M) : pick_trace(m->M)));
+  if (md) CK(srt_team_attributes(m->M, &fa));
+  else CK(cudaFuncGetAttributes(&fa, pick_trace(m->M)));
   if (mode) *mode = md;
   if (regs) *regs = fa.numRegs;
   if (local_bytes) *local_bytes = (int)fa.localSizeBytes;
-  if (blocks_per_sm) *blocks_per_sm = mm->blocks_per_sm[md];
-  if (grid) *grid = mm->grid[md];
-  if (block) *block = SRT_BLOCK_THREADS;
+  if (blocks_per_sm) *blocks_per_sm = nb;
+  if (grid) *grid = grd;
+  if (block) *block = blk;
   return SRT_OK;
 }
 

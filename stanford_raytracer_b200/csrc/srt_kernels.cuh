@@ -142,6 +142,7 @@ __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_THREAD_MIN_BLOCKS) srt_
   }
 }
 
+#if !defined(SRT_TEAM_TU)
 // log[slot] -> sorted[offsets[ray] + row]; entries of dropped rays are skipped
 __global__ void srt_scatter_kernel(const double* __restrict__ log, unsigned long long nlog, const unsigned long long* __restrict__ offsets,
                                    const unsigned* __restrict__ nlogged, double* __restrict__ sorted) {
@@ -222,3 +223,4 @@ __global__ void srt_fp64_peak_kernel(int iters, double seed, double* out) {
   double s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
   if (s == 123.456) out[0] = s;  // keeps the loop alive; never true
 }
+#endif  // !SRT_TEAM_TU

@@ -759,6 +759,8 @@ SRT_HD int srt_ray_attempt(SrtModelRef MR, const SrtRunParams& P, SrtRayState& s
   const double dt = st.dt;
   double xs[6] = {st.x[0], st.x[1], st.x[2], st.k[0], st.k[1], st.k[2]};
   double e2x[6];  // est2(1:6)
+  SrtCentre c2;   // plasma / derived / Stix(w) at est2(1:3) = the new point
+  bool have_c2 = false;
   double k1[6];
 #pragma unroll
   for (int i = 0; i < 6; ++i) k1[i] = dt * st.rhs1[i];
@@ -811,8 +813,10 @@ SRT_HD int srt_ray_attempt(SrtModelRef MR, const SrtRunParams& P, SrtRayState& s
       double g1[3], g2[3];
       srt_centre<DENS, USE_IGRF>(MR, e1x, st.wl, c1);
       srt_dFdk(e1x + 3, st.wl, c1.d, c1.s, g1);
-      srt_centre<DENS, USE_IGRF>(MR, e2x, st.wl, c1);
-      srt_dFdk(e2x + 3, st.wl, c1.d, c1.s, g2);
+      // the plasma at est2 is also the plasma of the new point (:819): kept for the re-projection below
+      srt_centre<DENS, USE_IGRF>(MR, e2x, st.wl, c2);
+      srt_dFdk(e2x + 3, st.wl, c2.d, c2.s, g2);
+      have_c2 = (st.wl == st.w);
       double sc = 0.0, sd = 0.0;
 #pragma unroll
       for (int i = 0; i < 3; ++i) sc = sc + srt_fabs(g1[i] - g2[i]);
@@ -857,8 +861,7 @@ SRT_HD int srt_ray_attempt(SrtModelRef MR, const SrtRunParams& P, SrtRayState& s
   }
   const double dtincr = dt;
   // re-project |k| onto the dispersion surface at the new point (:819-836)
-  SrtCentre c2;
-  srt_centre<DENS, USE_IGRF>(MR, e2x, st.w, c2);
+  if (!have_c2) srt_centre<DENS, USE_IGRF>(MR, e2x, st.w, c2);
   SrtCplx ksel = srt_solve_root(e2x + 3, st.w, c2.d, c2.s, P.root);
   // k = kmag*(k/sqrt(dot_product(k,k))) in complex arithmetic (Q18)
   double kk = 0.0;

@@ -141,7 +141,12 @@ __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_TEAM_MIN_BLOCKS) srt_tr
         }
       }
     }
+#if defined(SRT_TEAM_BLOCK_SYNC)
+    // block-synchronous rounds: the warps of a block walk the round's code in phase and share instruction lines
+    if (__syncthreads_or(phase != SRT_PH_IDLE ? 1 : 0) == 0) break;
+#else
     if (__ballot_sync(full, phase != SRT_PH_IDLE) == 0u) break;
+#endif
 
     if (phase != SRT_PH_IDLE) {
       // ================= top of an attempt: raytracer.f95:749-763
