@@ -35,24 +35,52 @@ import numpy as np  # noqa: E402
 
 METRIC = "accepted_ray_steps_per_sec"
 UNIT = "ray-steps/s"
-FLOPS_ACCEPTED = 4.2e4  # flop-equivalents per accepted RK45 step, Ngo + dipole
-FLOPS_REJECTED = 4.0e4  # per rejected attempt
 ROW_BYTES = 168         # one log entry
 
 
-def workload(rank, nf=100, nlat=100):
+WORKLOADS = {
+    # name: (n_freq, n_lat, n_lon, outputper, model, flop-eq per accepted step, per rejected attempt, description)
+    "c2": (100, 100, 1, 1, "ngo", 4.2e4, 4.0e4,
+           "C2: 10k-ray sweep (100 freq 0.2-30 kHz x 100 lat 10-60 deg), Ngo density + dipole B, adaptive RK45 "
+           "(dt0=1e-3, dtmax=0.1, maxerr=5e-4, tmax=10 s, root=2), per GPU"),
+    "c3": (100, 100, 10, 100, "grid", 6.8e4, 6.5e4,
+           "C3: 100k rays (100 freq x 100 lat x 10 lon) through a tricubic 80^3 log-density grid over +-10 R_E (sampled from "
+           "the Ngo model by the GPU funcPlasmaParams kernel: GCPM cannot be built here) + IGRF field, adaptive RK45, per GPU"),
+    "c4": (100, 1000, 10, 100, "ngo", 4.2e4, 4.0e4,
+           "C4: 1M-ray launch grid (100 freq x 1000 lat x 10 lon), Ngo density + dipole B, adaptive RK45, per GPU"),
+}
+R_E = 6371.2e3
+_GRID_CACHE = os.path.join(ROOT, "gpurun_out", "bench_grid80.txt")
+
+
+def workload(rank, name="c2"):
     import common
+    nf, nlat, nlon, outputper, model, fa, fr, desc = WORKLOADS[name]
     freqs = np.logspace(np.log10(200.0), np.log10(30000.0), nf)
     lats = np.linspace(10.0, 60.0, nlat)
-    pos0, dir0, w0 = common.launch_grid(freqs, lats, [36.0 * rank])
+    lons = (np.arange(nlon) * 36.0 + 36.0 * rank / max(nlon, 1)) if nlon > 1 else [36.0 * rank]
+    pos0, dir0, w0 = common.launch_grid(freqs, lats, lons)
     return pos0, dir0, w0, dict(common.C2), common.NGO_CFG
 
 
-def config_dict(n_gpus):
-    return {"workload": "C2: 10k-ray sweep (100 freq 0.2-30 kHz x 100 lat 10-60 deg), Ngo density + dipole B, adaptive RK45 "
-                        "(dt0=1e-3, dtmax=0.1, maxerr=5e-4, tmax=10 s, root=2), per GPU",
-            "rays_per_gpu": 10000, "global_rays": 10000 * n_gpus, "outputper": 1, "parallelism": "rays sharded by rank, no collective",
-            "l2": "flushed between timed iterations (256 MiB write)"}
+def make_model(srt, name, cfg):
+    """The plasma model of a workload, built through the product's own API (never the oracle)."""
+    if WORKLOADS[name][4] == "ngo":
+        return srt.ngosetup(cfg, 2010001, 0, 0, 0)
+    from stanford_raytracer_b200 import gridfile
+    os.makedirs(os.path.dirname(_GRID_CACHE), exist_ok=True)
+    path = _GRID_CACHE + ".%d" % int(os.environ.get("LOCAL_RANK", "0"))
+    if not os.path.exists(path):
+        ngo = srt.ngosetup(cfg, 2010001, 0, 0, 0)
+        ext = (-10 * R_E, 10 * R_E) * 3
+        f, qs, ms = gridfile.sample_grid(lambda x: ngo.funcPlasmaParams(x)["raw"], 80, 80, 80, ext)
+        gridfile.write_grid(path, f, qs, ms, ext)
+    return srt.interpsetup(path, 2010001, 0, 1, 0)
+
+
+def config_dict(n_gpus, name="c2", nrays=10000):
+    return {"workload": WORKLOADS[name][7], "rays_per_gpu": nrays, "global_rays": nrays * n_gpus, "outputper": WORKLOADS[name][3],
+            "parallelism": "rays sharded by rank, no collective", "l2": "flushed between timed iterations (256 MiB write)"}
 
 
 class ClockSampler(threading.Thread):
@@ -81,14 +109,14 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def cpu_reference_run(pos0, dir0, w0, params, cfg, nsample, threads):
+def cpu_reference_run(pos0, dir0, w0, params, cfg, nsample, threads, kind="ngo", use_igrf=0):
     """Times the CPU oracle (the port of the reference) on a strided sample of the workload,
     one model instance per thread.  Returns (accepted steps, seconds)."""
     import oracle_lib as ol
     idx = np.linspace(0, len(w0) - 1, nsample).astype(int)
     chunks = [idx[i::threads] for i in range(threads)]
     chunks = [c for c in chunks if len(c)]
-    models = [ol.OracleModel("ngo", cfg) for _ in chunks]
+    models = [ol.OracleModel(kind, cfg, use_igrf=use_igrf) for _ in chunks]
     acc = [0] * len(chunks)
 
     def work(i):
@@ -109,7 +137,7 @@ def run_reference(args):
         return
     import oracle_lib as ol
     ol.build()
-    pos0, dir0, w0, params, cfg = workload(0)
+    pos0, dir0, w0, params, cfg = workload(0, "c2")
     threads = os.cpu_count() or 1
     nsample = max(threads, 96)
     for _ in range(args.warmup):
@@ -136,6 +164,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="c2 is the bench line; c3/c4 are the other BASELINE configs")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -155,11 +184,14 @@ def main():
     dev = torch.device("cuda", local_rank)
     srt.init(local_rank)
 
-    pos0, dir0, w0, params, cfg = workload(rank)
+    wl = args.workload
+    outputper = WORKLOADS[wl][3]
+    FLOPS_ACCEPTED, FLOPS_REJECTED = WORKLOADS[wl][5], WORKLOADS[wl][6]
+    pos0, dir0, w0, params, cfg = workload(rank, wl)
     nrays = len(w0)
-    model = srt.ngosetup(cfg, 2010001, 0, 0, 0)
+    model = make_model(srt, wl, cfg)
     P = srt.RunParams(params["dt0"], params["dtmax"], params["maxerr"], params["minalt"], params["tmax"], params["maxsteps"], params["root"],
-                      params["fixedstep"], 1)
+                      params["fixedstep"], outputper)
     # device-resident inputs (SoA) and outputs
     rays_h = np.ascontiguousarray(np.concatenate([pos0.T, dir0.T, w0[None, :]], axis=0))  # [7][nrays], C order (concatenate keeps F order)
     rays0 = torch.from_numpy(rays_h).to(dev)
@@ -169,7 +201,7 @@ def main():
     # size the trajectory log from a counting pass (no log attached: nothing recorded, nothing dropped)
     srt.trace_batch_device(model, nrays, rays.data_ptr(), P, 0, 0, summary.data_ptr(), counters.data_ptr(), torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
-    log_cap = int(counters[1].item()) + nrays + 1024
+    log_cap = int(counters[1].item()) // outputper + 2 * nrays + 1024
     log = torch.empty((log_cap, srt.LOG_WORDS), dtype=torch.float64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream()
@@ -221,7 +253,7 @@ def main():
 
     # ---- end to end through the C ABI with host buffers
     e2e_steps = max(1, min(args.steps, 3))
-    res = srt.raytracer_run(model, pos0, dir0.copy(), w0, outputper=1, **params)  # warm-up (allocations)
+    res = srt.raytracer_run(model, pos0, dir0.copy(), w0, outputper=outputper, **params)  # warm-up (allocations)
     d2h = res.total_rows * 160 + nrays * (srt.SUMMARY_WORDS * 8 + 4 + 56) + 64
     h2d = nrays * 56 + nrays * 8
     res.close()
@@ -229,7 +261,7 @@ def main():
     t0 = time.perf_counter()
     e2e_acc = 0
     for _ in range(e2e_steps):
-        res = srt.raytracer_run(model, pos0, dir0.copy(), w0, outputper=1, **params)
+        res = srt.raytracer_run(model, pos0, dir0.copy(), w0, outputper=outputper, **params)
         e2e_acc += res.accepted_steps
         res.close()
     torch.cuda.synchronize()
@@ -255,10 +287,18 @@ def main():
         pass
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     hbm_ach = (rows_per_step * ROW_BYTES + nrays * (56 + srt.SUMMARY_WORDS * 8)) / avg_launch_s / 1e9
-    roofline = {"bound": "fp64", "achieved": achieved, "peak": peak_fma, "unit": "TFLOP/s", "frac": achieved / peak_fma, "traffic": None,
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1b_traffic.json")))
+        if tj.get("workload") == wl and model.kernel_info(nrays)["mode"] == "team8":
+            traffic = tj["dram_bytes_per_launch"]  # bytes per launch of this kernel on this workload, from the committed ncu pass
+    except Exception:
+        pass
+    roofline = {"bound": "fp64", "achieved": achieved, "peak": peak_fma, "unit": "TFLOP/s", "frac": achieved / peak_fma, "traffic": traffic,
+                "bound_note": "FP64 (non-tensor) pipe: the path is scalar FP64 with no dense contraction and ~1e-4 of HBM bandwidth, so neither 'hbm' nor 'tensor' applies",
                 "peak_source": "DFMA micro-kernel measured live (srt_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
                 "peak_no_fma": peak_nofma, "frac_no_fma": achieved / peak_nofma,
-                "work_model": "4.2e4 flop-eq per accepted RK45 step + 4.0e4 per rejected attempt (SURVEY.md 8d, Ngo+dipole)",
+                "work_model": "%.2g flop-eq per accepted RK45 step + %.2g per rejected attempt (SURVEY.md 8d)" % (FLOPS_ACCEPTED, FLOPS_REJECTED),
                 "hbm": {"achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak,
                         "of": "measured" if "hbm_gbs" in peaks else "fallback"}}
 
@@ -267,13 +307,17 @@ def main():
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             nsample = max(threads, 96)
-            a, t = cpu_reference_run(pos0, dir0, w0, params, cfg, nsample, threads)
+            if WORKLOADS[wl][4] == "grid":
+                nsample = threads
+                a, t = cpu_reference_run(pos0, dir0, w0, dict(params, maxsteps=300), _GRID_CACHE + ".%d" % local_rank, nsample, threads, "grid", 1)
+            else:
+                a, t = cpu_reference_run(pos0, dir0, w0, params, cfg, nsample, threads)
             cpu = {"value": a / t, "unit": UNIT, "cores": threads, "kind": "port",
-                   "sample": "%d rays strided out of the 10k-ray sweep, %.1f s, faithful call structure of the reference" % (nsample, t)}
+                   "sample": "%d rays strided out of the sweep%s, %.1f s, faithful call structure of the reference" % (nsample, " (first 300 steps of each)" if WORKLOADS[wl][4] == "grid" else "", t)}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": kernel_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-                "data": "synthetic", "config": config_dict(world),
-                "rays_per_sec": 10000.0 * world * args.steps / (kernel_ms_max * 1e-3),
+                "data": "synthetic", "config": config_dict(world, wl, nrays),
+                "rays_per_sec": float(nrays) * world * args.steps / (kernel_ms_max * 1e-3),
                 "attempted_steps_per_sec": total_attempts / (kernel_ms_max * 1e-3),
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": int(launches), "clocks": sampler.result(), "roofline": roofline, "cpu_baseline": cpu,
