@@ -6,8 +6,9 @@
 // 7-point stencil of raytracer_evalrhs (x, x+-dx, x+-dy, x+-dz; raytracer.f95:137,190,
 // 241-261) is embarrassingly parallel, so a team of 8 lanes evaluates it in ONE plasma-
 // evaluation latency: lanes 0-5 take the six displaced points, lanes 6 and 7 the centre
-// (for the w+d and w-d Stix sets).  An accepted step becomes 7 rounds (stage-1 dF/dx,
-// stages 2-6, error estimate + re-projection) instead of 43 sequential evaluations.
+// (for the w+d and w-d Stix sets).  An accepted step becomes 6 rounds (stages 2-6, then
+// error estimate + re-projection + the next step's stage-1 dF/dx stencil in one round)
+// instead of 43 sequential evaluations.
 //
 // Layout of a team: lane r < 6 OWNS component r of the state vector (x,y,z,kx,ky,kz): its
 // stage increments k1..k6, est1/est2 and the RK algebra for that component live only
@@ -197,11 +198,14 @@ __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_TEAM_MIN_BLOCKS) srt_tr
         team_gather6(T, e1c, e1);
         team_gather6(T, e2c, e2);
 #pragma unroll
-        for (int j = 0; j < 6; ++j) y[j] = (r < 4 && adaptive) ? e1[j] : e2[j];
+        for (int j = 0; j < 6; ++j) y[j] = (r == 6 && adaptive) ? e1[j] : e2[j];
       }
       double pt[3] = {y[0], y[1], y[2]};
       double dx_axis = 0.0;
-      if (phase != SRT_PH_EST && r < 6) {
+      // In the error-estimate round only two centre points are needed (lane 6: est1, lane 7: est2), so lanes 0-5
+      // already evaluate the six displaced points around est2 = the NEXT attempt's stage-1 dF/dx stencil
+      // (raytracer.f95:819: the new point is est2(1:3)); used if the step is accepted, discarded otherwise.
+      if (r < 6) {
         const double xi = axis == 0 ? y[0] : (axis == 1 ? y[1] : y[2]);
         dx_axis = srt_fd_step(M.del, xi);
         const double v = minus ? xi - dx_axis : xi + dx_axis;
@@ -212,7 +216,7 @@ __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_TEAM_MIN_BLOCKS) srt_tr
       const double dw = srt_fd_step(1.0e-8, w);
       double wr = w;  // the frequency my Stix set is evaluated at
       if (phase == SRT_PH_STAGE) wr = (r == 6) ? w + dw : (r == 7 ? w - dw : w);
-      else if (phase == SRT_PH_EST) wr = (wl != 0.0) ? wl : w;
+      else if (phase == SRT_PH_EST) wr = (r >= 6 && wl != 0.0) ? wl : w;
       SrtPlasma pl;
       SrtPlasmaDerived pd;
       SrtStix sx;

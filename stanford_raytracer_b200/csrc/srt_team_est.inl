@@ -1,7 +1,10 @@
         // ---- srt_team_est.inl: error estimate, re-projection, accept/reject (raytracer.f95:775-922).
-        // Included inside srt_trace_team_kernel; lanes 0-3 hold the plasma at est1, lanes 4-7 at est2
-        // (fixed step: all at est2).
+        // Included inside srt_trace_team_kernel; lane 6 holds the plasma at est1, lane 7 at est2 (fixed step:
+        // both at est2), lanes 0-5 at est2 +- d e_i (the next attempt's stage-1 stencil, speculative).
         const double dt_used = dt;
+        SrtPlasmaDerived pc1, pc2;
+        team_bcast_derived(T, pd, 6, pc1);
+        team_bcast_derived(T, pd, 7, pc2);
         bool retry = false;
         if (adaptive) {
           double sa = 0.0, sb = 0.0;
@@ -15,9 +18,13 @@
             const double* kset = set ? (e2 + 3) : (e1 + 3);
             double n1[3], n2[3], dk1, dk2;
             team_dfdk_n(kset, wl, q >> 1, q & 1, n1, dk1);  // axes 0 and 1 on the four lanes of the set
-            const double F1 = srt_F(n1, wl, pd, sx);
+            SrtPlasmaDerived ps = pc1;
+            if (set) ps = pc2;
+            SrtStix sw;
+            srt_stix(ps, wl, sw);
+            const double F1 = srt_F(n1, wl, ps, sw);
             team_dfdk_n(kset, wl, 2, q & 1, n2, dk2);       // axis 2 on the first two lanes of the set
-            const double F2 = srt_F(n2, wl, pd, sx);
+            const double F2 = srt_F(n2, wl, ps, sw);
             double g[2][3];
 #pragma unroll
             for (int s2 = 0; s2 < 2; ++s2) {
@@ -47,10 +54,10 @@
           }
         }
         if (!retry) {
-          // re-project |k| at est2 (lane 4 holds the plasma there and its Stix set at w)
+          // re-project |k| at est2 (lane 7 holds the plasma there and its Stix set at w)
           SrtCplx ksel = srt_solve_root(e2 + 3, w, pd, sx, P.root);
-          ksel.re = team_get(T, ksel.re, 4);
-          ksel.im = team_get(T, ksel.im, 4);
+          ksel.re = team_get(T, ksel.re, 7);
+          ksel.im = team_get(T, ksel.im, 7);
           double kk = 0.0;
 #pragma unroll
           for (int i = 0; i < 3; ++i) kk = kk + (e2[3 + i] * e2[3 + i] - (-0.0) * 0.0);
@@ -86,8 +93,7 @@
             t = t + dt_used;
             nstep = nstep + 1;
             // dF/dk and dF/dw at the new point: est2's plasma, spread over the 8 lanes
-            SrtPlasmaDerived pc;
-            team_bcast_derived(T, pd, 4, pc);
+            const SrtPlasmaDerived& pc = pc2;
             const double wr2 = (r == 6) ? w + dw : (r == 7 ? w - dw : w);
             SrtStix s2;
             srt_stix(pc, wr2, s2);
@@ -116,10 +122,10 @@
               row[4 + i] = nn[i] / n2;
               row[7 + i] = -(dfdk_new[i] / dfdw_rec) / C;
               row[10 + i] = nn[i];
-              row[13 + i] = team_get(T, pl.B0[i], 4);
+              row[13 + i] = team_get(T, pl.B0[i], 7);
             }
 #pragma unroll
-            for (int i = 0; i < SRT_NSPEC; ++i) row[16 + i] = team_get(T, pl.Ns[i], 4);
+            for (int i = 0; i < SRT_NSPEC; ++i) row[16 + i] = team_get(T, pl.Ns[i], 7);
             vg[0] = row[7]; vg[1] = row[8]; vg[2] = row[9];
             if (r == 0) {
               ++my_accepted;
@@ -134,7 +140,17 @@
               }
             }
             dropped = __shfl_sync(T.tmask, (int)dropped, T.tbase) != 0;
-            phase = SRT_PH_S1DX;
+            // stage 1 of the next attempt (raytracer_evalrhs at the new point): dF/dk, dF/dw just recorded,
+            // dF/dx from the six displaced points lanes 0-5 evaluated in this round
+            {
+              const double FA = srt_F(nn, w, pd, sx);
+              const int j2 = 2 * (comp % 3);
+              const double Fp = team_get(T, FA, j2), Fn = team_get(T, FA, j2 + 1);
+              const double ddx = team_get(T, dx_axis, j2);
+              if (comp < 3) rhs1c = -(dfdk_c / dfdw_rec);
+              else rhs1c = ((Fp - Fn) / ddx / 2.0) / dfdw_rec;
+            }
+            phase = SRT_PH_STAGE;  // the attempt-start block sets kk1, tmpc and stage = 2 from rhs1c
             attempt_start = true;
           }
         }
