@@ -42,11 +42,11 @@ def build(force=False, verbose=False):
     srcs = sources()
     if force or _newer(LIB, srcs):
         extra = (["-Xptxas", "-v"] if verbose else [])
-        # two translation units, compiled concurrently: the thread-per-ray kernel + C ABI (elementary functions
-        # inlined) and the team-of-8 kernel (elementary functions as calls); see srt_team_tu.cu
+        # two translation units, compiled concurrently: the thread-per-ray kernel + C ABI and the
+        # team-of-8 kernel in two register budgets; elementary functions inlined in both; see srt_team_tu.cu
         objs = [os.path.join(HERE, "srt_api.o"), os.path.join(HERE, "srt_team_tu.o")]
         procs = [subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-DSRT_INLINE_MATH", "-c", "-o", objs[0], os.path.join(CSRC, "srt_api.cu")]),
-                 subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-c", "-o", objs[1], os.path.join(CSRC, "srt_team_tu.cu")])]
+                 subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-DSRT_INLINE_MATH", "-c", "-o", objs[1], os.path.join(CSRC, "srt_team_tu.cu")])]
         for pr in procs:
             if pr.wait() != 0:
                 raise subprocess.CalledProcessError(pr.returncode, pr.args)

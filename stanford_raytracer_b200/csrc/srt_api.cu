@@ -107,7 +107,11 @@ int pick_mode(const srt_model* m, long long nrays) {
   const char* env = getenv("SRT_KERNEL");
   if (env && !strcmp(env, "thread")) return 0;
   if (env && !strcmp(env, "team")) return 1;
-  return nrays < (long long)m->grid[0] * SRT_BLOCK_THREADS ? 1 : 0;
+  // Since the team form steps block-synchronously with 6 equal rounds per attempt it is the faster one at every
+  // batch size measured (profiles/r1c_modes.txt: 34.7 M vs 32.9 M ray-steps/s at 40 k rays, 26.9 M vs 7.6 M at
+  // 10 k, config-3 shape 30.8 M vs 23.2 M), so it is the default; SRT_KERNEL=thread selects the other form.
+  (void)m; (void)nrays;
+  return 1;
 }
 
 // persistent launch geometry of a batch: mode (0 thread / 1 team), block, grid = one resident wave at most
@@ -312,7 +316,7 @@ int srt_kernel_info(const srt_model* m, int64_t nrays, int* mode, int* regs, int
   rc = launch_config(mm, nrays, &md, &blk, &grd, &nb);
   if (rc) return rc;
   cudaFuncAttributes fa;
-  if (md) CK(srt_team_attributes(m->M, &fa));
+  if (md) CK(srt_team_attributes(m->M, blk, &fa));
   else CK(cudaFuncGetAttributes(&fa, pick_trace(m->M)));
   if (mode) *mode = md;
   if (regs) *regs = fa.numRegs;

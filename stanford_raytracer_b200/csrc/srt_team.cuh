@@ -63,8 +63,8 @@ __device__ __forceinline__ void team_dfdk_n(const double k[3], double w, int axi
   dk_axis = dk;
 }
 
-template <int DENS, int USE_IGRF>
-__global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_TEAM_MIN_BLOCKS) srt_trace_team_kernel(const __grid_constant__ SrtRunParams P, const __grid_constant__ SrtBatch B) {
+template <int DENS, int USE_IGRF, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_constant__ SrtRunParams P, const __grid_constant__ SrtBatch B) {
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const SrtModelRef MR = SrtModelRef();
@@ -98,6 +98,8 @@ __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_TEAM_MIN_BLOCKS) srt_tr
   double tmpc = 0.0;        // my component of the current evaluation point
   double e1c = 0.0, e2c = 0.0;
 
+  unsigned sync_iter = 0;
+  (void)sync_iter;
   for (;;) {
     // ================= refill: idle teams take the next ray; one atomic per warp
     const bool want = (phase == SRT_PH_IDLE) && !exhausted;
@@ -144,6 +146,9 @@ __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_TEAM_MIN_BLOCKS) srt_tr
     }
 #if defined(SRT_TEAM_BLOCK_SYNC)
     // block-synchronous rounds: the warps of a block walk the round's code in phase and share instruction lines
+#if defined(SRT_TEAM_SYNC_EVERY)
+    if ((++sync_iter % SRT_TEAM_SYNC_EVERY) == 0)
+#endif
     if (__syncthreads_or(phase != SRT_PH_IDLE ? 1 : 0) == 0) break;
 #else
     if (__ballot_sync(full, phase != SRT_PH_IDLE) == 0u) break;

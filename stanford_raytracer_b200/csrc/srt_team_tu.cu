@@ -2,21 +2,15 @@
 //
 // The two forms of the integrator want different code generation (measured, profiles/r1_variants.txt):
 //   one thread per ray : 256-thread blocks stepping block-synchronously, elementary functions inlined
-//   team of 8 per ray  : up to 512-thread blocks (128 registers) stepping their rounds block-synchronously
-//                        (2.1x over unsynchronised 64-thread blocks), elementary functions as calls; the
-//                        launch picks a smaller block when the batch is too small to give every SM one
+//   team of 8 per ray  : up to 1024-thread blocks stepping their rounds block-synchronously (2.1x over
+//                        unsynchronised 64-thread blocks); the launch picks a smaller block when the batch is
+//                        too small to give every SM one
 // so each lives in its own translation unit with its own copy of the model in __constant__ memory.
 #define SRT_TEAM_TU 1
-#ifndef SRT_TEAM_BLOCK_THREADS
-#define SRT_TEAM_BLOCK_THREADS 512
-#endif
-#ifndef SRT_TEAM_MIN_BLOCKS
-#define SRT_TEAM_MIN_BLOCKS 1
-#endif
 #ifndef SRT_TEAM_BLOCK_SYNC
 #define SRT_TEAM_BLOCK_SYNC 1
 #endif
-#define SRT_BLOCK_THREADS SRT_TEAM_BLOCK_THREADS
+#define SRT_BLOCK_THREADS 512
 #define SRT_THREAD_MIN_BLOCKS 1
 #include "srt_kernels.cuh"
 #include "srt_team.cuh"
@@ -24,28 +18,35 @@
 
 typedef void (*team_kernel_t)(const SrtRunParams, const SrtBatch);
 
-static team_kernel_t pick_team(const SrtModel& M) {
-  if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_NGO, 1> : srt_trace_team_kernel<SRT_DENS_NGO, 0>;
-  return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_GRID, 1> : srt_trace_team_kernel<SRT_DENS_GRID, 0>;
+// Two register budgets of the same kernel: MAXT = 512 (128 registers; best when rays are scarce and the latency of
+// one ray matters, e.g. config 2 and every tail) and MAXT = 1024 (64 registers, 32 warps per SM; +8 % when the
+// batch fills the machine).  profiles/r1c_variants.txt.
+template <int MAXT>
+static team_kernel_t pick_team_t(const SrtModel& M) {
+  if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_NGO, 1, MAXT> : srt_trace_team_kernel<SRT_DENS_NGO, 0, MAXT>;
+  return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_GRID, 1, MAXT> : srt_trace_team_kernel<SRT_DENS_GRID, 0, MAXT>;
 }
+static team_kernel_t pick_team(const SrtModel& M, int block) { return block > 512 ? pick_team_t<1024>(M) : pick_team_t<512>(M); }
 
-// block size for a batch: the largest power of two <= SRT_TEAM_BLOCK_THREADS that still gives every SM a block
+// block size for a batch: the largest power of two <= 1024 that still gives every SM at least one block
 int srt_team_block_threads(long long nrays, int num_sms) {
-  long long lanes_per_sm = (nrays * 8 + num_sms - 1) / (num_sms > 0 ? num_sms : 1);
+  long long lanes_per_sm = (nrays * 8) / (num_sms > 0 ? num_sms : 1);
   int block = 64;
-  while (block < SRT_TEAM_BLOCK_THREADS && block < lanes_per_sm) block *= 2;
+  while (block * 2 <= 1024 && block * 2 <= lanes_per_sm) block *= 2;
+  const char* env = getenv("SRT_TEAM_BLOCK");  // test / tuning hook
+  if (env && atoi(env) >= 32 && atoi(env) <= 1024) block = atoi(env) / 32 * 32;
   return block;
 }
 
 cudaError_t srt_team_occupancy(const SrtModel& M, int block, int* blocks_per_sm) {
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, pick_team(M), block, 0);
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, pick_team(M, block), block, 0);
 }
 
-cudaError_t srt_team_attributes(const SrtModel& M, cudaFuncAttributes* fa) { return cudaFuncGetAttributes(fa, pick_team(M)); }
+cudaError_t srt_team_attributes(const SrtModel& M, int block, cudaFuncAttributes* fa) { return cudaFuncGetAttributes(fa, pick_team(M, block)); }
 
 cudaError_t srt_team_launch(const SrtModel& M, const SrtRunParams& P, const SrtBatch& B, int block, int grid, cudaStream_t stream) {
   cudaError_t e = cudaMemcpyToSymbolAsync(c_srt_model, &M, sizeof(SrtModel), 0, cudaMemcpyHostToDevice, stream);
   if (e != cudaSuccess) return e;
-  pick_team(M)<<<grid, block, 0, stream>>>(P, B);
+  pick_team(M, block)<<<grid, block, 0, stream>>>(P, B);
   return cudaGetLastError();
 }

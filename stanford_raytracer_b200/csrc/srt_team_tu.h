@@ -6,6 +6,6 @@ struct SrtRunParams;
 struct SrtBatch;
 int srt_team_block_threads(long long nrays, int num_sms);
 cudaError_t srt_team_occupancy(const SrtModel& M, int block, int* blocks_per_sm);
-cudaError_t srt_team_attributes(const SrtModel& M, cudaFuncAttributes* fa);
+cudaError_t srt_team_attributes(const SrtModel& M, int block, cudaFuncAttributes* fa);
 // uploads the model into this unit's __constant__ copy and launches the kernel on `stream`
 cudaError_t srt_team_launch(const SrtModel& M, const SrtRunParams& P, const SrtBatch& B, int block, int grid, cudaStream_t stream);

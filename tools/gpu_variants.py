@@ -17,7 +17,7 @@ for path in libs:
     srt._LIB_PATH = os.path.abspath(path)
     srt.init(0)
     m = srt.ngosetup(common.NGO_CFG, 2010001, 0, 0, 0)
-    for mode in ("thread", "team"):
+    for mode in (sys.argv[4].split(",") if len(sys.argv) > 4 else ("thread", "team")):
         os.environ["SRT_KERNEL"] = mode
         best = 1e30
         for rep in range(2):
