@@ -141,7 +141,21 @@ int launch_config(srt_model* m, long long nrays, int* mode_out, int* block_out, 
 }
 
 // upload the model and launch the persistent trace kernel on `stream`; caller holds g_model_mutex
-int launch_trace(srt_model* m, const SrtRunParams& P, const SrtBatch& B, cudaStream_t stream) {
+// multiplier of the queue permutation (srt_queue_ray): the integer nearest nrays/golden ratio that is coprime to nrays
+unsigned long long ray_order_mul(long long nrays) {
+  const char* e = getenv("SRT_RAY_ORDER");
+  if ((e && atoi(e) == 0) || nrays < 4) return 1ull;
+  unsigned long long n = (unsigned long long)nrays, mul = (unsigned long long)((double)nrays * 0.6180339887498949);
+  for (;; ++mul) {
+    unsigned long long a = n, b = mul % n;
+    while (b) { unsigned long long t = a % b; a = b; b = t; }
+    if (a == 1ull && mul % n != 0ull) return mul % n;
+  }
+}
+
+int launch_trace(srt_model* m, const SrtRunParams& P, const SrtBatch& B0, cudaStream_t stream) {
+  SrtBatch B = B0;
+  B.order_mul = ray_order_mul(B.nrays);
   int mode, block, grid;
   int rc = launch_config(m, B.nrays, &mode, &block, &grid, nullptr);
   if (rc) return rc;
@@ -342,6 +356,7 @@ int srt_trace_batch_device(const srt_model* m, int64_t nrays, double* d_rays, co
   B.summary = d_summary;
   B.counters = (unsigned long long*)d_counters;
   B.nlogged = nullptr;
+  B.order_mul = 1;  // set by launch_trace
   std::lock_guard<std::mutex> lk(g_model_mutex);
   return launch_trace(const_cast<srt_model*>(m), P, B, (cudaStream_t)stream);
 }

@@ -35,7 +35,16 @@ struct SrtBatch {
   double* summary;                  // [nrays][SRT_SUMMARY_WORDS]
   unsigned long long* counters;     // [0] log rows, [1] accepted steps, [2] attempts, [3] dropped rays, [4] ray queue head
   unsigned* nlogged;                // optional [nrays]: rows this ray put in the log
+  unsigned long long order_mul;     // queue position q is ray (q * order_mul) mod nrays; coprime to nrays (1 = input order)
 };
+
+// Queue position -> ray index.  A batch of the size of one machine fill (config 2) is handed out once: in input order
+// the long-lived rays (neighbours in frequency) would all land in the same few blocks and the rest of the SMs would
+// idle through the tail.  A golden-ratio stride spreads every run of consecutive queue positions evenly over the
+// input order.  Which thread integrates which ray has no effect on any result.
+__device__ __forceinline__ long long srt_queue_ray(const SrtBatch& B, long long q) {
+  return (long long)(((unsigned long long)q * B.order_mul) % (unsigned long long)B.nrays);
+}
 
 __device__ __forceinline__ void srt_log_row(const SrtBatch& B, long long ray, int rowidx, const double row[SRT_ROW_DOUBLES], bool& dropped) {
   if (!B.log) return;  // summary-only run: nothing is recorded, nothing is dropped
@@ -74,6 +83,7 @@ __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_THREAD_MIN_BLOCKS) srt_
         if (slot >= B.nrays) {
           exhausted = true;
         } else {
+          slot = srt_queue_ray(B, slot);
           ray = slot;
           // coalesced SoA loads: neighbouring lanes hold neighbouring rays
           double pos0[3] = {B.rays[0 * B.nrays + slot], B.rays[1 * B.nrays + slot], B.rays[2 * B.nrays + slot]};

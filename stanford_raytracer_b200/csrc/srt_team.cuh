@@ -63,6 +63,11 @@ __device__ __forceinline__ void team_dfdk_n(const double k[3], double w, int axi
   dk_axis = dk;
 }
 
+// compaction scratch: 24 eight-byte words per lane slot, blockDim/2 lane slots (dynamic shared memory)
+#define SRT_PACK_WORDS 24
+extern __shared__ unsigned long long srt_pack_smem[];
+__shared__ int srt_pack_count;
+
 template <int DENS, int USE_IGRF, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_constant__ SrtRunParams P, const __grid_constant__ SrtBatch B) {
   const unsigned full = 0xffffffffu;
@@ -99,7 +104,8 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
   double e1c = 0.0, e2c = 0.0;
 
   unsigned sync_iter = 0;
-  (void)sync_iter;
+  int cap_teams = (int)(blockDim.x >> 3);  // team slots of this block that may hold a live ray
+  (void)sync_iter; (void)cap_teams;
   for (;;) {
     // ================= refill: idle teams take the next ray; one atomic per warp
     const bool want = (phase == SRT_PH_IDLE) && !exhausted;
@@ -115,6 +121,7 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
         if (slot >= B.nrays) {
           exhausted = true;
         } else {
+          slot = srt_queue_ray(B, slot);
           double pos0[3] = {B.rays[0 * B.nrays + slot], B.rays[1 * B.nrays + slot], B.rays[2 * B.nrays + slot]};
           double dir0[3] = {B.rays[3 * B.nrays + slot], B.rays[4 * B.nrays + slot], B.rays[5 * B.nrays + slot]};
           double w0 = B.rays[6 * B.nrays + slot];
@@ -146,14 +153,64 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
     }
 #if defined(SRT_TEAM_BLOCK_SYNC)
     // block-synchronous rounds: the warps of a block walk the round's code in phase and share instruction lines
-#if defined(SRT_TEAM_SYNC_EVERY)
-    if ((++sync_iter % SRT_TEAM_SYNC_EVERY) == 0)
-#endif
-    if (__syncthreads_or(phase != SRT_PH_IDLE ? 1 : 0) == 0) break;
+    const int live = __syncthreads_count((phase != SRT_PH_IDLE && r == 0) ? 1 : 0);  // live teams of this block
+    if (live == 0) break;
+    // ---- compaction.  Once the ray queue is empty, finished rays leave holes: a block whose few live teams are
+    // spread over all its warps still issues every warp.  When at most half of the team slots in use are live, the
+    // live teams are re-packed into the lowest warps through shared memory (pure data movement: results unchanged);
+    // the emptied warps then only attend the barrier.  Config 2 spends most of its time in this regime.
+    if ((++sync_iter & 31u) == 0u && live * 2 <= cap_teams && cap_teams > 4) {
+      if (__syncthreads_or(exhausted ? 1 : 0)) {
+        unsigned long long* pk = srt_pack_smem;
+        const int nslots = (int)(blockDim.x >> 1);  // lane slots available: half a block
+        if (threadIdx.x == 0) srt_pack_count = 0;
+        __syncthreads();
+        if (phase != SRT_PH_IDLE) {
+          int idx = 0;
+          if (r == 0) idx = atomicAdd(&srt_pack_count, 1);
+          idx = __shfl_sync(T.tmask, idx, T.tbase);
+          const int o = idx * 8 + r;
+          const double dv[20] = {w, wl, t, dt, dfdw_rec, vg[0], vg[1], vg[2], xc, dfdk_c, rhs1c, kk1, kk2, kk3, kk4, kk5, kk6, tmpc, e1c, e2c};
+#pragma unroll
+          for (int i = 0; i < 20; ++i) pk[i * nslots + o] = (unsigned long long)__double_as_longlong(dv[i]);
+          pk[20 * nslots + o] = (unsigned long long)slot;
+          const unsigned flags = (dropped ? 1u : 0u) | (attempt_start ? 2u : 0u) | (finish_now ? 4u : 0u) | (cone_exit ? 8u : 0u) |
+                                 ((unsigned)lastrefinedown << 4) | ((unsigned)phase << 8) | ((unsigned)stage << 12) | ((unsigned)stopcond << 16);
+          pk[21 * nslots + o] = (unsigned long long)flags | ((unsigned long long)(unsigned)nstep << 32);
+          pk[22 * nslots + o] = (unsigned long long)nrej | ((unsigned long long)ncone << 32);
+          pk[23 * nslots + o] = (unsigned long long)nlog;
+        }
+        __syncthreads();
+        const int nlive = srt_pack_count;
+        if ((int)(threadIdx.x >> 3) < nlive) {
+          const int o = (int)threadIdx.x;  // team (threadIdx.x >> 3), role r
+          double dv[20];
+#pragma unroll
+          for (int i = 0; i < 20; ++i) dv[i] = __longlong_as_double((long long)pk[i * nslots + o]);
+          w = dv[0]; wl = dv[1]; t = dv[2]; dt = dv[3]; dfdw_rec = dv[4]; vg[0] = dv[5]; vg[1] = dv[6]; vg[2] = dv[7];
+          xc = dv[8]; dfdk_c = dv[9]; rhs1c = dv[10]; kk1 = dv[11]; kk2 = dv[12]; kk3 = dv[13]; kk4 = dv[14]; kk5 = dv[15]; kk6 = dv[16];
+          tmpc = dv[17]; e1c = dv[18]; e2c = dv[19];
+          slot = (long long)pk[20 * nslots + o];
+          const unsigned long long f = pk[21 * nslots + o];
+          const unsigned flags = (unsigned)f;
+          dropped = flags & 1u; attempt_start = flags & 2u; finish_now = flags & 4u; cone_exit = (flags >> 3) & 1u;
+          lastrefinedown = (int)((flags >> 4) & 0xfu); phase = (int)((flags >> 8) & 0xfu); stage = (int)((flags >> 12) & 0xfu);
+          stopcond = (int)((flags >> 16) & 0xfu);
+          nstep = (int)(unsigned)(f >> 32);
+          const unsigned long long g = pk[22 * nslots + o];
+          nrej = (unsigned)g; ncone = (unsigned)(g >> 32);
+          nlog = (unsigned)pk[23 * nslots + o];
+        } else {
+          phase = SRT_PH_IDLE;
+          exhausted = true;
+        }
+        cap_teams = (nlive + 3) & ~3;  // whole warps
+        __syncthreads();
+      }
+    }
 #else
     if (__ballot_sync(full, phase != SRT_PH_IDLE) == 0u) break;
 #endif
-
     if (phase != SRT_PH_IDLE) {
       // ================= top of an attempt: raytracer.f95:749-763
       if (attempt_start) {

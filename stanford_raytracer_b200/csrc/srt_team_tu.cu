@@ -31,15 +31,19 @@ static team_kernel_t pick_team(const SrtModel& M, int block) { return block > 51
 // block size for a batch: the largest power of two <= 1024 that still gives every SM at least one block
 int srt_team_block_threads(long long nrays, int num_sms) {
   long long lanes_per_sm = (nrays * 8) / (num_sms > 0 ? num_sms : 1);
-  int block = 64;
+  int block = 128;
   while (block * 2 <= 1024 && block * 2 <= lanes_per_sm) block *= 2;
   const char* env = getenv("SRT_TEAM_BLOCK");  // test / tuning hook
   if (env && atoi(env) >= 32 && atoi(env) <= 1024) block = atoi(env) / 32 * 32;
   return block;
 }
 
+static size_t team_smem_bytes(int block) { return (size_t)SRT_PACK_WORDS * 8 * (size_t)(block / 2); }
+
 cudaError_t srt_team_occupancy(const SrtModel& M, int block, int* blocks_per_sm) {
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, pick_team(M, block), block, 0);
+  cudaError_t e = cudaFuncSetAttribute(pick_team(M, block), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)team_smem_bytes(1024));
+  if (e != cudaSuccess) return e;
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, pick_team(M, block), block, team_smem_bytes(block));
 }
 
 cudaError_t srt_team_attributes(const SrtModel& M, int block, cudaFuncAttributes* fa) { return cudaFuncGetAttributes(fa, pick_team(M, block)); }
@@ -47,6 +51,8 @@ cudaError_t srt_team_attributes(const SrtModel& M, int block, cudaFuncAttributes
 cudaError_t srt_team_launch(const SrtModel& M, const SrtRunParams& P, const SrtBatch& B, int block, int grid, cudaStream_t stream) {
   cudaError_t e = cudaMemcpyToSymbolAsync(c_srt_model, &M, sizeof(SrtModel), 0, cudaMemcpyHostToDevice, stream);
   if (e != cudaSuccess) return e;
-  pick_team(M, block)<<<grid, block, 0, stream>>>(P, B);
+  e = cudaFuncSetAttribute(pick_team(M, block), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)team_smem_bytes(1024));
+  if (e != cudaSuccess) return e;
+  pick_team(M, block)<<<grid, block, team_smem_bytes(block), stream>>>(P, B);
   return cudaGetLastError();
 }
