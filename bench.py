@@ -21,6 +21,7 @@ roofline: FP64 (non-tensor) pipe.  achieved = algorithmic flop-equivalents (SURV
 import argparse
 import json
 import os
+import tempfile
 import subprocess
 import sys
 import threading
@@ -50,7 +51,7 @@ WORKLOADS = {
            "C4: 1M-ray launch grid (100 freq x 1000 lat x 10 lon), Ngo density + dipole B, adaptive RK45, per GPU"),
 }
 R_E = 6371.2e3
-_GRID_CACHE = os.path.join(ROOT, "gpurun_out", "bench_grid80.txt")
+_GRID_CACHE = os.path.join(tempfile.gettempdir(), "srt_bench_grid80.txt")  # ~50 MB of text: kept out of the repo tree
 
 
 def workload(rank, name="c2"):
@@ -164,6 +165,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (supplementary workloads whose sweep takes minutes)")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="c2 is the bench line; c3/c4 are the other BASELINE configs")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -252,26 +254,28 @@ def main():
     value = total_accepted / (kernel_ms_max * 1e-3)
 
     # ---- end to end through the C ABI with host buffers
-    e2e_steps = max(1, min(args.steps, 3))
-    res = srt.raytracer_run(model, pos0, dir0.copy(), w0, outputper=outputper, **params)  # warm-up (allocations)
-    d2h = res.total_rows * 160 + nrays * (srt.SUMMARY_WORDS * 8 + 4 + 56) + 64
-    h2d = nrays * 56 + nrays * 8
-    res.close()
-    barrier()
-    t0 = time.perf_counter()
-    e2e_acc = 0
-    for _ in range(e2e_steps):
-        res = srt.raytracer_run(model, pos0, dir0.copy(), w0, outputper=outputper, **params)
-        e2e_acc += res.accepted_steps
+    e2e_value, h2d, d2h = None, 0, 0
+    if not args.no_e2e:
+        e2e_steps = max(1, min(args.steps, 3))
+        res = srt.raytracer_run(model, pos0, dir0.copy(), w0, outputper=outputper, **params)  # warm-up (allocations)
+        d2h = res.total_rows * 160 + nrays * (srt.SUMMARY_WORDS * 8 + 4 + 56) + 64
+        h2d = nrays * 56 + nrays * 8
         res.close()
-    torch.cuda.synchronize()
-    t_e2e = time.perf_counter() - t0
-    t_e = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
-    a_e = torch.tensor([float(e2e_acc)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
-        dist.all_reduce(a_e)
-    e2e_value = float(a_e.item()) / float(t_e.item())
+        barrier()
+        t0 = time.perf_counter()
+        e2e_acc = 0
+        for _ in range(e2e_steps):
+            res = srt.raytracer_run(model, pos0, dir0.copy(), w0, outputper=outputper, **params)
+            e2e_acc += res.accepted_steps
+            res.close()
+        torch.cuda.synchronize()
+        t_e2e = time.perf_counter() - t0
+        t_e = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
+        a_e = torch.tensor([float(e2e_acc)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+            dist.all_reduce(a_e)
+        e2e_value = float(a_e.item()) / float(t_e.item())
 
     # ---- roofline of the dominant kernel (srt_trace_kernel): FP64 pipe
     peak_fma = srt.fp64_peak(True) / 1e3   # TFLOP/s
@@ -289,7 +293,7 @@ def main():
     hbm_ach = (rows_per_step * ROW_BYTES + nrays * (56 + srt.SUMMARY_WORDS * 8)) / avg_launch_s / 1e9
     traffic = None
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r1b_traffic.json")))
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1j_traffic.json")))
         if tj.get("workload") == wl and model.kernel_info(nrays)["mode"] == "team8":
             traffic = tj["dram_bytes_per_launch"]  # bytes per launch of this kernel on this workload, from the committed ncu pass
     except Exception:

@@ -156,6 +156,7 @@ unsigned long long ray_order_mul(long long nrays) {
 int launch_trace(srt_model* m, const SrtRunParams& P, const SrtBatch& B0, cudaStream_t stream) {
   SrtBatch B = B0;
   B.order_mul = ray_order_mul(B.nrays);
+  { const char* e = getenv("SRT_TEAM_COMPACT"); B.compact = (e && atoi(e) == 0) ? 0 : 1; }
   int mode, block, grid;
   int rc = launch_config(m, B.nrays, &mode, &block, &grid, nullptr);
   if (rc) return rc;

@@ -33,8 +33,9 @@ struct SrtBatch {
   double* log;                      // [capacity][SRT_LOG_WORDS]
   unsigned long long log_capacity;
   double* summary;                  // [nrays][SRT_SUMMARY_WORDS]
-  unsigned long long* counters;     // [0] log rows, [1] accepted steps, [2] attempts, [3] dropped rays, [4] ray queue head
+  unsigned long long* counters;     // [0] log rows, [1] accepted steps, [2] attempts, [3] dropped rays, [4] ray queue head, team kernel: [5] re-packs, [6] sum and [7] max over blocks of rounds
   unsigned* nlogged;                // optional [nrays]: rows this ray put in the log
+  int compact;                      // team kernel: re-pack live teams once the queue is empty
   unsigned long long order_mul;     // queue position q is ray (q * order_mul) mod nrays; coprime to nrays (1 = input order)
 };
 

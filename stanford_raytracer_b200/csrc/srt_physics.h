@@ -363,7 +363,7 @@ SRT_HDN void srt_dFdk(const double k[3], double w, const SrtPlasmaDerived& d, co
   const double del = 1.0e-8;
   double n0[3];
 #pragma unroll
-  for (int j = 0; j < 3; ++j) n0[j] = k[j] * C / w;
+  for (int j = 0; j < 3; ++j) n0[j] = srt_div(k[j] * C, w);
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
     double dd = srt_fd_step(del, k[i]);
@@ -371,7 +371,7 @@ SRT_HDN void srt_dFdk(const double k[3], double w, const SrtPlasmaDerived& d, co
     double nn[3] = {n0[0], n0[1], n0[2]};
     np[i] = (k[i] + dd) * C / w;
     nn[i] = (k[i] - dd) * C / w;
-    out[i] = (srt_F(np, w, d, s) - srt_F(nn, w, d, s)) / dd / 2.0;
+    out[i] = srt_div(srt_F(np, w, d, s) - srt_F(nn, w, d, s), dd) / 2.0;
   }
 }
 
@@ -383,8 +383,8 @@ SRT_HDN double srt_dFdw(const double k[3], double w, const SrtPlasmaDerived& d) 
   double np[3], nn[3];
 #pragma unroll
   for (int j = 0; j < 3; ++j) {
-    np[j] = k[j] * C / wp;
-    nn[j] = k[j] * C / wm;
+    np[j] = srt_div(k[j] * C, wp);
+    nn[j] = srt_div(k[j] * C, wm);
   }
   SrtStix sp, sm;
   srt_stix(d, wp, sp);
@@ -412,7 +412,7 @@ SRT_HD void srt_dFdx(SrtModelRef MR, const double k[3], double w, const double x
   const double C = srt_c_light();
   double n[3];
 #pragma unroll
-  for (int j = 0; j < 3; ++j) n[j] = k[j] * C / w;
+  for (int j = 0; j < 3; ++j) n[j] = srt_div(k[j] * C, w);
 #pragma unroll 1
   for (int i = 0; i < 3; ++i) {
     double dd = srt_fd_step(M.del, x[i]);
@@ -421,7 +421,7 @@ SRT_HD void srt_dFdx(SrtModelRef MR, const double k[3], double w, const double x
     xn[i] = x[i] - dd;
     double Fp = srt_F_at<DENS, USE_IGRF>(MR, xp, n, w);
     double Fn = srt_F_at<DENS, USE_IGRF>(MR, xn, n, w);
-    out[i] = (Fp - Fn) / dd / 2.0;
+    out[i] = srt_div(Fp - Fn, dd) / 2.0;
   }
 }
 
@@ -451,9 +451,9 @@ SRT_HDN void srt_evalrhs(SrtModelRef MR, const double x[3], const double k[3], d
   double dfdw = srt_dFdw(k, w, c.d);
   srt_dFdx<DENS, USE_IGRF>(MR, k, w, x, dfdx);
 #pragma unroll
-  for (int i = 0; i < 3; ++i) rhs[i] = -(dfdk[i] / dfdw);
+  for (int i = 0; i < 3; ++i) rhs[i] = -srt_div(dfdk[i], dfdw);
 #pragma unroll
-  for (int i = 0; i < 3; ++i) rhs[3 + i] = dfdx[i] / dfdw;
+  for (int i = 0; i < 3; ++i) rhs[3 + i] = srt_div(dfdx[i], dfdw);
 }
 
 // ------------------------------------------------------------------ root solve + handedness
@@ -464,15 +464,15 @@ SRT_HD SrtCplx srt_cdiv(SrtCplx a, SrtCplx b) {
   // Smith's algorithm, the order GCC emits for Fortran complex division
   SrtCplx r;
   if (srt_fabs(b.re) < srt_fabs(b.im)) {
-    double ratio = b.re / b.im;
+    double ratio = srt_div(b.re, b.im);
     double div = (b.re * ratio) + b.im;
-    r.re = ((a.re * ratio) + a.im) / div;
-    r.im = ((a.im * ratio) - a.re) / div;
+    r.re = srt_div((a.re * ratio) + a.im, div);
+    r.im = srt_div((a.im * ratio) - a.re, div);
   } else {
-    double ratio = b.im / b.re;
+    double ratio = srt_div(b.im, b.re);
     double div = (b.im * ratio) + b.re;
-    r.re = ((a.im * ratio) + a.re) / div;
-    r.im = (a.im - (a.re * ratio)) / div;
+    r.re = srt_div((a.im * ratio) + a.re, div);
+    r.im = srt_div(a.im - (a.re * ratio), div);
   }
   return r;
 }
@@ -579,7 +579,7 @@ SRT_HDN SrtCplx srt_solve_root(const double k[3], double w, const SrtPlasmaDeriv
   // k1 = w*n1/C, k2 = w*n2/C; swapped when root 1 is the right-handed mode
   bool want_n1 = (root == 1) ? !swap : swap;
   SrtCplx n = want_n1 ? n1 : n2;
-  SrtCplx kk = {w * n.re / C, w * n.im / C};
+  SrtCplx kk = {w * n.re / C, srt_div(w * n.im, C)};
   return kk;
 }
 
@@ -615,16 +615,16 @@ SRT_HDN void srt_fill_row(const SrtRayState& st, const SrtPlasma& pl, bool propa
   const double C = srt_c_light();
   double n[3];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) n[i] = st.k[i] * C / st.w;
+  for (int i = 0; i < 3; ++i) n[i] = srt_div(st.k[i] * C, st.w);
   row[0] = st.t;
 #pragma unroll
   for (int i = 0; i < 3; ++i) row[1 + i] = st.x[i];
   if (propagating) {
     double nn = srt_dot3(n, n);
 #pragma unroll
-    for (int i = 0; i < 3; ++i) row[4 + i] = n[i] / nn;
+    for (int i = 0; i < 3; ++i) row[4 + i] = srt_div(n[i], nn);
 #pragma unroll
-    for (int i = 0; i < 3; ++i) row[7 + i] = -(st.dfdk[i] / st.dfdw) / C;
+    for (int i = 0; i < 3; ++i) row[7 + i] = -srt_div(srt_div(st.dfdk[i], st.dfdw), C);
   } else {
 #pragma unroll
     for (int i = 0; i < 3; ++i) { row[4 + i] = 0.0; row[7 + i] = 0.0; }
@@ -691,7 +691,7 @@ SRT_HDN void srt_ray_init(SrtModelRef MR, const SrtRunParams& P, const double po
   const double C = srt_c_light();
   double n[3];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) n[i] = st.k[i] * C / w0;
+  for (int i = 0; i < 3; ++i) n[i] = srt_div(st.k[i] * C, w0);
   bool prop = srt_dot3(n, n) > 0;
   srt_fill_row(st, c.pl, prop, row);
 #pragma unroll

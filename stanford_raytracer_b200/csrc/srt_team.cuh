@@ -53,7 +53,7 @@ __device__ __forceinline__ void team_bcast_derived(const SrtTeamCtx& T, const Sr
 __device__ __forceinline__ void team_dfdk_n(const double k[3], double w, int axis, int minus, double n[3], double& dk_axis) {
   const double C = srt_c_light();
 #pragma unroll
-  for (int j = 0; j < 3; ++j) n[j] = k[j] * C / w;
+  for (int j = 0; j < 3; ++j) n[j] = srt_div(k[j] * C, w);
   double dk = srt_fd_step(1.0e-8, axis == 0 ? k[0] : (axis == 1 ? k[1] : k[2]));
   double kc = axis == 0 ? k[0] : (axis == 1 ? k[1] : k[2]);
   double v = (minus ? (kc - dk) : (kc + dk)) * C / w;
@@ -159,11 +159,11 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
     // spread over all its warps still issues every warp.  When at most half of the team slots in use are live, the
     // live teams are re-packed into the lowest warps through shared memory (pure data movement: results unchanged);
     // the emptied warps then only attend the barrier.  Config 2 spends most of its time in this regime.
-    if ((++sync_iter & 31u) == 0u && live * 2 <= cap_teams && cap_teams > 4) {
+    if ((++sync_iter & 31u) == 0u && live * 2 <= cap_teams && cap_teams > 4 && B.compact) {
       if (__syncthreads_or(exhausted ? 1 : 0)) {
         unsigned long long* pk = srt_pack_smem;
         const int nslots = (int)(blockDim.x >> 1);  // lane slots available: half a block
-        if (threadIdx.x == 0) srt_pack_count = 0;
+        if (threadIdx.x == 0) { srt_pack_count = 0; atomicAdd(&B.counters[5], 1ull); }
         __syncthreads();
         if (phase != SRT_PH_IDLE) {
           int idx = 0;
@@ -290,13 +290,13 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
         // ---- stage 1: dF/dx at the current point; dF/dk, dF/dw are the recorded ones
         double n[3];
 #pragma unroll
-        for (int j = 0; j < 3; ++j) n[j] = y[3 + j] * C / w;
+        for (int j = 0; j < 3; ++j) n[j] = srt_div(y[3 + j] * C, w);
         const double FA = srt_F(n, w, pd, sx);
         const int j2 = 2 * (comp % 3);
         const double Fp = team_get(T, FA, j2), Fn = team_get(T, FA, j2 + 1);
         const double ddx = team_get(T, dx_axis, j2);
-        if (comp < 3) rhs1c = -(dfdk_c / dfdw_rec);
-        else rhs1c = ((Fp - Fn) / ddx / 2.0) / dfdw_rec;
+        if (comp < 3) rhs1c = -srt_div(dfdk_c, dfdw_rec);
+        else rhs1c = srt_div(srt_div(Fp - Fn, ddx) / 2.0, dfdw_rec);
         kk1 = dt * rhs1c;
         tmpc = adaptive ? xc + (SRT_A21 * kk1) : xc + 1.0 / 2.0 * kk1;
         stage = 2;
@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
         // ---- raytracer_evalrhs at y (raytracer.f95:282-314)
         double nA[3];
 #pragma unroll
-        for (int j = 0; j < 3; ++j) nA[j] = y[3 + j] * C / wr;  // lanes 0-5: k*C/w; 6,7: k*c/(w+-d)
+        for (int j = 0; j < 3; ++j) nA[j] = srt_div(y[3 + j] * C, wr);  // lanes 0-5: k*C/w; 6,7: k*c/(w+-d)
         const double FA = srt_F(nA, wr, pd, sx);
         SrtPlasmaDerived pc;
         team_bcast_derived(T, pd, 6, pc);
@@ -320,8 +320,8 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
         const double FBp = team_get(T, FB, j2), FBn = team_get(T, FB, j2 + 1);
         const double ddx = team_get(T, dx_axis, j2), ddk = team_get(T, dk_axis, j2);
         double rhsc;
-        if (comp < 3) rhsc = -(((FBp - FBn) / ddk / 2.0) / dfdw);
-        else rhsc = ((FAp - FAn) / ddx / 2.0) / dfdw;
+        if (comp < 3) rhsc = -srt_div(srt_div(FBp - FBn, ddk) / 2.0, dfdw);
+        else rhsc = srt_div(srt_div(FAp - FAn, ddx) / 2.0, dfdw);
         const double kk = dt * rhsc;
         if (adaptive) {
           if (stage == 2) { kk2 = kk; tmpc = xc + (SRT_A31 * kk1 + SRT_A32 * kk2); }
@@ -356,6 +356,7 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
     my_attempts += __shfl_down_sync(full, my_attempts, o);
   }
   if (lane == 0) {
+    if (threadIdx.x == 0) { atomicAdd(&B.counters[6], (unsigned long long)sync_iter); atomicMax(&B.counters[7], (unsigned long long)sync_iter); }
     atomicAdd(&B.counters[1], my_accepted);
     atomicAdd(&B.counters[2], my_attempts);
   }

@@ -12,7 +12,7 @@
           for (int i = 0; i < 3; ++i) sa = sa + srt_fabs(e1[3 + i] - e2[3 + i]);
 #pragma unroll
           for (int i = 0; i < 3; ++i) sb = sb + srt_fabs(e2[3 + i]);
-          double err = sa / sb;
+          double err = srt_div(sa, sb);
           if (wl != 0.0) {
             const int set = r >> 2, q = r & 3;
             const double* kset = set ? (e2 + 3) : (e1 + 3);
@@ -29,16 +29,16 @@
 #pragma unroll
             for (int s2 = 0; s2 < 2; ++s2) {
               const double* ks = s2 ? (e2 + 3) : (e1 + 3);
-              g[s2][0] = (team_get(T, F1, s2 * 4 + 0) - team_get(T, F1, s2 * 4 + 1)) / srt_fd_step(1.0e-8, ks[0]) / 2.0;
-              g[s2][1] = (team_get(T, F1, s2 * 4 + 2) - team_get(T, F1, s2 * 4 + 3)) / srt_fd_step(1.0e-8, ks[1]) / 2.0;
-              g[s2][2] = (team_get(T, F2, s2 * 4 + 0) - team_get(T, F2, s2 * 4 + 1)) / srt_fd_step(1.0e-8, ks[2]) / 2.0;
+              g[s2][0] = srt_div(team_get(T, F1, s2 * 4 + 0) - team_get(T, F1, s2 * 4 + 1), srt_fd_step(1.0e-8, ks[0])) / 2.0;
+              g[s2][1] = srt_div(team_get(T, F1, s2 * 4 + 2) - team_get(T, F1, s2 * 4 + 3), srt_fd_step(1.0e-8, ks[1])) / 2.0;
+              g[s2][2] = srt_div(team_get(T, F2, s2 * 4 + 0) - team_get(T, F2, s2 * 4 + 1), srt_fd_step(1.0e-8, ks[2])) / 2.0;
             }
             double sc2 = 0.0, sd2 = 0.0;
 #pragma unroll
             for (int i = 0; i < 3; ++i) sc2 = sc2 + srt_fabs(g[0][i] - g[1][i]);
 #pragma unroll
             for (int i = 0; i < 3; ++i) sd2 = sd2 + srt_fabs(g[1][i]);
-            const double eg = sc2 / sd2;
+            const double eg = srt_div(sc2, sd2);
             if (eg > err || err != err) err = eg;  // MAX() as gfortran <= 8 expands it
           } else {
             if (err != err) err = srt_nan();  // Q1
@@ -101,26 +101,26 @@
             team_dfdk_n(knew, w, axis, minus, nT, dkT);
             if (r >= 6) {
 #pragma unroll
-              for (int j = 0; j < 3; ++j) nT[j] = knew[j] * C / wr2;
+              for (int j = 0; j < 3; ++j) nT[j] = srt_div(knew[j] * C, wr2);
             }
             const double FT = srt_F(nT, wr2, pc, s2);
             dfdw_rec = (team_get(T, FT, 6) - team_get(T, FT, 7)) / dw / 2.0;
             double dfdk_new[3];
 #pragma unroll
-            for (int i = 0; i < 3; ++i) dfdk_new[i] = (team_get(T, FT, 2 * i) - team_get(T, FT, 2 * i + 1)) / srt_fd_step(1.0e-8, knew[i]) / 2.0;
+            for (int i = 0; i < 3; ++i) dfdk_new[i] = srt_div(team_get(T, FT, 2 * i) - team_get(T, FT, 2 * i + 1), srt_fd_step(1.0e-8, knew[i])) / 2.0;
             dfdk_c = (comp % 3 == 0) ? dfdk_new[0] : (comp % 3 == 1) ? dfdk_new[1] : dfdk_new[2];
             // the recorded row (raytracer.f95:937-986)
             double row[SRT_ROW_DOUBLES];
             double nn[3];
 #pragma unroll
-            for (int i = 0; i < 3; ++i) nn[i] = knew[i] * C / w;
+            for (int i = 0; i < 3; ++i) nn[i] = srt_div(knew[i] * C, w);
             const double n2 = srt_dot3(nn, nn);
             row[0] = t;
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
               row[1 + i] = e2[i];
-              row[4 + i] = nn[i] / n2;
-              row[7 + i] = -(dfdk_new[i] / dfdw_rec) / C;
+              row[4 + i] = srt_div(nn[i], n2);
+              row[7 + i] = -srt_div(srt_div(dfdk_new[i], dfdw_rec), C);
               row[10 + i] = nn[i];
               row[13 + i] = team_get(T, pl.B0[i], 7);
             }
@@ -147,8 +147,8 @@
               const int j2 = 2 * (comp % 3);
               const double Fp = team_get(T, FA, j2), Fn = team_get(T, FA, j2 + 1);
               const double ddx = team_get(T, dx_axis, j2);
-              if (comp < 3) rhs1c = -(dfdk_c / dfdw_rec);
-              else rhs1c = ((Fp - Fn) / ddx / 2.0) / dfdw_rec;
+              if (comp < 3) rhs1c = -srt_div(dfdk_c, dfdw_rec);
+              else rhs1c = srt_div(srt_div(Fp - Fn, ddx) / 2.0, dfdw_rec);
             }
             phase = SRT_PH_STAGE;  // the attempt-start block sets kk1, tmpc and stage = 2 from rhs1c
             attempt_start = true;

@@ -16,6 +16,10 @@
 #include "srt_team.cuh"
 #include "srt_team_tu.h"
 
+#ifndef SRT_TEAM_MAXT_SMALL
+#define SRT_TEAM_MAXT_SMALL 512  // tuning hook: 256 gives the scarce-ray kernel 255 registers
+#endif
+
 typedef void (*team_kernel_t)(const SrtRunParams, const SrtBatch);
 
 // Two register budgets of the same kernel: MAXT = 512 (128 registers; best when rays are scarce and the latency of
@@ -26,7 +30,7 @@ static team_kernel_t pick_team_t(const SrtModel& M) {
   if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_NGO, 1, MAXT> : srt_trace_team_kernel<SRT_DENS_NGO, 0, MAXT>;
   return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_GRID, 1, MAXT> : srt_trace_team_kernel<SRT_DENS_GRID, 0, MAXT>;
 }
-static team_kernel_t pick_team(const SrtModel& M, int block) { return block > 512 ? pick_team_t<1024>(M) : pick_team_t<512>(M); }
+static team_kernel_t pick_team(const SrtModel& M, int block) { return block > SRT_TEAM_MAXT_SMALL ? pick_team_t<1024>(M) : pick_team_t<SRT_TEAM_MAXT_SMALL>(M); }
 
 // block size for a batch: the largest power of two <= 1024 that still gives every SM at least one block
 int srt_team_block_threads(long long nrays, int num_sms) {

@@ -12,6 +12,8 @@ rays0 = torch.from_numpy(np.ascontiguousarray(np.concatenate([pos0.T, dir0.T, w0
 summary = torch.zeros((n, 24), dtype=torch.float64, device="cuda")
 counters = torch.zeros(8, dtype=torch.int64, device="cuda")
 libs = [os.path.join("stanford_raytracer_b200", "libsrt.so")] + sorted(glob.glob("tools/_variants/*.so"))
+if os.environ.get("SRT_VARIANT_ONLY"):
+    libs = [p for p in libs if os.environ["SRT_VARIANT_ONLY"] in p]
 for path in libs:
     srt._lib = None
     srt._LIB_PATH = os.path.abspath(path)
