@@ -115,6 +115,24 @@ int srt_kernel_info(const srt_model* m, int64_t nrays, int* mode, int* regs, int
  * or DMUL+DADD pairs (fma=0) per thread on a full grid; returns achieved GFLOP/s in *gflops. */
 int srt_fp64_peak(int fma, int iters, double* gflops);
 
+/* ---- the driver's two text formats (host side, no GPU; srt_io.cpp) ------------------------------------------------
+ * Text of n doubles under the ES24.15E3 edit descriptor (driver:1197-1217), 24 characters each, no terminator. */
+int srt_format_es24(const double* v, int64_t n, char* out /*[24*n]*/);
+/* bytes of one output line for nspec species: 2 I10, 17 ES24, I10, 4*nspec ES24, newline */
+int64_t srt_row_text_bytes(int nspec);
+/* The lines the driver writes for one ray (driver:1197-1217): raynum (1-based), stopcond, the 16 leading columns of
+ * each row, w, nspec, qs, ms, Ns (row columns 16..), nus.  Returns the bytes written (nrows * srt_row_text_bytes). */
+int64_t srt_format_rows(int64_t raynum, int stopcond, const double* rows /*[nrows][SRT_ROW_DOUBLES]*/, int64_t nrows, double w, int nspec,
+                        const double* qs, const double* ms, const double* nus, char* out);
+/* The whole output file of a batch, byte for byte what the driver's loop writes (rays in input order, raynum counted
+ * from first_raynum).  nthreads workers format, the caller's thread writes; nthreads <= 0: all host cores. */
+int srt_result_write_text(const srt_result* r, const srt_model* m, const double* w0 /*[nrays]*/, const char* path, int64_t first_raynum,
+                          int append, int nthreads);
+/* inputraysfile (driver:1146): list-directed `pos0(3) dir0(3) w` per ray; stops at the first record that does not
+ * parse.  The three arrays are allocated by the library: release each with srt_free. */
+int srt_read_inputrays(const char* path, double** pos0 /*[n][3]*/, double** dir0 /*[n][3]*/, double** w0 /*[n]*/, int64_t* nrays);
+void srt_free(void* p);
+
 #ifdef __cplusplus
 }
 #endif

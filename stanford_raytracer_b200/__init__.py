@@ -74,6 +74,15 @@ def lib():
     L.srt_launch_count.restype = i64
     L.srt_kernel_info.argtypes = [vp, i64] + [C.POINTER(i)] * 6
     L.srt_fp64_peak.argtypes = [i, i, C.POINTER(d)]
+    L.srt_format_es24.argtypes = [vp, i64, vp]
+    L.srt_row_text_bytes.restype = i64
+    L.srt_row_text_bytes.argtypes = [i]
+    L.srt_format_rows.restype = i64
+    L.srt_format_rows.argtypes = [i64, i, vp, i64, d, i, vp, vp, vp, vp]
+    L.srt_result_write_text.argtypes = [vp, vp, vp, C.c_char_p, i64, i, i]
+    L.srt_read_inputrays.argtypes = [C.c_char_p, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(i64)]
+    L.srt_free.argtypes = [vp]
+    L.srt_free.restype = None
     _lib = L
     return L
 
@@ -197,6 +206,13 @@ class BatchResult:
         return RayOutput(self.rows(ray), int(self.stopcond[ray]), int(self.nsteps[ray]), L.srt_result_flags(self._h, ray), self.model,
                          float(self.w0[ray]), self.outputper)
 
+    def write_text(self, path, first_raynum=1, append=False, nthreads=0):
+        """The driver's output file for this batch (fortran/raytracer_driver.f95:1197-1217), written by the
+        library's multi-threaded formatter."""
+        w0 = np.ascontiguousarray(self.w0, dtype=np.float64)
+        _check(lib().srt_result_write_text(self._h, self.model._h, _ptr(w0), os.fsencode(path), int(first_raynum), int(bool(append)),
+                                           int(nthreads)), "srt_result_write_text")
+
     def close(self):
         if self._h:
             lib().srt_result_free(self._h)
@@ -207,6 +223,42 @@ class BatchResult:
             self.close()
         except Exception:
             pass
+
+
+def format_es24(values):
+    """ES24.15E3 text of an array of doubles (24 characters each) by the library's formatter."""
+    v = np.ascontiguousarray(values, dtype=np.float64).reshape(-1)
+    out = C.create_string_buffer(24 * len(v))
+    _check(lib().srt_format_es24(_ptr(v), len(v), out), "srt_format_es24")
+    raw = out.raw
+    return [raw[24 * k:24 * k + 24].decode() for k in range(len(v))]
+
+
+def format_rows(raynum, stopcond, rows, w, qs, ms, nus):
+    """The output lines of one ray as bytes (driver:1197-1217)."""
+    rows = np.ascontiguousarray(rows, dtype=np.float64).reshape(-1, ROW_DOUBLES)
+    qs, ms, nus = (np.ascontiguousarray(a, dtype=np.float64) for a in (qs, ms, nus))
+    L = lib()
+    out = C.create_string_buffer(int(L.srt_row_text_bytes(len(qs))) * len(rows) + 1)
+    n = L.srt_format_rows(int(raynum), int(stopcond), _ptr(rows), len(rows), float(w), len(qs), _ptr(qs), _ptr(ms), _ptr(nus), out)
+    if n < 0:
+        _check(int(n), "srt_format_rows")
+    return out.raw[:n]
+
+
+def read_inputrays(path):
+    """inputraysfile -> pos0[n][3], dir0[n][3], w[n] by the library's reader (driver:1146)."""
+    L = lib()
+    p, dd, w, n = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_int64()
+    _check(L.srt_read_inputrays(os.fsencode(path), C.byref(p), C.byref(dd), C.byref(w), C.byref(n)), "srt_read_inputrays")
+    try:
+        k = n.value
+        pos0 = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_double)), shape=(max(k, 1) * 3,))[:3 * k].reshape(k, 3).copy()
+        dir0 = np.ctypeslib.as_array(C.cast(dd, C.POINTER(C.c_double)), shape=(max(k, 1) * 3,))[:3 * k].reshape(k, 3).copy()
+        w0 = np.ctypeslib.as_array(C.cast(w, C.POINTER(C.c_double)), shape=(max(k, 1),))[:k].copy()
+    finally:
+        L.srt_free(p); L.srt_free(dd); L.srt_free(w)
+    return pos0, dir0, w0
 
 
 def raytracer_run(model, pos0, dir0, w0, dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep, outputper=1):
@@ -242,5 +294,4 @@ def launch_count():
     return lib().srt_launch_count()
 
 
-read_inputrays = rayfile.read_inputrays
-write_output = rayfile.write_output
+write_output = rayfile.write_output  # pure-Python writer (tests compare it with BatchResult.write_text)

@@ -47,14 +47,18 @@ def build(force=False, verbose=False):
         objs = [os.path.join(HERE, "srt_api.o"), os.path.join(HERE, "srt_team_tu.o")]
         procs = [subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-DSRT_INLINE_MATH", "-c", "-o", objs[0], os.path.join(CSRC, "srt_api.cu")]),
                  subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-DSRT_INLINE_MATH", "-c", "-o", objs[1], os.path.join(CSRC, "srt_team_tu.cu")])]
+        # host-only unit (text formats of the driver), plain g++
+        gxx = shutil.which("g++") or "g++"
+        objs.append(os.path.join(HERE, "srt_io.o"))
+        procs.append(subprocess.Popen([gxx, "-O2", "-std=c++17", "-fPIC", "-pthread", "-c", "-o", objs[2], os.path.join(CSRC, "srt_io.cpp")]))
         for pr in procs:
             if pr.wait() != 0:
                 raise subprocess.CalledProcessError(pr.returncode, pr.args)
-        subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB] + objs)
+        subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB] + objs + ["-lpthread"])
         for o in objs:
             os.remove(o)
     cli_src = os.path.join(CSRC, "srt_cli.cpp")
-    if os.path.exists(cli_src) and (force or _newer(CLI, srcs + [LIB])):
+    if os.path.exists(cli_src) and (force or _newer(CLI, [cli_src, srcs[0], LIB])):
         gxx = shutil.which("g++") or "g++"
         subprocess.check_call([gxx, "-O2", "-std=c++17", "-ffp-contract=off", "-o", CLI, cli_src, "-I", os.path.join(HERE, "..", "include"),
                                "-L", HERE, "-lsrt", "-Wl,-rpath,$ORIGIN"])

@@ -24,23 +24,27 @@ def _fortran_float(tok):
 
 
 def read_inputrays(path):
-    """Returns pos0[n][3], dir0[n][3], w[n]."""
+    """Returns pos0[n][3], dir0[n][3], w[n].  A READ takes seven items, continuing over records if it has to, and
+    drops what is left of the record it ends in; the first item that is not a number ends the file (iostat /= 0).
+    Pure-Python statement of the library's srt_read_inputrays (csrc/srt_io.cpp)."""
     vals = []
+    toks = []
+    stop = False
     with open(path) as f:
-        toks = []
         for line in f:
-            line = line.split("!")[0]
-            toks.extend(t for t in _SEP.split(line.strip()) if t)
-            while len(toks) >= 7:
-                try:
-                    vals.append([_fortran_float(t) for t in toks[:7]])
-                except ValueError:
+            for t in _SEP.split(line.strip()):
+                if not t:
+                    continue
+                toks.append(t)
+                if len(toks) == 7:
+                    try:
+                        vals.append([_fortran_float(x) for x in toks])
+                    except ValueError:
+                        stop = True
                     toks = []
-                    break
-                # a READ consumes whole records: anything left on the line is dropped
-                toks = []
-            else:
-                continue
+                    break  # rest of the record is dropped
+            if stop:
+                break
     a = np.array(vals, dtype=np.float64).reshape(-1, 7)
     return a[:, 0:3].copy(), a[:, 3:6].copy(), a[:, 6].copy()
 

@@ -34,3 +34,88 @@ def test_read_inputrays(tmp_path):
     assert pos0.shape == (3, 3)
     assert pos0[0, 0] == 1.0e7 and dir0[0, 2] == 1.0 and w[0] == 6.28e4
     assert pos0[1, 0] == 7.3712e6 and w[1] == 12566.37
+
+
+# ---- the library's formatter / reader (csrc/srt_io.cpp) against the Python statement above
+
+def _awkward_doubles():
+    rng = np.random.default_rng(12)
+    bits = rng.integers(0, 2 ** 63, 60000, dtype=np.int64).view(np.float64)          # whole exponent range, incl. subnormals / NaNs
+    typical = np.exp(rng.uniform(-60, 60, 60000)) * rng.choice([-1.0, 1.0], 60000)
+    ties = np.array([0.5, 1.5, 2.5, 9.5, 1.0000000000000005, 9.9999999999999995e99, 9.999999999999999e-100, 1e23, 8.5e-5, 5e-324,
+                     2.2250738585072014e-308, 1.7976931348623157e308, 0.0, -0.0, 1.0, -1.0, np.nan, np.inf, -np.inf, 123456789012345675.0])
+    return np.concatenate([bits, -bits[:2000], typical, ties])
+
+
+def test_native_es24_equals_python(built):
+    import stanford_raytracer_b200 as srt
+    v = _awkward_doubles()
+    got = srt.format_es24(v)
+    for x, g in zip(v, got):
+        assert g == rayfile.es24(x), (x, g)
+
+
+def test_native_rows_equal_python(built):
+    import stanford_raytracer_b200 as srt
+    rng = np.random.default_rng(13)
+    rows = np.exp(rng.uniform(-40, 40, (37, 20))) * rng.choice([-1.0, 1.0], (37, 20))
+    rows[5, 3] = np.nan
+    rows[6, 16] = 0.0
+    for nspec in (4, 2, 1):
+        qs, ms, nus = [-1.602e-19, 1.602e-19, 1.602e-19, 1.602e-19][:nspec], [9.1e-31, 1.67e-27, 6.7e-27, 2.7e-26][:nspec], [0.0] * nspec
+        want = "".join(rayfile.format_row(123456, 6, r, 31415.926, qs, ms, nus) for r in rows).encode()
+        got = srt.format_rows(123456, 6, rows, 31415.926, qs, ms, nus)
+        assert got == want
+        assert len(got) == 37 * srt.lib().srt_row_text_bytes(nspec)
+    # I10 overflow prints asterisks, as Fortran does
+    assert srt.format_rows(12345678901, 0, rows[:1], 1.0, [1.0], [1.0], [0.0])[:10] == b"*" * 10
+    assert srt.format_rows(1, 0, rows[:0], 1.0, [1.0], [1.0], [0.0]) == b""
+
+
+def test_native_reader_equals_python(built, tmp_path):
+    import stanford_raytracer_b200 as srt
+    p = tmp_path / "rays.txt"
+    p.write_text("1.0E007 0.0 0.0 0.0 0.0 1.0 6.28e4\n 7.3712d6, 0, 0, 0 0 0 12566.37 trailing ignored\n\n5 5 5\n 1 0 0 100 200 300\n"
+                 "\t1.5+3,2,3,4,5,6,7\r\nbad line stops reading\n9 9 9 0 0 1 7\n")
+    a = rayfile.read_inputrays(str(p))
+    b = srt.read_inputrays(str(p))
+    assert len(b[2]) == 4 and b[0][3, 0] == 1500.0 and b[2][2] == 100.0
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+    # a file written at full precision comes back bit for bit
+    rng = np.random.default_rng(14)
+    rays = rng.normal(size=(500, 7)) * 1e7
+    q = tmp_path / "many.txt"
+    q.write_text("".join(" ".join(repr(float(v)) for v in r) + "\n" for r in rays))
+    pos0, dir0, w0 = srt.read_inputrays(str(q))
+    assert np.array_equal(np.concatenate([pos0, dir0, w0[:, None]], axis=1), rays)
+    e = tmp_path / "empty.txt"
+    e.write_text("")
+    assert len(srt.read_inputrays(str(e))[2]) == 0
+    import pytest
+    with pytest.raises(srt.SrtError):
+        srt.read_inputrays(str(tmp_path / "missing.txt"))
+
+
+def test_cli_usage_and_errors(built, tmp_path):
+    """`raytracer`: usage without arguments (driver:75-177), loud failures for missing options, unsupported models and
+    -- in this container -- the missing GPU (no CPU path)."""
+    import os
+    import subprocess
+    import common
+    exe = os.path.join(common.ROOT, "stanford_raytracer_b200", "raytracer")
+    assert os.path.exists(exe)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0 and "--inputraysfile" in r.stdout and "--modelnum" in r.stdout
+    r = subprocess.run([exe, "--dt0=1e-3"], capture_output=True, text=True)
+    assert r.returncode == 2 and "--dtmax is required" in r.stderr
+    rays = tmp_path / "rays.txt"
+    rays.write_text("7.3712e6 0 0 0 0 0 12566.37\n")
+    common_args = ["--dt0=5e-4", "--dtmax=0.1", "--tmax=0.01", "--root=2", "--fixedstep=1", "--maxerr=5e-4", "--maxsteps=100", "--minalt=6.4712d6",
+                   "--inputraysfile=%s" % rays, "--outputfile=%s" % (tmp_path / "out.ray"), "--yearday=2010001", "--milliseconds_day=0"]
+    r = subprocess.run([exe] + common_args + ["--modelnum=2"], capture_output=True, text=True)
+    import torch
+    if not torch.cuda.is_available():
+        assert r.returncode == 1 and "CUDA" in r.stderr
+    else:
+        assert r.returncode == 3 and "not available on the GPU path" in r.stderr
