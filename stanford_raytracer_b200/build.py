@@ -30,7 +30,7 @@ def _newer(target, sources):
 
 
 def sources():
-    out = [os.path.join(HERE, "..", "include", "srt.h")]
+    out = [os.path.join(HERE, "..", "include", "srt.h"), os.path.abspath(__file__)]  # a flag change here rebuilds too
     for f in sorted(os.listdir(CSRC)):
         if f.endswith((".h", ".cu", ".cuh", ".inl", ".cpp")):
             out.append(os.path.join(CSRC, f))
@@ -46,7 +46,7 @@ def build(force=False, verbose=False):
         # team-of-8 kernel in two register budgets; elementary functions inlined in both; see srt_team_tu.cu
         objs = [os.path.join(HERE, "srt_api.o"), os.path.join(HERE, "srt_team_tu.o")]
         procs = [subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-DSRT_INLINE_MATH", "-c", "-o", objs[0], os.path.join(CSRC, "srt_api.cu")]),
-                 subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-DSRT_INLINE_MATH", "-c", "-o", objs[1], os.path.join(CSRC, "srt_team_tu.cu")])]
+                 subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-DSRT_INLINE_MATH", "-DSRT_INLINE_STIX", "-DSRT_INLINE_PLASMA", "-DSRT_INLINE_ACCEPT", "-c", "-o", objs[1], os.path.join(CSRC, "srt_team_tu.cu")])]
         # host-only unit (text formats of the driver), plain g++
         gxx = shutil.which("g++") or "g++"
         objs.append(os.path.join(HERE, "srt_io.o"))

@@ -97,7 +97,7 @@ SRT_HD void srt_rot_y(double c, double s, const double a[3], double b[3]) {
 // fortran/ngo_dens_model.f95:165-353 (`dens`), live outputs only: ani(1:4).
 // z1 = geocentric radius seen by the model [km], z2 = colatitude [rad],
 // latitu = latitude [deg] (used by the duct branches).
-SRT_HDN void srt_ngo_dens(const SrtNgo& g, double z1, double z2, double latitu, double ani[SRT_NSPEC]) {
+SRT_HDP void srt_ngo_dens(const SrtNgo& g, double z1, double z2, double latitu, double ani[SRT_NSPEC]) {
   double sinz2, cosz2;
   srt_sincos(z2, sinz2, cosz2);
   double sinz22 = sinz2 * sinz2;
@@ -220,7 +220,7 @@ SRT_HDN void srt_ngo_dens(const SrtNgo& g, double z1, double z2, double latitu, 
 // spherical_to_cartesian_vec (fortran/util.f95:126-142, matmul(transpose(A),p) with
 // the accumulator starting at 0).  p = cartesian_to_spherical(x); sph/cph, sth/cth
 // are sin/cos of p(3) (polar angle) and p(2) (azimuth).
-SRT_HDN void srt_dipole_sm(const double p[3], double sph, double cph, double sth, double cth, double B[3]) {
+SRT_HDP void srt_dipole_sm(const double p[3], double sph, double cph, double sth, double cth, double B[3]) {
   double Bo = .312 / 10000.0;
   double R = p[0] / SRT_R_E;
   double Bor3 = Bo * (srt_pow(R, -3.0));
@@ -272,7 +272,7 @@ SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT
 //   Ngo:  fortran/ngo_dens_model_adapter.f95:63-207
 //   grid: fortran/interp_dens_model_adapter.f95:148-269
 template <int DENS, int USE_IGRF>
-SRT_HDN void srt_plasma(SrtModelRef MR, const double x[3], SrtPlasma& o) {
+SRT_HDP void srt_plasma(SrtModelRef MR, const double x[3], SrtPlasma& o) {
   const SrtModel& M = MR.get();
   double p[3] = {0.0, 0.0, 0.0};
   double sph = 0.0, cph = 0.0, sth = 0.0, cth = 0.0;
@@ -305,7 +305,7 @@ SRT_HDN void srt_plasma(SrtModelRef MR, const double x[3], SrtPlasma& o) {
 // ------------------------------------------------------------------ Stix / dispersion
 // plasma-only parts of stix_parameters (raytracer.f95:92-93) and of the free-space
 // test (raytracer.f95:65)
-SRT_HDN void srt_plasma_derive(SrtModelRef MR, const SrtPlasma& pl, SrtPlasmaDerived& d) {
+SRT_HDS void srt_plasma_derive(SrtModelRef MR, const SrtPlasma& pl, SrtPlasmaDerived& d) {
   const SrtModel& M = MR.get();
   d.B0[0] = pl.B0[0]; d.B0[1] = pl.B0[1]; d.B0[2] = pl.B0[2];
   d.B0sq = srt_dot3(pl.B0, pl.B0);
@@ -321,7 +321,7 @@ SRT_HDN void srt_plasma_derive(SrtModelRef MR, const SrtPlasma& pl, SrtPlasmaDer
 }
 
 // stix_parameters, raytracer.f95:96-100
-SRT_HDN void srt_stix(const SrtPlasmaDerived& d, double w, SrtStix& s) {
+SRT_HDS void srt_stix(const SrtPlasmaDerived& d, double w, SrtStix& s) {
   double sr = 0.0, sl = 0.0, sp = 0.0;
 #pragma unroll
   for (int i = 0; i < SRT_NSPEC; ++i) sr = sr + d.wps2[i] / (w * (w + d.wcs[i]));
@@ -338,7 +338,7 @@ SRT_HDN void srt_stix(const SrtPlasmaDerived& d, double w, SrtStix& s) {
 }
 
 // dispersion_relation after the Stix parameters are known (raytracer.f95:50-68)
-SRT_HDN double srt_F(const double n[3], double w, const SrtPlasmaDerived& d, const SrtStix& s) {
+SRT_HDS double srt_F(const double n[3], double w, const SrtPlasmaDerived& d, const SrtStix& s) {
   double nmag2 = srt_dot3(n, n);
   double nb = srt_dot3(n, d.B0);
   double cos2phi = (nb * nb) / (nmag2 * d.B0sq);
@@ -491,7 +491,7 @@ SRT_HD SrtCplx srt_cmul(SrtCplx a, SrtCplx b) {
 // unit phase) with v the eigenvector of Mr whose eigenvalue is smallest in
 // magnitude, and the reference's angle has the sign of v1*v2.  Mr is diagonalised by
 // cyclic Jacobi rotations.
-SRT_HDN bool srt_is_right_handed(double n2, double phi_deg, double S, double D, double P) {
+SRT_HDE bool srt_is_right_handed(double n2, double phi_deg, double S, double D, double P) {
   double sphi, cphi;
   srt_sincos(phi_deg, sphi, cphi);
   double d0 = (double)(float)(S - n2 * (cphi * cphi));
@@ -556,7 +556,7 @@ SRT_HDN bool srt_is_right_handed(double n2, double phi_deg, double S, double D, 
 // solve_dispersion_relation (raytracer.f95:408-502) with the plasma at x (derived) and
 // the Stix set at (x, w) supplied.  Returns the complex root selected by `root`
 // (1: k1, else k2), i.e. what raytracer_run picks at :685-689 / :828-836.
-SRT_HDN SrtCplx srt_solve_root(const double k[3], double w, const SrtPlasmaDerived& d, const SrtStix& s, int root) {
+SRT_HDE SrtCplx srt_solve_root(const double k[3], double w, const SrtPlasmaDerived& d, const SrtStix& s, int root) {
   const double C = srt_c_light();
   double kb = srt_dot3(k, d.B0);
   double cos2phi = (kb * kb) / (srt_dot3(k, k) * d.B0sq);
@@ -611,7 +611,7 @@ struct SrtRayState {
 };
 
 // fills row[] for the current state (:710-741 and :937-986)
-SRT_HDN void srt_fill_row(const SrtRayState& st, const SrtPlasma& pl, bool propagating, double row[SRT_ROW_DOUBLES]) {
+SRT_HDE void srt_fill_row(const SrtRayState& st, const SrtPlasma& pl, bool propagating, double row[SRT_ROW_DOUBLES]) {
   const double C = srt_c_light();
   double n[3];
 #pragma unroll
