@@ -10,13 +10,16 @@
 // floored, as the driver does.  Options the reference leaves uninitialised when absent are required here.
 //
 // Additions (not in the reference): --device=N (CUDA device, default current), --threads=N (formatter threads,
-// default all cores), --batch=N (rays per srt_trace_batch call, default 1000000), --verbose=1 (timing to stderr).
+// default all cores), --batch=N (rays per srt_trace_batch call; default: as many as keep the worst-case
+// trajectory rows, maxsteps/outputper per ray, inside a quarter of the host's memory), --verbose=1 (timing to stderr).
 #include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
+
+#include <unistd.h>
 
 #include "srt.h"
 
@@ -128,7 +131,15 @@ int main(int argc, char** argv) {
   const int use_igrf = (int)std::floor(opt_real("use_igrf", 0.0));
   const int device = (int)std::floor(opt_real("device", -1.0));
   const int threads = (int)std::floor(opt_real("threads", 0.0));
-  const long long batch = (long long)std::floor(opt_real("batch", 1.0e6));
+  long long batch = (long long)std::floor(opt_real("batch", 0.0));
+  if (batch == 0) {
+    // rows come back to host memory before they are written: bound the worst case (every ray runs to maxsteps)
+    const double ram = (double)sysconf(_SC_PHYS_PAGES) * (double)sysconf(_SC_PAGE_SIZE);
+    const double per_ray = ((double)p.maxsteps / p.outputper + 2.0) * SRT_ROW_DOUBLES * sizeof(double);
+    batch = (long long)(0.25 * ram / per_ray);
+    if (batch < 1024) batch = 1024;
+    if (batch > 4000000) batch = 4000000;
+  }
   const bool verbose = opt_real("verbose", 0.0) != 0.0;
   if (batch < 1) die(2, "--batch must be >= 1");
 
