@@ -140,7 +140,7 @@ def run_reference(args):
     ol.build()
     pos0, dir0, w0, params, cfg = workload(0, "c2")
     threads = os.cpu_count() or 1
-    nsample = max(threads, 96)
+    nsample = max(threads, 256)  # ~12 s of CPU work per step on 16 cores
     for _ in range(args.warmup):
         cpu_reference_run(pos0, dir0, w0, params, cfg, max(threads, 8), threads)
     acc_total, t_total = 0, 0.0
@@ -201,8 +201,12 @@ def main():
     summary = torch.empty((nrays, srt.SUMMARY_WORDS), dtype=torch.float64, device=dev)
     counters = torch.zeros(8, dtype=torch.int64, device=dev)
     # size the trajectory log from a counting pass (no log attached: nothing recorded, nothing dropped)
+    t_count = time.perf_counter()
     srt.trace_batch_device(model, nrays, rays.data_ptr(), P, 0, 0, summary.data_ptr(), counters.data_ptr(), torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
+    if rank == 0:
+        print("bench: counting pass %.1f s, %d accepted steps, %d attempts" % (time.perf_counter() - t_count, int(counters[1].item()), int(counters[2].item())),
+              file=sys.stderr, flush=True)
     log_cap = int(counters[1].item()) // outputper + 2 * nrays + 1024
     log = torch.empty((log_cap, srt.LOG_WORDS), dtype=torch.float64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -310,7 +314,7 @@ def main():
         cpu = None
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            nsample = max(threads, 96)
+            nsample = max(threads, 256)  # ~12 s of CPU work on 16 cores
             if WORKLOADS[wl][4] == "grid":
                 nsample = threads
                 a, t = cpu_reference_run(pos0, dir0, w0, dict(params, maxsteps=300), _GRID_CACHE + ".%d" % local_rank, nsample, threads, "grid", 1)
