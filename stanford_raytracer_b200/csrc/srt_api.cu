@@ -157,6 +157,7 @@ int launch_trace(srt_model* m, const SrtRunParams& P, const SrtBatch& B0, cudaSt
   SrtBatch B = B0;
   B.order_mul = ray_order_mul(B.nrays);
   { const char* e = getenv("SRT_TEAM_COMPACT"); B.compact = (e && atoi(e) == 0) ? 0 : 1; }
+  { const char* e = getenv("SRT_TEAM_PHASE_ALIGN"); B.phase_align = (e && atoi(e) != 0) ? 1 : 0; }  // off until measured (open item)
   int mode, block, grid;
   int rc = launch_config(m, B.nrays, &mode, &block, &grid, nullptr);
   if (rc) return rc;

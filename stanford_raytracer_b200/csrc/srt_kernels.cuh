@@ -36,6 +36,7 @@ struct SrtBatch {
   unsigned long long* counters;     // [0] log rows, [1] accepted steps, [2] attempts, [3] dropped rays, [4] ray queue head, team kernel: [5] re-packs, [6] sum and [7] max over blocks of rounds
   unsigned* nlogged;                // optional [nrays]: rows this ray put in the log
   int compact;                      // team kernel: re-pack live teams once the queue is empty
+  int phase_align;                  // team kernel: idle teams refill only on the block's attempt boundary (srt_team.cuh)
   unsigned long long order_mul;     // queue position q is ray (q * order_mul) mod nrays; coprime to nrays (1 = input order)
 };
 

@@ -108,7 +108,18 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
   (void)sync_iter; (void)cap_teams;
   for (;;) {
     // ================= refill: idle teams take the next ray; one atomic per warp
-    const bool want = (phase == SRT_PH_IDLE) && !exhausted;
+#if defined(SRT_TEAM_BLOCK_SYNC)
+    // Phase alignment (B.phase_align, off by default): an attempt is `cyc` rounds (stages 2..6 + estimate; fixed step:
+    // stages 2..4 + estimate) and the first wave of a block starts at round 0, so every team's estimate round falls on
+    // a multiple of cyc for as long as no team joins in between.  A team that refills at another round would run its
+    // estimate branch while its warp neighbours run a stage branch, in every round from then on.  With the knob on,
+    // an idle team takes its next ray only at a multiple of cyc: its stage-1 stencil round coincides with the others'
+    // estimate round and the block stays in phase (at most cyc-1 idle rounds per ray).  Pure scheduling: no result changes.
+    const bool refill_round = !B.phase_align || (sync_iter % (adaptive ? 6u : 4u)) == 0u;
+#else
+    const bool refill_round = true;
+#endif
+    const bool want = (phase == SRT_PH_IDLE) && !exhausted && refill_round;
     const unsigned need = __ballot_sync(full, want && r == 0);
     if (need) {
       const int leader = __ffs(need) - 1;
@@ -153,7 +164,8 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
     }
 #if defined(SRT_TEAM_BLOCK_SYNC)
     // block-synchronous rounds: the warps of a block walk the round's code in phase and share instruction lines
-    const int live = __syncthreads_count((phase != SRT_PH_IDLE && r == 0) ? 1 : 0);  // live teams of this block
+    // live teams of this block; a team waiting for its refill round (phase alignment) still has the queue to look at
+    const int live = __syncthreads_count(((phase != SRT_PH_IDLE || (B.phase_align && !exhausted)) && r == 0) ? 1 : 0);
     if (live == 0) break;
     // ---- compaction.  Once the ray queue is empty, finished rays leave holes: a block whose few live teams are
     // spread over all its warps still issues every warp.  When at most half of the team slots in use are live, the

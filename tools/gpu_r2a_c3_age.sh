@@ -1,0 +1,23 @@
+#!/bin/bash
+# Round 2, first GPU call: the config-3 open item.  ~6 GPU-minutes.  Output: gpurun_out/r2a_c3_age.txt
+#   gpurun --timeout 900 -- 'bash tools/gpu_r2a_c3_age.sh'
+set -u
+mkdir -p gpurun_out
+out=gpurun_out/r2a_c3_age.txt
+: > $out
+run() { echo "## $*" >> $out; timeout 300 env "$@" >> $out 2>&1 || echo "FAILED rc=$?" >> $out; }
+# knob parity first (bit-identical results required before any timing counts)
+run SRT_X=0 python -m pytest tests/test_gpu_zz_phase_align.py -x -q
+# rate against age, default knobs
+for ms in 200 1000 4000; do run SRT_X=0 python tools/c3_age.py --maxsteps $ms; done
+# young rays with an old population's cell footprint
+run SRT_X=0 python tools/c3_age.py --maxsteps 200 --alts 1000,4000,9000,15000,21000
+# ingredients apart
+run SRT_X=0 python tools/c3_age.py --maxsteps 1000 --model ngo --igrf 1
+run SRT_X=0 python tools/c3_age.py --maxsteps 1000 --model grid --igrf 0
+# scheduling knobs
+run SRT_TEAM_PHASE_ALIGN=1 python tools/c3_age.py --maxsteps 1000
+run SRT_TEAM_BLOCK=512 python tools/c3_age.py --maxsteps 1000
+run SRT_TEAM_PHASE_ALIGN=1 SRT_TEAM_BLOCK=512 python tools/c3_age.py --maxsteps 1000
+run SRT_KERNEL=thread python tools/c3_age.py --maxsteps 1000
+tail -40 $out
