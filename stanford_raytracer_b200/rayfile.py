@@ -87,3 +87,32 @@ def write_output(path, batch, w=None):
             sc = int(batch.stopcond[r])
             for row in rows:
                 f.write(format_row(r + 1, sc, row, wr, batch.model.qs, batch.model.ms, batch.model.nus))
+
+
+def read_output(path):
+    """Reads an output file back (the consumer side of the driver's format: damping/src/wipp_fileutils.cpp:6-170,
+    damping/matlab/readrayoutput.m:24-47).  Returns {raynum: dict} in file order, each with w, stopcond, nspec (taken
+    from the ray's first line), qs[nspec], ms[nspec] (first line) and per recorded row time[n], pos/vprel/vgrel/n/B0
+    [n][3], Ns/nus[n][nspec].  The fields are fixed-width (i10, es24.15e3), so the line is cut by column and a value
+    that touches its neighbour (a four-digit exponent cannot occur, a 24-character negative number can) still parses."""
+    rays = {}
+    acc = {}
+    with open(path) as f:
+        for line in f:
+            line = line.rstrip("\n")
+            if not line.strip():
+                continue
+            raynum, stopcond = int(line[0:10]), int(line[10:20])
+            v = [_fortran_float(line[20 + 24 * i:44 + 24 * i]) for i in range(17)]
+            nspec = int(line[428:438])
+            tail = [_fortran_float(line[438 + 24 * i:462 + 24 * i]) for i in range(4 * nspec)]
+            if raynum not in rays:
+                rays[raynum] = dict(w=v[16], stopcond=stopcond, nspec=nspec, qs=np.array(tail[0:nspec]), ms=np.array(tail[nspec:2 * nspec]))
+                acc[raynum] = []
+            acc[raynum].append(v[0:16] + tail[2 * nspec:4 * nspec])
+    for raynum, rows in acc.items():
+        a = np.array(rows, dtype=np.float64)
+        ns = rays[raynum]["nspec"]
+        rays[raynum].update(time=a[:, 0], pos=a[:, 1:4], vprel=a[:, 4:7], vgrel=a[:, 7:10], n=a[:, 10:13], B0=a[:, 13:16],
+                            Ns=a[:, 16:16 + ns], nus=a[:, 16 + ns:16 + 2 * ns])
+    return rays

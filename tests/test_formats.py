@@ -119,3 +119,39 @@ def test_cli_usage_and_errors(built, tmp_path):
         assert r.returncode == 1 and "CUDA" in r.stderr
     else:
         assert r.returncode == 3 and "not available on the GPU path" in r.stderr
+
+
+def test_read_output_round_trip(tmp_path):
+    """The consumer side of the output format (damping/src/wipp_fileutils.cpp:6-170): what the writer puts is what
+    the reader returns, ray by ray, to the 16 digits of the text."""
+    from stanford_raytracer_b200 import rayfile
+    rng = np.random.default_rng(11)
+    qs = np.array([-1.602e-19, 1.602e-19, 1.602e-19, 1.602e-19])
+    ms = np.array([9.10938188e-31, 1.6726e-27, 6.6904e-27, 2.67616e-26])
+    nus = np.zeros(4)
+    p = tmp_path / "out.ray"
+    want = {}
+    with open(p, "w") as f:
+        for raynum, (nrows, sc, w) in enumerate([(3, 1, 2 * np.pi * 2000.0), (1, 2, 2 * np.pi * 200.0), (5, 0, 1.0e5)], start=1):
+            rows = rng.standard_normal((nrows, 20)) * 10.0 ** rng.integers(-12, 12, (nrows, 20))
+            rows[:, 1] = -np.abs(rows[:, 1])  # negative values fill all 24 columns of their field
+            want[raynum] = (rows, sc, w)
+            for row in rows:
+                f.write(rayfile.format_row(raynum, sc, row, w, qs, ms, nus))
+    got = rayfile.read_output(str(p))
+    assert list(got) == [1, 2, 3]
+    for raynum, (rows, sc, w) in want.items():
+        g = got[raynum]
+        assert g["stopcond"] == sc and g["nspec"] == 4
+        assert np.isclose(g["w"], w, rtol=1e-15, atol=0)
+        assert np.array_equal(g["qs"], qs) and np.allclose(g["ms"], ms, rtol=1e-15, atol=0)
+        back = np.concatenate([g["time"][:, None], g["pos"], g["vprel"], g["vgrel"], g["n"], g["B0"], g["Ns"]], axis=1)
+        assert back.shape == rows.shape
+        assert np.allclose(back, rows, rtol=1e-15, atol=0)
+        assert np.array_equal(g["nus"], np.zeros((len(rows), 4)))
+        # re-writing what was read gives the same bytes
+    text = "".join(rayfile.format_row(k, got[k]["stopcond"],
+                                      np.concatenate([[got[k]["time"][i]], got[k]["pos"][i], got[k]["vprel"][i], got[k]["vgrel"][i], got[k]["n"][i], got[k]["B0"][i], got[k]["Ns"][i]]),
+                                      got[k]["w"], got[k]["qs"], got[k]["ms"], got[k]["nus"][i])
+                   for k in got for i in range(len(got[k]["time"])))
+    assert text == p.read_text()
