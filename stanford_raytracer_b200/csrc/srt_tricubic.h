@@ -123,6 +123,10 @@ SRT_HDN double srt_tricubic_slow(const SrtGrid& g, int is0, int js0, int ks0, do
   return v;
 }
 
+#if defined(__CUDA_ARCH__) && defined(SRT_GRID_STAGE) && defined(SRT_TEAM_TU)
+extern __shared__ unsigned long long srt_stage_smem[];  // the team kernel's dynamic shared memory (srt_team.cuh)
+#endif
+
 // Ns(1:4) = exp(tricubic(log-density)) at x (SM, metres)
 SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT_NSPEC]) {
   const int is0 = srt_grid_locate(g.xs, g.nx, g.minx, g.delx, x[0]);
@@ -134,6 +138,54 @@ SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT
   if (inj) yil = (x[1] - g.ys[js0 - 1]) / g.dely;
   if (ink) zil = (x[2] - g.zs[ks0 - 1]) / g.delz;
   double v[SRT_NSPEC] = {0.0, 0.0, 0.0, 0.0};
+#if defined(__CUDA_ARCH__) && defined(SRT_GRID_STAGE) && defined(SRT_TEAM_TU)
+  // ---- Build variant (-DSRT_GRID_STAGE, team translation unit only; not in the default build until measured).
+  // The 8 lanes of a team evaluate points a finite-difference step apart, i.e. almost always in the same cell, and
+  // each of them walks the cell's whole 2 KiB record with its own 128 LDG.128.  Here the team fetches the record of
+  // the centre lane's cell together, one i-slab (64 doubles) at a time: 4 coalesced LDG.128 per lane and slab into a
+  // 528-byte shared-memory row per team (aliased onto the compaction scratch, which is only live between block
+  // barriers), then every lane of that cell reads the slab by broadcast.  Lanes in another cell (a stencil point
+  // across a cell face, est1 vs est2) or on the edge path fall through to the per-lane code below.  Same operands in
+  // the same order: same bits.  Every caller in this translation unit reaches this point with whole teams.
+  {
+    const int lane_ = threadIdx.x & 31, tbase_ = lane_ & ~7, r_ = lane_ & 7;
+    const unsigned tmask_ = 0xffu << tbase_;
+    const long long c_ = (ini && inj && ink && g.coef) ? (long long)((((size_t)(ks0 - 1) * (g.ny - 1) + (js0 - 1)) * (g.nx - 1) + (is0 - 1))) : -1ll;
+    const long long c0_ = __shfl_sync(tmask_, c_, tbase_ + 6);
+    if (c0_ >= 0) {  // team-uniform
+      double* stage = (double*)srt_stage_smem + (size_t)(threadIdx.x >> 3) * 66;  // 66: the 4 teams of a warp on distinct banks
+      const double2* src = (const double2*)(g.coef + (size_t)c0_ * 256);
+      double xp[4], yp[4], zp[4];
+      srt_powers3(xil, xp);
+      srt_powers3(yil, yp);
+      srt_powers3(zil, zp);
+#pragma unroll 1
+      for (int i = 0; i < 4; ++i) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) ((double2*)stage)[q * 8 + r_] = __ldg(src + i * 32 + q * 8 + r_);
+        __syncwarp(tmask_);
+        if (c_ == c0_) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const double2 a01 = ((const double2*)stage)[2 * (4 * j + k)];
+              const double2 a23 = ((const double2*)stage)[2 * (4 * j + k) + 1];
+              const double as[4] = {a01.x, a01.y, a23.x, a23.y};
+#pragma unroll
+              for (int s = 0; s < SRT_NSPEC; ++s) v[s] = v[s] + as[s] * xp[i] * yp[j] * zp[k];
+            }
+          }
+        }
+        __syncwarp(tmask_);
+      }
+    }
+    if (c0_ >= 0 && c_ == c0_) {
+      for (int s = 0; s < SRT_NSPEC; ++s) Ns[s] = (s < g.nspec) ? srt_exp(v[s]) : 0.0;
+      return;
+    }
+  }
+#endif
   if (ini && inj && ink && g.coef) {
     const double* a = g.coef + ((((size_t)(ks0 - 1) * (g.ny - 1) + (js0 - 1)) * (g.nx - 1) + (is0 - 1)) * 256);
     double xp[4], yp[4], zp[4];

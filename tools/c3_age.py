@@ -10,6 +10,8 @@ What separates the suspects:
     population's cell footprint): if the rate falls as with old rays, the loss is the coefficient-table working set;
   * --model ngo --igrf 1 keeps IGRF and drops the grid, --model grid --igrf 0 the other way round;
   * SRT_TEAM_PHASE_ALIGN=1 / SRT_TEAM_BLOCK=512 in the environment select the scheduling knobs;
+  * --lib tools/_variants/stage.so runs the -DSRT_GRID_STAGE build (team-cooperative fetch of the cell record through
+    shared memory, srt_tricubic.h); --save / --compare check that knobs and variants return the same bits;
   * --maxsteps 200 / 1000 / 4000 gives the rate against age.
 Product API only (no oracle); needs a GPU."""
 import argparse, os, sys, time
@@ -25,9 +27,14 @@ ap.add_argument("--igrf", type=int, default=1)
 ap.add_argument("--alts", default="1000", help="comma-separated launch altitudes in km, cycled over the rays")
 ap.add_argument("--nlon", type=int, default=10)
 ap.add_argument("--reps", type=int, default=2)
+ap.add_argument("--lib", default="", help="an alternative build of libsrt (tools/build_variant.sh -> tools/_variants/NAME.so)")
+ap.add_argument("--save", default="", help="write the per-ray summaries (last row, steps, stop code) to this .npy")
+ap.add_argument("--compare", default="", help="require the per-ray summaries to equal, bit for bit, those saved in this .npy")
 a = ap.parse_args()
 
 R_E = 6371.2e3
+if a.lib:
+    srt._LIB_PATH = os.path.abspath(a.lib)
 srt.init(0)
 ngo = srt.ngosetup(common.NGO_CFG, 2010001, 0, a.igrf, 0)
 if a.model == "grid":
@@ -64,9 +71,14 @@ c = counters.cpu().numpy()
 ms_ = e0.elapsed_time(e1)
 sc = summary[:, 21].cpu().numpy().astype(int)
 r = np.sqrt((summary[:, 1:4].cpu().numpy() ** 2).sum(axis=1)) / R_E
+same = ""
+if a.save:
+    np.save(a.save, summary.cpu().numpy())
+if a.compare:
+    same = "| summaries identical to %s: %s" % (a.compare, bool(np.array_equal(np.load(a.compare), summary.cpu().numpy(), equal_nan=True)))
 knobs = {k: os.environ[k] for k in ("SRT_TEAM_PHASE_ALIGN", "SRT_TEAM_BLOCK", "SRT_KERNEL", "SRT_TEAM_COMPACT") if k in os.environ}
 print("c3_age model", a.model, "igrf", a.igrf, "alts", a.alts, "n", n, "maxsteps", a.maxsteps, "knobs", knobs,
       "| ms %.1f" % ms_, "accepted", c[1], "attempts", c[2], "steps/s %.3g" % (c[1] / ms_ * 1e3),
       "| block rounds max", c[7], "us/round %.1f" % (ms_ * 1e3 / max(int(c[7]), 1)),
       "| final radius R_E min/median/max %.2f/%.2f/%.2f" % (r.min(), np.median(r), r.max()),
-      "| stopcond", np.bincount(sc, minlength=7).tolist(), m.kernel_info(n), flush=True)
+      "| stopcond", np.bincount(sc, minlength=7).tolist(), m.kernel_info(n), "lib", a.lib or "default", same, flush=True)
