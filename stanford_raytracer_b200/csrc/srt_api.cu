@@ -244,7 +244,8 @@ int srt_model_grid(srt_model** m, const char* path, int yearday, int msec, int u
   size_t nb = hg.nodes.size() * sizeof(double);
   size_t ax = (hg.xs.size() + hg.ys.size() + hg.zs.size()) * sizeof(double);
   const SrtGrid& hgd = mm->M.grid;
-  const size_t ncells = (size_t)(hgd.nx > 1 ? hgd.nx - 1 : 0) * (size_t)(hgd.ny > 1 ? hgd.ny - 1 : 0) * (size_t)(hgd.nz > 1 ? hgd.nz - 1 : 0);
+  // coefficient table over the extended lattice (edge and outside cells included), srt_tricubic.h
+  const size_t ncells = (hgd.nx > 1 && hgd.ny > 1 && hgd.nz > 1) ? srt_grid_cell_count(hgd) : 0;
   if (cudaMalloc(&mm->d_nodes, nb) != cudaSuccess || cudaMalloc(&mm->d_axes, ax) != cudaSuccess ||
       (ncells && cudaMalloc(&mm->d_coef, ncells * 256 * sizeof(double)) != cudaSuccess)) {
     rc = cuda_fail(cudaGetLastError(), "cudaMalloc(grid)");

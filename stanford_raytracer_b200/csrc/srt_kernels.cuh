@@ -194,13 +194,14 @@ __global__ void srt_eval_kernel(long long n, const double* __restrict__ x, doubl
   }
 }
 
-// One-shot set-up of the gridded model: tricubic coefficients of every interior cell
-// (tricubic_get_coeff, libtricubic.f95:638-656,715-720) -> coef[cell][64 terms][4 species].
+// One-shot set-up of the gridded model: tricubic coefficients of every cell of the extended lattice
+// (tricubic_get_coeff, libtricubic.f95:638-656,715-720, with the corner clamps of :859-921 for edge and outside
+// cells) -> coef[cell][64 terms][4 species].
 // One thread per (cell, species); the 64 x 64 int8 Amat sits in __constant__ memory and every
 // thread of a warp reads the same entry (broadcast).
 __global__ void srt_coef_kernel(const __grid_constant__ SrtGrid g, double* __restrict__ coef) {
-  const long long ncx = g.nx - 1, ncy = g.ny - 1, ncz = g.nz - 1;
-  const long long total = ncx * ncy * ncz * 4;
+  const long long ncx = g.nx + 1, ncy = g.ny + 1;
+  const long long total = (long long)srt_grid_cell_count(g) * 4;
   for (long long id = blockIdx.x * (long long)blockDim.x + threadIdx.x; id < total; id += (long long)gridDim.x * blockDim.x) {
     const int s = (int)(id & 3);
     const long long cell = id >> 2;
@@ -209,9 +210,9 @@ __global__ void srt_coef_kernel(const __grid_constant__ SrtGrid g, double* __res
       for (int t = 0; t < 64; ++t) dst[4 * t] = 0.0;
       continue;
     }
-    const int i0 = (int)(cell % ncx), j0 = (int)((cell / ncx) % ncy), k0 = (int)(cell / (ncx * ncy));
+    const int is0 = (int)(cell % ncx), js0 = (int)((cell / ncx) % ncy), ks0 = (int)(cell / (ncx * ncy));
     double a[64];
-    srt_tricubic_cell_coef(g, i0, j0, k0, s, a);
+    srt_tricubic_cell_coef_ext(g, is0, js0, ks0, s, a);
     for (int t = 0; t < 64; ++t) dst[4 * t] = a[t];
   }
 }

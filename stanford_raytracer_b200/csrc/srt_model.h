@@ -44,8 +44,9 @@ struct SrtGrid {
   // nodes: [nz][ny][nx][8 arrays][4 species] doubles -- the 32 values one cube corner contributes
   //        (f, dfdx, dfdy, dfdz, d2fdxdy, d2fdxdz, d2fdydz, d3fdxdydz; species fastest) are one
   //        contiguous 256-byte record.
-  // coef:  [nz-1][ny-1][nx-1][64 terms][4 species] doubles -- the tricubic coefficients of every
-  //        interior cell, a = Amat * (scaled corner data), precomputed once by srt_coef_kernel in
+  // coef:  [nz+1][ny+1][nx+1][64 terms][4 species] doubles -- the tricubic coefficients of every cell
+  //        of the extended lattice (index = the 1-based lower corner srt_grid_locate returns, 0..n per axis:
+  //        edge and outside cells included), a = Amat * (scaled, clamped corner data), precomputed once by srt_coef_kernel in
   //        the reference's accumulation order; term t = 16*i + 4*j + k holds a(i + 4j + 16k), the
   //        order tricubic_eval walks them (libtricubic.f95:677-693).  2 KiB per cell.  NULL: every
   //        query takes the on-the-fly path (CPU test build).

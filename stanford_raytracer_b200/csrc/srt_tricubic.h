@@ -6,13 +6,17 @@
 // 8 corners x 8 arrays, a dense 64x64 matmul with Amat, a 64-term polynomial.  What this does:
 //   * cell index from the regular axes (one division + a fix-up against the stored node
 //     coordinates, so the comparison `0 <= xi - x(ind)` is the reference's);
-//   * interior cells (every query of a ray inside the grid): the 64 coefficients x 4 species are
-//     PRECOMPUTED per cell (SrtGrid::coef, 2 KiB per cell, built once by srt_coef_kernel with
-//     srt_tricubic_cell_coef below, the same accumulation order as the reference's matmul), so a
-//     query is one 2 KiB gather served from L2 plus the polynomial;
-//   * cells touching or outside the grid edge take the on-the-fly path, which reproduces the sticky
-//     clamp flags statement by statement.
-// Both paths give the same bits where both apply (tests/test_grid_cpu.py).
+//   * the 64 coefficients x 4 species are PRECOMPUTED per cell (SrtGrid::coef, 2 KiB per cell, built once by
+//     srt_coef_kernel with srt_tricubic_cell_coef_ext below, the same accumulation order as the reference's
+//     matmul), so a query is one 2 KiB gather served from L2 plus the polynomial;
+//   * the table covers the EXTENDED lattice (nx+1)(ny+1)(nz+1): the cells touching or outside the grid edge too,
+//     with the sticky clamp flags applied when their coefficients are built.  This matters for
+//     speed, not only for completeness: about 1 % of the config-3 rays turn NaN and are then stepped to maxsteps
+//     by the reference's controller (no stop condition catches a NaN); a NaN position locates to cell (0,0,0), and
+//     on the on-the-fly path (a 64 x 64 product per species and query) each such ray held up its whole block in
+//     every round;
+//   * without a table (SrtGrid::coef == NULL: SRT_GRID_COEF=0, CPU test build) every query takes the on-the-fly path.
+// Both paths give the same bits (tests/test_grid_cpu.py).
 #pragma once
 #include "srt_physics.h"
 #include "srt_amat.h"
@@ -90,11 +94,12 @@ SRT_HD void srt_powers3(double x, double p[4]) {
   p[3] = x * (x * x);
 }
 
-// the on-the-fly path: tricubic_interpolate_at for one species with the clamp logic of
-// libtricubic.f95:859-921 (flags are sticky across the 8 corners, Q12)
-SRT_HDN double srt_tricubic_slow(const SrtGrid& g, int is0, int js0, int ks0, double xil, double yil, double zil, int s) {
+// The 64 stacked, scaled corner data of the cell whose lower corner is node (is0, js0, ks0) (1-BASED, as maxloc returns
+// them: 0 = below the first node, n = at or beyond the last), with the clamp logic of libtricubic.f95:859-921: an
+// out-of-range corner index is clamped and raises a flag that zeroes the derivative terms across that axis; the flags
+// are sticky across the 8 corners (Q12).  For an interior cell no clamp fires.
+SRT_HD void srt_tricubic_xv(const SrtGrid& g, int is0, int js0, int ks0, int s, double xv[64]) {
   int flagi = 0, flagj = 0, flagk = 0;
-  double xv[64];
   for (int l = 0; l < 8; ++l) {
     int istmp = is0 + (l & 1), jstmp = js0 + ((l >> 1) & 1), kstmp = ks0 + ((l >> 2) & 1);  // 1-based
     if (istmp < 1) { istmp = 1; flagi = 1; }
@@ -109,6 +114,31 @@ SRT_HDN double srt_tricubic_slow(const SrtGrid& g, int is0, int js0, int ks0, do
     if (flagj == 1) { xv[16 + l] = 0.0; xv[32 + l] = 0.0; xv[48 + l] = 0.0; xv[56 + l] = 0.0; }
     if (flagk == 1) { xv[24 + l] = 0.0; xv[40 + l] = 0.0; xv[48 + l] = 0.0; xv[56 + l] = 0.0; }
   }
+}
+
+// Coefficients of ANY cell of the extended lattice is0 in [0, nx], js0 in [0, ny], ks0 in [0, nz] (1-based lower
+// corner as srt_grid_locate returns it), species s: out[t], t = 16*i + 4*j + k  <-  a(i + 4j + 16k).  They depend on
+// the cell only, not on the query point, so edge and outside cells are tabulated like interior ones; for an interior
+// cell this is srt_tricubic_cell_coef(g, is0 - 1, js0 - 1, ks0 - 1, s, out).
+SRT_HD void srt_tricubic_cell_coef_ext(const SrtGrid& g, int is0, int js0, int ks0, int s, double out[64]) {
+  double xv[64];
+  srt_tricubic_xv(g, is0, js0, ks0, s, xv);
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j)
+      for (int k = 0; k < 4; ++k) out[16 * i + 4 * j + k] = srt_amat_row(i + 4 * j + 16 * k, xv);
+}
+
+// record of cell (is0, js0, ks0) in the extended coefficient table [nz+1][ny+1][nx+1][64 terms][4 species]
+SRT_HD size_t srt_grid_cell_index(const SrtGrid& g, int is0, int js0, int ks0) {
+  return ((size_t)ks0 * (size_t)(g.ny + 1) + (size_t)js0) * (size_t)(g.nx + 1) + (size_t)is0;
+}
+SRT_HD size_t srt_grid_cell_count(const SrtGrid& g) { return (size_t)(g.nx + 1) * (size_t)(g.ny + 1) * (size_t)(g.nz + 1); }
+
+// the on-the-fly path: tricubic_interpolate_at for one species with the clamp logic of
+// libtricubic.f95:859-921 (flags are sticky across the 8 corners, Q12)
+SRT_HDN double srt_tricubic_slow(const SrtGrid& g, int is0, int js0, int ks0, double xil, double yil, double zil, int s) {
+  double xv[64];
+  srt_tricubic_xv(g, is0, js0, ks0, s, xv);
   double xp[4], yp[4], zp[4];
   srt_powers3(xil, xp);
   srt_powers3(yil, yp);
@@ -150,7 +180,7 @@ SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT
   {
     const int lane_ = threadIdx.x & 31, tbase_ = lane_ & ~7, r_ = lane_ & 7;
     const unsigned tmask_ = 0xffu << tbase_;
-    const long long c_ = (ini && inj && ink && g.coef) ? (long long)((((size_t)(ks0 - 1) * (g.ny - 1) + (js0 - 1)) * (g.nx - 1) + (is0 - 1))) : -1ll;
+    const long long c_ = g.coef ? (long long)srt_grid_cell_index(g, is0, js0, ks0) : -1ll;
     const long long c0_ = __shfl_sync(tmask_, c_, tbase_ + 6);
     if (c0_ >= 0) {  // team-uniform
       double* stage = (double*)srt_stage_smem + (size_t)(threadIdx.x >> 3) * 66;  // 66: the 4 teams of a warp on distinct banks
@@ -186,8 +216,11 @@ SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT
     }
   }
 #endif
-  if (ini && inj && ink && g.coef) {
-    const double* a = g.coef + ((((size_t)(ks0 - 1) * (g.ny - 1) + (js0 - 1)) * (g.nx - 1) + (is0 - 1)) * 256);
+  if (g.coef) {
+    // every cell of the extended lattice is tabulated (edge and outside cells with their clamped corners), so a
+    // query outside the grid -- or a ray whose position has become NaN: all three locates return 0 and the local
+    // offsets stay 0 -- costs the same as an interior one
+    const double* a = g.coef + srt_grid_cell_index(g, is0, js0, ks0) * 256;
     double xp[4], yp[4], zp[4];
     srt_powers3(xil, xp);
     srt_powers3(yil, yp);

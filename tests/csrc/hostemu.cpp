@@ -70,12 +70,12 @@ void* emu_model_grid(const char* path, int yearday, int msec, int use_igrf) {
   if (use_igrf & 2) {  // bit 1: precompute the per-cell coefficients the way srt_coef_kernel does
     use_igrf &= 1;
     const SrtGrid& g = M->grid;
-    const size_t ncx = g.nx - 1, ncy = g.ny - 1, ncz = g.nz - 1;
-    std::vector<double>* coef = new std::vector<double>(ncx * ncy * ncz * 256, 0.0);
-    for (size_t cell = 0; cell < ncx * ncy * ncz; ++cell)
+    const size_t ncx = g.nx + 1, ncy = g.ny + 1, ncells = srt_grid_cell_count(g);
+    std::vector<double>* coef = new std::vector<double>(ncells * 256, 0.0);
+    for (size_t cell = 0; cell < ncells; ++cell)
       for (int sp = 0; sp < g.nspec; ++sp) {
         double a[64];
-        srt_tricubic_cell_coef(g, (int)(cell % ncx), (int)((cell / ncx) % ncy), (int)(cell / (ncx * ncy)), sp, a);
+        srt_tricubic_cell_coef_ext(g, (int)(cell % ncx), (int)((cell / ncx) % ncy), (int)(cell / (ncx * ncy)), sp, a);
         for (int t = 0; t < 64; ++t) (*coef)[cell * 256 + 4 * t + sp] = a[t];
       }
     M->grid.coef = coef->data();

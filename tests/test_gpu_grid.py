@@ -56,6 +56,13 @@ def test_precomputed_coefficients_equal_on_the_fly(srt, grid, monkeypatch):
     slow = srt.interpsetup(GRID13, 2010001, 0, 1, 0)
     x = np.random.default_rng(9).uniform(-4 * R_E, 4 * R_E, (20000, 3))
     assert np.array_equal(grid.funcPlasmaParams(x)["raw"], slow.funcPlasmaParams(x)["raw"], equal_nan=True)
+    # the table covers the extended lattice: edge and outside cells, and where a NaN / Inf position locates to
+    nan, inf = float("nan"), float("inf")
+    wild = np.array([[nan, nan, nan], [nan, 1.0e6, -2.0e7], [3.0e6, nan, nan], [inf, 0.0, 1.0e7], [-inf, -inf, inf], [2.0e8, -2.0e8, 0.0]])
+    xo = np.concatenate([np.random.default_rng(10).uniform(-1.4 * 4 * R_E, 1.4 * 4 * R_E, (20000, 3)), wild])
+    t, f = grid.funcPlasmaParams(xo)["raw"], slow.funcPlasmaParams(xo)["raw"]
+    assert np.array_equal(t, f, equal_nan=True)
+    assert np.isfinite(t[-len(wild):, 4:8]).all()  # the clamped corner's density
 
 
 def test_golden_grid_fixture(srt, grid):

@@ -100,10 +100,23 @@ def test_edges_and_outside_match_oracle_bitwise(built):
     nodes = gridfile.node_axes(13, -ext, ext)
     special = np.array([[nodes[0], nodes[3], nodes[5]], [nodes[12], nodes[12], nodes[12]], [nodes[11], 0.0, nodes[12]], [nodes[0], nodes[0], nodes[0]],
                         [np.nextafter(nodes[12], 0), 1.0, 2.0], [np.nextafter(nodes[0], -1e30), 1.0, 2.0]])
+    # far outside, and the positions of a ray whose state has become NaN / Inf (about 1 % of the config-3 rays do and
+    # are then stepped to maxsteps: raytracer_stopconditions catches no NaN): locate returns 0 or n on those axes
+    nan, inf = float("nan"), float("inf")
+    wild = np.array([[nan, nan, nan], [nan, 1.0e6, -2.0e7], [3.0e6, nan, nan], [inf, 0.0, 1.0e7], [-inf, -inf, inf], [50 * ext, -50 * ext, 0.0]])
     x = np.concatenate([x, special])
     a, b = og.plasma(x), he.plasma(x)
     assert np.array_equal(a, b, equal_nan=True)
     assert np.isfinite(a[np.linalg.norm(x, axis=1) > R_E]).all()
+    # the coefficient table covers the extended lattice: edge / outside / NaN queries read it like interior ones and
+    # give the bits of the on-the-fly path (hostemu without a table) and of the oracle
+    fly = common.HostEmu("grid", GRID13, use_igrf=1, precomputed_coef=False)
+    xa = np.concatenate([x, wild])
+    t, f, o = he.plasma(xa), fly.plasma(xa), og.plasma(xa)
+    assert np.array_equal(t, f, equal_nan=True)
+    assert np.array_equal(t[:, 4:8], o[:, 4:8], equal_nan=True)  # densities; B0 of a NaN position is NaN in all three
+    assert np.array_equal(t, o, equal_nan=True)
+    assert np.isfinite(t[-len(wild):, 4:8]).all()  # the clamped corner's density: finite even for a NaN position
 
 
 def test_dense_and_sparse_matmul_agree(built):
