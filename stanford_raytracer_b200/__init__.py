@@ -17,7 +17,7 @@ import numpy as np
 from . import rayfile
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libsrt.so")
+_LIB_PATH = os.environ.get("SRT_LIB") or os.path.join(_HERE, "libsrt.so")  # SRT_LIB: tuning hook, an alternative build (tools/build_variant.sh)
 ROW_DOUBLES = 20
 LOG_WORDS = 21
 SUMMARY_WORDS = 24

@@ -28,4 +28,12 @@ if [ -f tools/_variants/stage.so ]; then
   run SRT_X=0 python tools/c3_age.py --maxsteps 1000 --lib tools/_variants/stage.so --compare /tmp/c3_1000.npy
   run SRT_TEAM_PHASE_ALIGN=1 python tools/c3_age.py --maxsteps 4000 --lib tools/_variants/stage.so --compare /tmp/c3_4000.npy
 fi
-tail -40 $out
+# NaN fast-forward (build variant): the whole parity suite against it, then config 3 and config 2 timings
+#   tools/build_variant.sh nanff "$I" "$I -DSRT_INLINE_STIX -DSRT_INLINE_PLASMA -DSRT_INLINE_ACCEPT -DSRT_NAN_FASTFWD"
+if [ -f tools/_variants/nanff.so ]; then
+  run SRT_LIB=$PWD/tools/_variants/nanff.so python -m pytest tests/test_gpu_parity.py tests/test_gpu_grid.py -x -q
+  run SRT_X=0 python tools/c3_age.py --maxsteps 4000 --lib tools/_variants/nanff.so --compare /tmp/c3_4000.npy
+  run SRT_VARIANT_ONLY=nanff python tools/gpu_variants.py 100 100 20000 team
+  run SRT_VARIANT_ONLY=libsrt python tools/gpu_variants.py 100 100 20000 team
+fi
+tail -60 $out
