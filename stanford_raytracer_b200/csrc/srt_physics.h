@@ -860,6 +860,9 @@ SRT_HD int srt_ray_attempt(SrtModelRef MR, const SrtRunParams& P, SrtRayState& s
     for (int i = 0; i < 6; ++i) e2x[i] = xs[i] + 1.0 / 6.0 * (k1[i] + 2.0 * k2[i] + 2.0 * k3[i] + k4[i]);
   }
   const double dtincr = dt;
+  // :821 `w = est2(7)`: the local w of raytracer_run is set as soon as an attempt passes the error test -- before the
+  // resonance-cone test -- so an attempt that is cone-refined before the first acceptance already ends Q1
+  st.wl = st.w;
   // re-project |k| onto the dispersion surface at the new point (:819-836)
   if (!have_c2) srt_centre<DENS, USE_IGRF>(MR, e2x, st.w, c2);
   SrtCplx ksel = srt_solve_root(e2x + 3, st.w, c2.d, c2.s, P.root);
@@ -894,7 +897,6 @@ SRT_HD int srt_ray_attempt(SrtModelRef MR, const SrtRunParams& P, SrtRayState& s
   for (int i = 0; i < 3; ++i) st.x[i] = e2x[i];
 #pragma unroll
   for (int i = 0; i < 3; ++i) st.k[i] = kn[i].re;
-  st.wl = st.w;
   st.lastrefinedown = 0;
   st.t = st.t + dtincr;
   st.nstep = st.nstep + 1;

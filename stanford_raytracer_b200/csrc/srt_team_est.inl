@@ -54,6 +54,7 @@
           }
         }
         if (!retry) {
+          wl = w;  // raytracer.f95:821, before the cone test (see srt_ray_attempt)
           // re-project |k| at est2 (lane 7 holds the plasma there and its Stix set at w)
           SrtCplx ksel = srt_solve_root(e2 + 3, w, pd, sx, P.root);
           ksel.re = team_get(T, ksel.re, 7);
@@ -88,7 +89,6 @@
           } else {
             // ---- accept (raytracer.f95:909-922)
             xc = (comp == 0) ? e2[0] : (comp == 1) ? e2[1] : (comp == 2) ? e2[2] : (comp == 3) ? knew[0] : (comp == 4) ? knew[1] : knew[2];
-            wl = w;
             lastrefinedown = 0;
             t = t + dt_used;
             nstep = nstep + 1;

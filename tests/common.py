@@ -107,3 +107,28 @@ class HostEmu:
         n = self.E.emu_trace(self.h, pos0.ctypes.data, dir0.ctypes.data, w0, dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep,
                              rows.ctypes.data, len(rows), C.byref(sc), C.byref(nr), C.byref(nc), C.byref(ce))
         return dict(rows=rows[:n].copy(), stopcond=sc.value, nrejected=nr.value, ncone=nc.value, fixed_cone_exit=ce.value, dir0=dir0)
+
+
+# Rays whose FIRST attempt that passes the error test leaves the resonance cone (launched 1-5 degrees inside the cone with a
+# large dt0): raytracer.f95:821 sets the local `w` before the cone test at :891, so the retry already carries the dF/dk
+# error term (with `w` set only on acceptance, 57 of 95 such rays differed from the oracle).
+# (launch latitude deg, frequency Hz, wave-normal angle from B0 deg, dt0)
+CONE_FIRST = [(15.0, 30000.0, 94.05, 0.05), (20.0, 8000.0, 91.3, 0.02), (20.0, 20000.0, 92.925, 0.1), (30.0, 10000.0, 85.7, 0.05),
+              (30.0, 10000.0, 86.1, 0.1), (30.0, 15000.0, 91.6, 0.05), (20.0, 30000.0, 86.95, 0.05), (45.0, 30000.0, 87.525, 0.05)]
+
+
+def cone_first_rays(oracle_model):
+    """pos0, dir0, w0, params of the CONE_FIRST rays (direction built from the oracle's field at the launch point)."""
+    pos, dirs, ws, dts = [], [], [], []
+    for lat, f, ang, dt0 in CONE_FIRST:
+        p0 = ol.launch_point(lat, 0.0, 1000.0)
+        B = oracle_model.plasma(p0)[0][16:19]
+        b = B / np.linalg.norm(B)
+        e = np.cross(b, [0.0, 1.0, 0.0])
+        e /= np.linalg.norm(e)
+        a = np.deg2rad(ang)
+        pos.append(p0)
+        dirs.append(np.cos(a) * b + np.sin(a) * e)
+        ws.append(2 * np.pi * f)
+        dts.append(dt0)
+    return np.array(pos), np.array(dirs), np.array(ws), dts

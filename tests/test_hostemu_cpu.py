@@ -71,6 +71,23 @@ def test_root1_and_given_direction(pair):
         assert a["stopcond"] == b["stopcond"] and np.array_equal(a["rows"], b["rows"], equal_nan=True)
 
 
+def test_first_attempt_cone_refined(pair):
+    """raytracer.f95:821: the local `w` is set before the resonance-cone test, so a retry after a cone refinement that
+    precedes the first acceptance already includes the dF/dk error term."""
+    o, h = pair
+    pos0, dirs, ws, dts = common.cone_first_rays(o)
+    ncone_before_first = 0
+    for i in range(len(ws)):
+        P = dict(common.C2, maxsteps=40, dt0=dts[i], dtmax=0.2)
+        first = o.trace(pos0[i], dirs[i], ws[i], **dict(P, maxsteps=2))
+        ncone_before_first += first["ncone"] > 0
+        a = o.trace(pos0[i], dirs[i], ws[i], **P)
+        b = h.trace(pos0[i], dirs[i], ws[i], **P)
+        assert a["stopcond"] == b["stopcond"] and a["nrejected"] == b["nrejected"] and a["ncone"] == b["ncone"], i
+        assert np.array_equal(a["rows"], b["rows"], equal_nan=True), i
+    assert ncone_before_first == len(ws)
+
+
 def test_libm_build_is_close_but_not_identical(built):
     """The oracle linked against glibc's libm (what the reference Fortran uses) instead of srt_math.h:
     endpoints of a 300-step fixed-step ray agree to ~1e-6 relative (NOT 1e-9) and individual bits differ -- the measured
