@@ -5,18 +5,24 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
     python bench.py --impl reference ...     (the CPU restatement of the reference on the host cores)
 
-One "step" = one pass of the hot path over one batch of synthetic rays: BASELINE config 2
-(10 000 rays = 100 frequencies 0.2-30 kHz x 100 launch latitudes 10-60 deg, Ngo density +
-dipole field, adaptive RK45) per GPU.  With N > 1 every rank traces its own 10 000-ray sweep
-(the launch longitude differs per rank), no collective on the data path: weak scaling.
+One "step" = one pass of the hot path over one batch of synthetic rays.
 
-value   = accepted ray-steps/s, whole job, inputs resident in HBM, device-timed (CUDA events on
-          the launching stream, max over ranks).
-e2e     = the same metric through srt_trace_batch() with HOST buffers: H2D of the rays, the
-          kernels, the (ray,row) gather and D2H of every trajectory row inside the timed region.
-roofline: FP64 (non-tensor) pipe.  achieved = algorithmic flop-equivalents (SURVEY.md 8d:
-          4.2e4 per accepted RK45 step, 4.0e4 per rejected attempt, Ngo+dipole) / kernel time;
-          peak = DFMA rate measured live by srt_fp64_peak().
+The line (BASELINE configs[1], "C2"): per GPU 10 000 rays = 100 frequencies 0.2-30 kHz x 100 launch latitudes 10-60 deg,
+Ngo density + dipole field, adaptive RK45.  With N > 1 the launch set is ONE lattice of N x 10 000 rays (N launch
+longitudes) split over the ranks by ray index through the product's own shard path (stanford_raytracer_b200/shard.py):
+fixed work per GPU = weak scaling, no collective on the data path; the host-side gather on rank 0 is inside `e2e`.
+
+value   = accepted ray-steps/s, whole job, inputs resident in HBM, device-timed (CUDA events on the launching stream,
+          max over ranks).
+e2e     = the same metric through the reference-facing call with HOST buffers: H2D of the rays, the kernels, the
+          (ray,row) ordering, D2H of every trajectory row and (N > 1) the gather of all rays on rank 0.
+roofline: FP64 (non-tensor) pipe.  achieved = algorithmic flop-equivalents / kernel time; peak = DFMA
+          rate measured live by srt_fp64_peak().
+extra   = the other BASELINE configs on the same box in the same run (fewer sweeps): C3 (100 k rays, tricubic grid +
+          IGRF), a C4-shaped 100 k-ray lattice (strong scaling: sharded over the N ranks) and, at N = 8, the full
+          1 M-ray C4; each with value, e2e and roofline.
+parity  = rays of the timed sweeps traced by the CPU oracle as well (the cpu_baseline leg) and compared with the
+          GPU summaries bit for bit: parity_checked_rays / parity_mismatches (non-zero exits 1).
 """
 import argparse
 import json
@@ -38,50 +44,60 @@ METRIC = "accepted_ray_steps_per_sec"
 UNIT = "ray-steps/s"
 ROW_BYTES = 168         # one log entry
 
-
 WORKLOADS = {
-    # name: (n_freq, n_lat, n_lon, outputper, model, flop-eq per accepted step, per rejected attempt, description)
-    "c2": (100, 100, 1, 1, "ngo", 4.2e4, 4.0e4,
-           "C2: 10k-ray sweep (100 freq 0.2-30 kHz x 100 lat 10-60 deg), Ngo density + dipole B, adaptive RK45 "
-           "(dt0=1e-3, dtmax=0.1, maxerr=5e-4, tmax=10 s, root=2), per GPU"),
-    "c3": (100, 100, 10, 100, "grid", 6.8e4, 6.5e4,
+    # name: (n_freq, n_lat, n_lon, outputper, model, description); n_lon None = one longitude per rank (the line)
+    "c2": (100, 100, None, 1, "ngo",
+           "C2: 10k-ray sweep per GPU (100 freq 0.2-30 kHz x 100 lat 10-60 deg x one launch longitude per GPU), Ngo density + dipole B, "
+           "adaptive RK45 (dt0=1e-3, dtmax=0.1, maxerr=5e-4, tmax=10 s, root=2); N > 1: one lattice sharded by ray index"),
+    "c3": (100, 100, 10, 100, "grid",
            "C3: 100k rays (100 freq x 100 lat x 10 lon) through a tricubic 80^3 log-density grid over +-10 R_E (sampled from "
-           "the Ngo model by the GPU funcPlasmaParams kernel: GCPM cannot be built here) + IGRF field, adaptive RK45, per GPU"),
-    "c4": (100, 1000, 10, 100, "ngo", 4.2e4, 4.0e4,
-           "C4: 1M-ray launch grid (100 freq x 1000 lat x 10 lon), Ngo density + dipole B, adaptive RK45, per GPU"),
+           "the Ngo model by the GPU funcPlasmaParams kernel: GCPM cannot be built here) + IGRF field, adaptive RK45"),
+    "c4_100k": (100, 100, 10, 100, "ngo",
+                "C4-shaped: 100k-ray launch grid (100 freq x 100 lat x 10 lon), Ngo density + dipole B, adaptive RK45, one lattice sharded over the GPUs"),
+    "c4": (100, 1000, 10, 100, "ngo",
+           "C4: 1M-ray launch grid (100 freq x 1000 lat x 10 lon), Ngo density + dipole B, adaptive RK45, one lattice sharded over the GPUs"),
 }
 R_E = 6371.2e3
 _GRID_CACHE = os.path.join(tempfile.gettempdir(), "srt_bench_grid80.txt")  # ~50 MB of text: kept out of the repo tree
 
 
-def workload(rank, name="c2"):
+def work_model():
+    """flop-equivalents per accepted step / rejected attempt and where the figures come from"""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "work_tally.json")))
+        return t
+    except Exception:
+        return {"ngo": {"accepted": 4.2e4, "rejected": 4.0e4}, "grid": {"accepted": 6.8e4, "rejected": 6.5e4},
+                "source": "SURVEY.md 8(d) hand count (+-20 %)"}
+
+
+def lattice(name, world):
     import common
-    nf, nlat, nlon, outputper, model, fa, fr, desc = WORKLOADS[name]
+    nf, nlat, nlon, outputper, model, desc = WORKLOADS[name]
     freqs = np.logspace(np.log10(200.0), np.log10(30000.0), nf)
     lats = np.linspace(10.0, 60.0, nlat)
-    lons = (np.arange(nlon) * 36.0 + 36.0 * rank / max(nlon, 1)) if nlon > 1 else [36.0 * rank]
+    lons = np.arange(nlon if nlon else world) * 36.0
     pos0, dir0, w0 = common.launch_grid(freqs, lats, lons)
     return pos0, dir0, w0, dict(common.C2), common.NGO_CFG
 
 
-def make_model(srt, name, cfg):
-    """The plasma model of a workload, built through the product's own API (never the oracle)."""
-    if WORKLOADS[name][4] == "ngo":
-        return srt.ngosetup(cfg, 2010001, 0, 0, 0)
+def grid_file(srt, cfg, local_rank):
     from stanford_raytracer_b200 import gridfile
-    os.makedirs(os.path.dirname(_GRID_CACHE), exist_ok=True)
-    path = _GRID_CACHE + ".%d" % int(os.environ.get("LOCAL_RANK", "0"))
+    path = _GRID_CACHE + ".%d" % local_rank
     if not os.path.exists(path):
         ngo = srt.ngosetup(cfg, 2010001, 0, 0, 0)
         ext = (-10 * R_E, 10 * R_E) * 3
         f, qs, ms = gridfile.sample_grid(lambda x: ngo.funcPlasmaParams(x)["raw"], 80, 80, 80, ext)
         gridfile.write_grid(path, f, qs, ms, ext)
-    return srt.interpsetup(path, 2010001, 0, 1, 0)
+    return path
 
 
-def config_dict(n_gpus, name="c2", nrays=10000):
-    return {"workload": WORKLOADS[name][7], "rays_per_gpu": nrays, "global_rays": nrays * n_gpus, "outputper": WORKLOADS[name][3],
-            "parallelism": "rays sharded by rank, no collective", "l2": "flushed between timed iterations (256 MiB write)"}
+def make_model(srt, name, cfg, local_rank):
+    """The plasma model of a workload, built through the product's own API (never the oracle)."""
+    if WORKLOADS[name][4] == "ngo":
+        return srt.ngosetup(cfg, 2010001, 0, 0, 0), cfg
+    path = grid_file(srt, cfg, local_rank)
+    return srt.interpsetup(path, 2010001, 0, 1, 0), path
 
 
 class ClockSampler(threading.Thread):
@@ -110,132 +126,194 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def cpu_reference_run(pos0, dir0, w0, params, cfg, nsample, threads, kind="ngo", use_igrf=0):
-    """Times the CPU oracle (the port of the reference) on a strided sample of the workload,
-    one model instance per thread.  Returns (accepted steps, seconds)."""
+# ------------------------------------------------------------------------------------------ CPU side (oracle/: checker + baseline)
+def cpu_run(mode, kind, path, use_igrf, pos0, dir0, w0, params, idx, threads):
+    """Traces the rays `idx` of a launch set on the host cores, `threads` workers pulling rays from ONE queue (per-ray
+    step counts differ by >100x, so static chunks would time the unluckiest thread).
+    mode "faithful": oracle/ with the reference's call structure (8 plasma + 14 dispersion_relation calls per RHS);
+    "refcost": the same plus RECALC_08 and the dipole-tilt chain on every plasma call, as the Fortran adapters do
+    (ngo_dens_model_adapter.f95:169) -- what the reference binary itself would cost; "dedup": the de-duplicated
+    evaluation order of the GPU kernels compiled for the host at -O3 (same algorithmic work as the GPU).  All give
+    the same bits.
+    Returns dict(accepted, seconds, last_row, nrows, stopcond, busy_max/busy_mean of the workers)."""
     import oracle_lib as ol
-    idx = np.linspace(0, len(w0) - 1, nsample).astype(int)
-    chunks = [idx[i::threads] for i in range(threads)]
-    chunks = [c for c in chunks if len(c)]
-    models = [ol.OracleModel(kind, cfg, use_igrf=use_igrf) for _ in chunks]
-    acc = [0] * len(chunks)
+    n = len(idx)
+    last = np.zeros((n, 20))
+    nrows = np.zeros(n, dtype=np.int64)
+    stop = np.zeros(n, dtype=np.int32)
+    nthreads = max(1, min(threads, n))
+    if mode in ("faithful", "refcost"):
+        models = [ol.OracleModel(kind, path, use_igrf=use_igrf, faithful_cost=(mode == "refcost")) for _ in range(nthreads)]
+    else:
+        shared = ol.DedupModel(kind, path, use_igrf=use_igrf)
+        models = [shared] * nthreads  # read-only during a trace
+    lock, head, busy = threading.Lock(), [0], [0.0] * nthreads
 
-    def work(i):
-        c = chunks[i]
-        acc[i] = models[i].trace_batch_summary(pos0[c], dir0[c], w0[c], **params)["accepted"]
+    def work(t):
+        while True:
+            with lock:
+                j = head[0]
+                head[0] += 1
+            if j >= n:
+                return
+            t0 = time.perf_counter()
+            r = int(idx[j])
+            s = models[t].trace_summary(pos0[r], dir0[r], w0[r], **params)
+            last[j], nrows[j], stop[j] = s["last_row"], s["nrows"], s["stopcond"]
+            busy[t] += time.perf_counter() - t0
 
     t0 = time.perf_counter()
-    ts = [threading.Thread(target=work, args=(i,)) for i in range(len(chunks))]
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(nthreads)]
     [t.start() for t in ts]
     [t.join() for t in ts]
     dt = time.perf_counter() - t0
-    return int(sum(acc)), dt
+    return dict(accepted=int((nrows - 1).sum()), seconds=dt, last_row=last, nrows=nrows, stopcond=stop, threads=nthreads,
+                busy_max=max(busy), busy_mean=float(np.mean(busy)))
+
+
+def cpu_baselines(kind, path, use_igrf, pos0, dir0, w0, params, n_all, n_one, threads, short):
+    """The CPU figures of SURVEY.md 8(d) on bounded samples of one launch set (strided rays): {faithful, dedup} x
+    {1 core, all cores}, plus the reference's own cost (RECALC_08 per plasma call) on a small sample.  `short`
+    (e.g. {"maxsteps": 300}) shortens the rays of every run but dedup/all-cores, whose full-length rays double as the
+    parity sample.  Returns (modes dict, (ray indices, dedup/all-cores run))."""
+    idx_all = np.unique(np.linspace(0, len(w0) - 1, n_all).astype(int))
+    idx_one = np.unique(np.linspace(0, len(w0) - 1, n_one).astype(int))
+    ps = dict(params, **short)
+    note = (" first %d steps of each ray" % short["maxsteps"]) if short else ""
+
+    def entry(r, idx, nt):
+        e = {"value": r["accepted"] / r["seconds"], "cores": r["threads"], "rays": len(idx), "seconds": r["seconds"]}
+        if nt > 1:
+            e["slowest_worker_over_mean"] = r["busy_max"] / max(r["busy_mean"], 1e-9)
+        return e
+
+    out = {}
+    full = cpu_run("dedup", kind, path, use_igrf, pos0, dir0, w0, params, idx_all, threads)
+    out["dedup_all_cores"] = entry(full, idx_all, threads)
+    out["dedup_1_core"] = dict(entry(cpu_run("dedup", kind, path, use_igrf, pos0, dir0, w0, ps, idx_one, 1), idx_one, 1), note=note)
+    tf = min(threads, 8) if kind == "grid" else threads  # every faithful worker parses its own copy of the grid file
+    fa = cpu_run("faithful", kind, path, use_igrf, pos0, dir0, w0, ps, idx_all, tf)
+    out["faithful_all_cores"] = dict(entry(fa, idx_all, tf), note=note)
+    out["faithful_1_core"] = dict(entry(cpu_run("faithful", kind, path, use_igrf, pos0, dir0, w0, ps, idx_one, 1), idx_one, 1), note=note)
+    idx_rc = idx_all[:: max(1, len(idx_all) // max(threads, 16))]
+    rc = cpu_run("refcost", kind, path, use_igrf, pos0, dir0, w0, ps, idx_rc, tf)
+    out["reference_cost_all_cores"] = dict(entry(rc, idx_rc, threads), note="RECALC_08 and the dipole-tilt chain on every plasma call, as the Fortran adapters do;" + note)
+    if not short:  # the two statements of the arithmetic must agree bit for bit
+        out["faithful_equals_dedup"] = bool(np.array_equal(fa["last_row"], full["last_row"], equal_nan=True) and np.array_equal(fa["nrows"], full["nrows"]))
+    return out, (idx_all, full)
+
+
+def parity_check(summary_rows, idx, cpu):
+    """GPU summaries ([nrays][24]: last row, nsteps, stopcond, ...) of the rays idx against the CPU traces, bit for bit."""
+    g = summary_rows[idx]
+    bad = 0
+    for j in range(len(idx)):
+        ok = np.array_equal(g[j, :20], cpu["last_row"][j], equal_nan=True) and int(g[j, 20]) == int(cpu["nrows"][j]) and int(g[j, 21]) == int(cpu["stopcond"][j])
+        bad += 0 if ok else 1
+    return len(idx), bad
 
 
 def run_reference(args):
+    """The reference arm: the CPU restatement of the reference on every host core, on the line's workload (C2),
+    each step a bounded sample of it.  value = the de-duplicated statement (same algorithmic work as the GPU: the
+    conservative denominator); the faithful call structure is reported beside it."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import oracle_lib as ol
     ol.build()
-    pos0, dir0, w0, params, cfg = workload(0, "c2")
+    pos0, dir0, w0, params, cfg = lattice("c2", 1)
     threads = os.cpu_count() or 1
-    nsample = max(threads, 256)  # ~12 s of CPU work per step on 16 cores
+    nsample = max(threads, 256)
+    idx = np.unique(np.linspace(0, len(w0) - 1, nsample).astype(int))
+    small = np.unique(np.linspace(0, len(w0) - 1, max(threads, 8)).astype(int))
     for _ in range(args.warmup):
-        cpu_reference_run(pos0, dir0, w0, params, cfg, max(threads, 8), threads)
+        cpu_run("dedup", "ngo", cfg, 0, pos0, dir0, w0, params, small, threads)
     acc_total, t_total = 0, 0.0
     for _ in range(args.steps):
-        a, t = cpu_reference_run(pos0, dir0, w0, params, cfg, nsample, threads)
-        acc_total += a
-        t_total += t
+        r = cpu_run("dedup", "ngo", cfg, 0, pos0, dir0, w0, params, idx, threads)
+        acc_total += r["accepted"]
+        t_total += r["seconds"]
+    f = cpu_run("faithful", "ngo", cfg, 0, pos0, dir0, w0, params, idx, threads)
+    idx_rc = idx[:: max(1, len(idx) // max(threads, 16))]
+    rc = cpu_run("refcost", "ngo", cfg, 0, pos0, dir0, w0, params, idx_rc, threads)
     val = acc_total / t_total
     line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "impl": "reference", "config": config_dict(args.gpus),
+            "data": "synthetic", "impl": "reference", "config": config_dict(args.gpus, "c2", 10000, 10000 * args.gpus),
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                             "sample": "%d rays strided out of the 10k-ray sweep per step (C++ restatement of the Fortran; no Fortran compiler on the box)" % nsample},
+                             "sample": "%d rays strided out of the 10k-ray sweep per step, one dynamic ray queue; de-duplicated evaluation order (same work as the GPU) "
+                                       "of the C++ restatement of the Fortran (no Fortran compiler on the box)" % len(idx),
+                             "faithful_call_structure": {"value": f["accepted"] / f["seconds"], "cores": f["threads"], "seconds": f["seconds"], "rays": len(idx)},
+                             "reference_cost": {"value": rc["accepted"] / rc["seconds"], "cores": rc["threads"], "seconds": rc["seconds"], "rays": len(idx_rc),
+                                                "note": "RECALC_08 and the dipole-tilt chain on every plasma call, as the Fortran adapters do"}},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (supplementary workloads whose sweep takes minutes)")
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="c2 is the bench line; c3/c4 are the other BASELINE configs")
-    args = ap.parse_args()
-    if args.impl == "reference":
-        return run_reference(args)
+def config_dict(n_gpus, name, rays_per_gpu, global_rays):
+    return {"workload": WORKLOADS[name][5], "rays_per_gpu": int(rays_per_gpu), "global_rays": int(global_rays), "outputper": WORKLOADS[name][3],
+            "parallelism": "one launch set sharded by ray index over the ranks, host-side gather on rank 0, no collective",
+            "l2": "flushed between timed iterations (256 MiB write)"}
 
+
+# ------------------------------------------------------------------------------------------ GPU side
+class Ctx:
+    pass
+
+
+def measure(C, name, steps, warmup, e2e_steps, with_cpu, cpu_sizes):
+    """Times one workload: device-resident sweeps of this rank's shard + the end-to-end sharded call.  Collective."""
     import torch
     import torch.distributed as dist
-    import stanford_raytracer_b200 as srt
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: libsrt has no CPU path")
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    dev = torch.device("cuda", local_rank)
-    srt.init(local_rank)
-
-    wl = args.workload
-    outputper = WORKLOADS[wl][3]
-    FLOPS_ACCEPTED, FLOPS_REJECTED = WORKLOADS[wl][5], WORKLOADS[wl][6]
-    pos0, dir0, w0, params, cfg = workload(rank, wl)
-    nrays = len(w0)
-    model = make_model(srt, wl, cfg)
+    srt, shard = C.srt, C.shard
+    outputper, kind = WORKLOADS[name][3], WORKLOADS[name][4]
+    pos0, dir0, w0, params, cfg = lattice(name, C.world)
+    nglobal = len(w0)
+    idx = shard.shard_indices(nglobal, C.rank, C.world)
+    nrays = len(idx)
+    model, model_path = make_model(srt, name, cfg, C.local_rank)
     P = srt.RunParams(params["dt0"], params["dtmax"], params["maxerr"], params["minalt"], params["tmax"], params["maxsteps"], params["root"],
                       params["fixedstep"], outputper)
-    # device-resident inputs (SoA) and outputs
-    rays_h = np.ascontiguousarray(np.concatenate([pos0.T, dir0.T, w0[None, :]], axis=0))  # [7][nrays], C order (concatenate keeps F order)
+    dev = C.dev
+    rays_h = np.ascontiguousarray(np.concatenate([pos0[idx].T, dir0[idx].T, w0[idx][None, :]], axis=0))  # [7][nrays]
     rays0 = torch.from_numpy(rays_h).to(dev)
     rays = rays0.clone()
     summary = torch.empty((nrays, srt.SUMMARY_WORDS), dtype=torch.float64, device=dev)
     counters = torch.zeros(8, dtype=torch.int64, device=dev)
+    stream = torch.cuda.current_stream()
     # size the trajectory log from a counting pass (no log attached: nothing recorded, nothing dropped)
     t_count = time.perf_counter()
-    srt.trace_batch_device(model, nrays, rays.data_ptr(), P, 0, 0, summary.data_ptr(), counters.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    srt.trace_batch_device(model, nrays, rays.data_ptr(), P, 0, 0, summary.data_ptr(), counters.data_ptr(), stream.cuda_stream)
     torch.cuda.synchronize()
-    if rank == 0:
-        print("bench: counting pass %.1f s, %d accepted steps, %d attempts" % (time.perf_counter() - t_count, int(counters[1].item()), int(counters[2].item())),
+    c0 = counters.cpu().numpy()
+    if C.rank == 0:
+        print("bench[%s]: counting pass %.1f s, %d accepted steps, %d attempts (rank 0 shard: %d rays)" % (name, time.perf_counter() - t_count, int(c0[1]), int(c0[2]), nrays),
               file=sys.stderr, flush=True)
-    log_cap = int(counters[1].item()) // outputper + 2 * nrays + 1024
+    log_cap = int(c0[1]) // outputper + 2 * nrays + 1024
     log = torch.empty((log_cap, srt.LOG_WORDS), dtype=torch.float64, device=dev)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    stream = torch.cuda.current_stream()
-
-    def device_step():
-        rays.copy_(rays0)
-        srt.trace_batch_device(model, nrays, rays.data_ptr(), P, log.data_ptr(), log_cap, summary.data_ptr(), counters.data_ptr(), stream.cuda_stream)
 
     def barrier():
-        if world > 1:
+        if C.world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 0)):
-        device_step()
+    for _ in range(max(warmup, 0)):
+        rays.copy_(rays0)
+        srt.trace_batch_device(model, nrays, rays.data_ptr(), P, log.data_ptr(), log_cap, summary.data_ptr(), counters.data_ptr(), stream.cuda_stream)
     torch.cuda.synchronize()
     c = counters.cpu().numpy()
     if c[3] != 0:
         raise SystemExit("trajectory log overflowed in the bench (%d rays dropped)" % c[3])
-    accepted_per_step, attempts_per_step, rows_per_step = int(c[1]), int(c[2]), int(c[0])
+    accepted, attempts, rows, ff = int(c[1]), int(c[2]), int(c[0]), int(c[5])
 
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(C.local_rank)
     sampler.start()
     launches0 = srt.launch_count()
     evs = []
     barrier()
-    for _ in range(args.steps):
-        flush.zero_()  # L2 flush, outside the per-step event pair
+    for _ in range(steps):
+        C.flush.zero_()  # L2 flush, outside the per-step event pair
         rays.copy_(rays0)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
@@ -247,92 +325,186 @@ def main():
     kernel_ms = sum(a.elapsed_time(b) for a, b in evs)
     sampler.stop_flag = True
     t_dev = torch.tensor([kernel_ms], dtype=torch.float64, device=dev)
-    if world > 1:
+    tot = torch.tensor([accepted * steps, attempts * steps, rows * steps, ff * steps, launches], dtype=torch.float64, device=dev)
+    if C.world > 1:
         dist.all_reduce(t_dev, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot)
     kernel_ms_max = float(t_dev.item())
-    total_accepted = accepted_per_step * args.steps * world  # every rank traces a sweep of the same size; counts differ by <1 %
-    acc_t = torch.tensor([accepted_per_step * args.steps, attempts_per_step * args.steps, rows_per_step * args.steps], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(acc_t)
-    total_accepted, total_attempts, total_rows = [float(v) for v in acc_t.tolist()]
-    value = total_accepted / (kernel_ms_max * 1e-3)
+    total_accepted, total_attempts, total_rows, total_ff, total_launches = [float(v) for v in tot.tolist()]
+    secs = kernel_ms_max * 1e-3
+    summary_h = summary.cpu().numpy()
+    del log
 
-    # ---- end to end through the C ABI with host buffers
-    e2e_value, h2d, d2h = None, 0, 0
-    if not args.no_e2e:
-        e2e_steps = max(1, min(args.steps, 3))
-        res = srt.raytracer_run(model, pos0, dir0.copy(), w0, outputper=outputper, **params)  # warm-up (allocations)
-        d2h = res.total_rows * 160 + nrays * (srt.SUMMARY_WORDS * 8 + 4 + 56) + 64
-        h2d = nrays * 56 + nrays * 8
-        res.close()
+    # ---- end to end: the sharded reference-facing call with host buffers, gather on rank 0 inside the timed region
+    e2e = {"value": None, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    if e2e_steps > 0:
+        def one():
+            res = shard.raytracer_run_sharded(model, pos0, dir0.copy(), w0, C.rank, C.world, C.host_group, outputper=outputper, **params)
+            acc = rws = 0
+            if C.rank == 0:
+                acc, rws = res.accepted_steps, res.total_rows
+                touched = 0.0
+                for r in range(0, nglobal, max(1, nglobal // 512)):  # the gathered rows are readable on rank 0
+                    rr = res.rows(r)
+                    if len(rr):
+                        touched += float(rr[-1, 0])
+            res.close()
+            return acc, rws
+
+        one()  # warm-up (page-locked row buffers are created once and pooled)
         barrier()
         t0 = time.perf_counter()
-        e2e_acc = 0
+        acc = rws = 0
         for _ in range(e2e_steps):
-            res = srt.raytracer_run(model, pos0, dir0.copy(), w0, outputper=outputper, **params)
-            e2e_acc += res.accepted_steps
-            res.close()
+            a, r_ = one()
+            acc += a
+            rws = r_
         torch.cuda.synchronize()
-        t_e2e = time.perf_counter() - t0
-        t_e = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
-        a_e = torch.tensor([float(e2e_acc)], dtype=torch.float64, device=dev)
-        if world > 1:
+        t_e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if C.world > 1:
             dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
-            dist.all_reduce(a_e)
-        e2e_value = float(a_e.item()) / float(t_e.item())
+        if C.rank == 0:
+            e2e = {"value": acc / float(t_e.item()), "unit": UNIT, "h2d_bytes_per_step": int(nglobal * 56),
+                   "d2h_bytes_per_step": int(rws * 160 + nglobal * (srt.SUMMARY_WORDS * 8 + 4 + 56) + 64 * C.world),
+                   "gather": "per-ray records (256 B) over gloo, rows mapped from the owners' shared-memory segments" if C.world > 1 else "single process"}
 
-    # ---- roofline of the dominant kernel (srt_trace_kernel): FP64 pipe
-    peak_fma = srt.fp64_peak(True) / 1e3   # TFLOP/s
-    peak_nofma = srt.fp64_peak(False) / 1e3
-    rejected = attempts_per_step - accepted_per_step
-    flops_per_launch = accepted_per_step * FLOPS_ACCEPTED + rejected * FLOPS_REJECTED
-    avg_launch_s = (kernel_ms / args.steps) * 1e-3
-    achieved = flops_per_launch / avg_launch_s / 1e12
+    out = None
+    if C.rank == 0:
+        wm = work_model()
+        fa, fr = wm[kind]["accepted"], wm[kind]["rejected"]
+        integrated = accepted - ff  # fast-forwarded NaN steps cost one addition each: not in the work model
+        flops_per_launch = integrated * fa + (attempts - accepted) * fr
+        avg_launch_s = (kernel_ms / steps) * 1e-3
+        achieved = flops_per_launch / avg_launch_s / 1e12
+        hbm_ach = (rows * ROW_BYTES + nrays * (56 + srt.SUMMARY_WORDS * 8)) / avg_launch_s / 1e9
+        ki = model.kernel_info(nrays)
+        roofline = {"bound": "fp64", "achieved": achieved, "peak": C.peak_fma, "unit": "TFLOP/s", "frac": achieved / C.peak_fma,
+                    "traffic": traffic_from_profiles(name, ki),
+                    "bound_note": "FP64 (non-tensor) pipe: the path is scalar FP64 with no dense contraction and ~1e-4 of HBM bandwidth, so neither 'hbm' nor 'tensor' applies",
+                    "peak_source": "DFMA micro-kernel measured live (srt_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
+                    "peak_no_fma": C.peak_nofma, "frac_no_fma": achieved / C.peak_nofma,
+                    "work_model": "%.3g flop-eq per integrated accepted RK45 step + %.3g per rejected attempt (%s); fast-forwarded NaN steps count 0" % (fa, fr, wm.get("source", "")),
+                    "hbm": {"achieved": hbm_ach, "peak": C.hbm_peak, "unit": "GB/s", "frac": hbm_ach / C.hbm_peak, "of": C.hbm_of}}
+        out = {"value": total_accepted / secs, "ms_per_step": kernel_ms_max / steps, "steps": steps, "warmup": warmup,
+               "rays_per_sec": float(nglobal) * steps / secs, "attempted_steps_per_sec": total_attempts / secs,
+               "value_without_fastforwarded_nan_steps": (total_accepted - total_ff) / secs,
+               "fastforwarded_nan_steps_per_sweep": total_ff / steps,
+               "accepted_steps_per_sweep": total_accepted / steps, "e2e": e2e, "gpu_launches": int(total_launches), "clocks": sampler.result(),
+               "roofline": roofline, "kernel": ki, "config": config_dict(C.world, name, nrays, nglobal)}
+        if with_cpu:
+            threads = os.cpu_count() or 1
+            n_all, n_one, short = cpu_sizes(threads)
+            modes, (cidx, crun) = cpu_baselines(kind, model_path, 1 if kind == "grid" else 0, pos0, dir0, w0, params, n_all, n_one, threads, short)
+            d = modes["dedup_all_cores"]
+            out["cpu_baseline"] = {"value": d["value"], "unit": UNIT, "cores": d["cores"], "kind": "port",
+                                   "sample": "%d whole rays strided out of the launch set, %.1f s, one dynamic ray queue; de-duplicated evaluation order (same algorithmic work as "
+                                             "the GPU) of the C++ restatement of the reference" % (d["rays"], d["seconds"]),
+                                   "modes": modes}
+            # the same rays on the GPU (this rank's shard holds those with shard_of == 0), bit for bit
+            mine = np.searchsorted(idx, cidx)
+            ok = (mine < len(idx)) & (idx[np.minimum(mine, len(idx) - 1)] == cidx)
+            sel = {k: v[ok] if isinstance(v, np.ndarray) else v for k, v in crun.items()}
+            out["parity_checked_rays"], out["parity_mismatches"] = parity_check(summary_h, mine[ok], sel)
+    model.close()
+    return out
+
+
+def traffic_from_profiles(name, ki):
+    """DRAM bytes per launch of the trace kernel on this workload, from a committed ncu pass -- only if that pass
+    measured the kernel this library would launch now (same mode, block, registers, local bytes), else null."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        e = t.get(name)
+        if e and all(e["kernel"].get(k) == ki.get(k) for k in ("mode", "block", "regs", "local_bytes")):
+            return e["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    return None
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg")
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="c2 is the bench line; the others run as `extra`")
+    ap.add_argument("--extras", default="auto", help="auto (c3, c4_100k, and c4 at 8 GPUs), none, or a comma list of workloads")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import stanford_raytracer_b200 as srt
+    from stanford_raytracer_b200 import shard
+
+    C = Ctx()
+    C.srt, C.shard = srt, shard
+    C.world = int(os.environ.get("WORLD_SIZE", "1"))
+    C.rank = int(os.environ.get("RANK", "0"))
+    C.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: libsrt has no CPU path")
+    torch.cuda.set_device(C.local_rank)
+    C.host_group = None
+    if C.world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", C.local_rank))
+        C.host_group = shard.host_group(C.world)
+    C.dev = torch.device("cuda", C.local_rank)
+    srt.init(C.local_rank)
+    C.flush = torch.empty(256 << 20, dtype=torch.uint8, device=C.dev)
+    C.peak_fma = srt.fp64_peak(True) / 1e3   # TFLOP/s
+    C.peak_nofma = srt.fp64_peak(False) / 1e3
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    hbm_peak = peaks.get("hbm_gbs", 6650.0)
-    hbm_ach = (rows_per_step * ROW_BYTES + nrays * (56 + srt.SUMMARY_WORDS * 8)) / avg_launch_s / 1e9
-    traffic = None
-    try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r1j_traffic.json")))
-        if tj.get("workload") == wl and model.kernel_info(nrays)["mode"] == "team8":
-            traffic = tj["dram_bytes_per_launch"]  # bytes per launch of this kernel on this workload, from the committed ncu pass
-    except Exception:
-        pass
-    roofline = {"bound": "fp64", "achieved": achieved, "peak": peak_fma, "unit": "TFLOP/s", "frac": achieved / peak_fma, "traffic": traffic,
-                "bound_note": "FP64 (non-tensor) pipe: the path is scalar FP64 with no dense contraction and ~1e-4 of HBM bandwidth, so neither 'hbm' nor 'tensor' applies",
-                "peak_source": "DFMA micro-kernel measured live (srt_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
-                "peak_no_fma": peak_nofma, "frac_no_fma": achieved / peak_nofma,
-                "work_model": "%.2g flop-eq per accepted RK45 step + %.2g per rejected attempt (SURVEY.md 8d)" % (FLOPS_ACCEPTED, FLOPS_REJECTED),
-                "hbm": {"achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak,
-                        "of": "measured" if "hbm_gbs" in peaks else "fallback"}}
+    C.hbm_peak, C.hbm_of = peaks.get("hbm_gbs", 6650.0), ("measured" if "hbm_gbs" in peaks else "fallback")
 
-    if rank == 0:
-        cpu = None
-        if not args.no_cpu_baseline:
-            threads = os.cpu_count() or 1
-            nsample = max(threads, 256)  # ~12 s of CPU work on 16 cores
-            if WORKLOADS[wl][4] == "grid":
-                nsample = threads
-                a, t = cpu_reference_run(pos0, dir0, w0, dict(params, maxsteps=300), _GRID_CACHE + ".%d" % local_rank, nsample, threads, "grid", 1)
-            else:
-                a, t = cpu_reference_run(pos0, dir0, w0, params, cfg, nsample, threads)
-            cpu = {"value": a / t, "unit": UNIT, "cores": threads, "kind": "port",
-                   "sample": "%d rays strided out of the sweep%s, %.1f s, faithful call structure of the reference" % (nsample, " (first 300 steps of each)" if WORKLOADS[wl][4] == "grid" else "", t)}
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": kernel_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-                "data": "synthetic", "config": config_dict(world, wl, nrays),
-                "rays_per_sec": float(nrays) * world * args.steps / (kernel_ms_max * 1e-3),
-                "attempted_steps_per_sec": total_attempts / (kernel_ms_max * 1e-3),
-                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
-                "gpu_launches": int(launches), "clocks": sampler.result(), "roofline": roofline, "cpu_baseline": cpu,
-                "kernel": model.kernel_info(nrays)}
+    t_start = time.perf_counter()
+    e2e_steps = 0 if args.no_e2e else max(1, min(args.steps, 3))
+    with_cpu = not args.no_cpu_baseline
+
+    def c2_cpu(threads):
+        return max(threads, 256), max(8, 256 // max(threads, 1)), {}
+
+    def c3_cpu(threads):  # the faithful statement of a gridded ray is a dense 64x64 product per species and query: shortened rays there
+        return max(threads, 64), 4, {"maxsteps": 300}
+
+    main_out = measure(C, args.workload, args.steps, args.warmup, e2e_steps, with_cpu, c3_cpu if WORKLOADS[args.workload][4] == "grid" else c2_cpu)
+    extras = {}
+    if args.extras != "none":
+        names = ["c3", "c4_100k"] + (["c4"] if C.world >= 8 else []) if args.extras == "auto" else [s for s in args.extras.split(",") if s]
+        for nm in names:
+            if nm == args.workload or nm not in WORKLOADS:
+                continue
+            o = measure(C, nm, 2, 1, 0 if args.no_e2e else 1, with_cpu and nm == "c3", c3_cpu if WORKLOADS[nm][4] == "grid" else c2_cpu)
+            if C.rank == 0:
+                extras[nm] = o
+    if C.rank == 0:
+        m = main_out
+        line = {"metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": C.world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": m["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "config": m["config"], "rays_per_sec": m["rays_per_sec"], "attempted_steps_per_sec": m["attempted_steps_per_sec"],
+                "value_without_fastforwarded_nan_steps": m["value_without_fastforwarded_nan_steps"],
+                "e2e": m["e2e"], "gpu_launches": m["gpu_launches"], "clocks": m["clocks"], "roofline": m["roofline"],
+                "cpu_baseline": m.get("cpu_baseline"), "kernel": m["kernel"],
+                "parity_checked_rays": m.get("parity_checked_rays", 0) + sum(e.get("parity_checked_rays", 0) for e in extras.values()),
+                "parity_mismatches": m.get("parity_mismatches", 0) + sum(e.get("parity_mismatches", 0) for e in extras.values()),
+                "extra": extras, "bench_wall_s": time.perf_counter() - t_start}
         print(json.dumps(line))
-    if world > 1:
+        bad = line["parity_mismatches"]
+    else:
+        bad = 0
+    if C.world > 1:
+        dist.barrier()
         dist.destroy_process_group()
+    if bad:
+        raise SystemExit("bench: %d rays of the timed sweep differ from the CPU oracle" % bad)
 
 
 if __name__ == "__main__":

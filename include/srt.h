@@ -1,4 +1,4 @@
-/* srt.h -- C ABI of libsrt.so: batched Haselgrove ray integration on one B200.
+/* srt.h -- C ABI of libsrt.so: batched Haselgrove ray integration on the B200s of one box.
  *
  * The reference has no C ABI; what this library replaces is the Fortran call
  *   call raytracer_run(pos,time,vprel,vgrel,n,B0,qs,ms,Ns,nus,stopcond, pos0,dir0,w,
@@ -14,10 +14,14 @@
  *
  * Conventions: plain C types; every call returns 0 or a negative SRT_E_* code (never
  * exits); input arrays are caller-owned; the result object is library-owned until
- * srt_result_free().  A call uses the CUDA device selected by srt_init() for the
- * calling process (one process per GPU; rays shard across processes by index, no
- * collective).  There is no CPU fallback: without a CUDA device every compute call
- * fails with SRT_E_NODEVICE.
+ * srt_result_free().  srt_trace_batch() spreads the rays of a batch over every device
+ * selected by srt_init() / srt_init_devices() (ray i on device i mod n, one host thread
+ * and one model replica per device, no exchange between devices: SURVEY.md 8b "blocking;
+ * internally multi-GPU"); the other compute calls use the calling thread's current
+ * device.  Under a one-process-per-GPU launcher each process selects its own device
+ * and rays shard across processes by index (stanford_raytracer_b200/shard.py).  There
+ * is no CPU fallback: without a CUDA device every compute call fails with
+ * SRT_E_NODEVICE.
  *
  * INTEGRATION.md shows the ISO_C_BINDING interface block and the patched driver loop.
  */
@@ -61,6 +65,11 @@ typedef struct srt_run_params {
 
 /* Selects the CUDA device of this process.  device < 0: keep the current one. */
 int srt_init(int device);
+/* Selects the devices srt_trace_batch() spreads a batch over (the reference's one-ray-at-a-time loop,
+ * driver:1143-1232, becomes one call that uses the whole box).  ndevices <= 0: every visible device.
+ * The first one becomes the calling thread's current device. */
+int srt_init_devices(const int* devices, int ndevices);
+int srt_device_count(void); /* devices selected by the last srt_init / srt_init_devices */
 const char* srt_strerror(int code);
 const char* srt_last_cuda_error(void);
 
@@ -84,6 +93,12 @@ int64_t srt_result_nrays(const srt_result* r);
 int64_t srt_result_total_rows(const srt_result* r);     /* rows held (after outputper decimation) */
 int64_t srt_result_accepted_steps(const srt_result* r); /* sum over rays of (rows the reference would hold - 1) */
 int64_t srt_result_attempts(const srt_result* r);       /* accepted + rejected + cone-refined attempts */
+/* Of the accepted steps, those of rays whose state had become all-NaN: the reference steps such a ray on to
+ * maxsteps / tmax, every row equal to the last but for t = t + dt (tests/test_nan_rays_cpu.py); the kernels
+ * write those rows without integrating (srt_nan_fastforward).  Rates quoted "without fast-forwarded steps"
+ * subtract this count. */
+int64_t srt_result_fastforwarded_steps(const srt_result* r);
+int srt_result_devices(const srt_result* r);            /* devices the batch ran on */
 /* per ray */
 int64_t srt_result_nrows(const srt_result* r, int64_t ray);       /* rows held for this ray = ceil(nsteps/outputper) */
 int64_t srt_result_nsteps(const srt_result* r, int64_t ray);      /* size(time) in the reference */
@@ -94,7 +109,17 @@ int srt_result_copy_ray(const srt_result* r, int64_t ray, double* rows /*[nrows]
 int srt_result_ray_view(const srt_result* r, int64_t ray, const double** rows, int64_t* nrows);
 /* endpoint summary for all rays (any pointer may be NULL) */
 int srt_result_summary(const srt_result* r, double* last_row /*[nrays][20]*/, int64_t* nsteps, int64_t* nrejected, int32_t* stopcond);
+/* Where the rows live: a batch returns one row buffer ("chunk") per device and wave.  With srt_set_rows_shm() the
+ * chunks are POSIX shared-memory segments (page-locked for the D2H copy), so that the gathering process of a
+ * one-process-per-GPU run maps the rows of the other ranks instead of receiving a copy (shard.py). */
+int srt_set_rows_shm(const char* prefix /* NULL or "": ordinary pinned memory */);
+int srt_result_chunk_count(const srt_result* r);
+int srt_result_chunk_info(const srt_result* r, int chunk, char* shm_name, int name_capacity, int64_t* nrows, const double** rows);
+/* per ray: chunk, first row inside the chunk, rows held (arrays of nrays entries; any may be NULL) */
+int srt_result_ray_location(const srt_result* r, int64_t nrays, int32_t* chunk, int64_t* first_row, int64_t* nrows);
 void srt_result_free(srt_result* r);
+/* frees every buffer the library caches between calls (device scratch, staging, pooled row buffers) */
+int srt_release_scratch(void);
 
 /* Device-resident variant (pipelines, bench `value`): inputs already in HBM, outputs stay there.
  *   d_rays      [7][nrays] structure-of-arrays: pos0 x,y,z; dir0 x,y,z; w0   (dir0 rows are updated in place)
@@ -102,7 +127,8 @@ void srt_result_free(srt_result* r);
  *   d_summary   [nrays][24]: words 0..19 last row, 20 nsteps, 21 stopcond, 22 rejected+cone attempts, 23 flags
  *               (integers stored as doubles)
  *   d_counters  [8] uint64: log rows used, accepted steps, attempts, rays dropped because the log was full,
- *               ray-queue head, 3 spare (zeroed by the call)
+ *               ray-queue head, fast-forwarded NaN steps (included in accepted and attempts), block rounds sum / max
+ *               (zeroed by the call)
  * stream: a cudaStream_t (NULL = default stream).  Asynchronous: returns after the launch. */
 int srt_trace_batch_device(const srt_model* m, int64_t nrays, double* d_rays, const srt_run_params* p, double* d_log, int64_t log_capacity,
                            double* d_summary, uint64_t* d_counters, void* stream);

@@ -55,7 +55,13 @@ def lib():
     L.srt_model_species.argtypes = [vp, C.POINTER(i), vp, vp, vp]
     L.srt_model_eval.argtypes = [vp, i64, vp, vp]
     L.srt_trace_batch.argtypes = [vp, i64, vp, vp, vp, C.POINTER(RunParams), C.POINTER(vp)]
-    for name in ("nrays", "total_rows", "accepted_steps", "attempts"):
+    L.srt_init_devices.argtypes = [vp, i]
+    L.srt_set_rows_shm.argtypes = [C.c_char_p]
+    L.srt_result_chunk_count.argtypes = [vp]
+    L.srt_result_chunk_info.argtypes = [vp, i, C.c_char_p, i, C.POINTER(i64), C.POINTER(vp)]
+    L.srt_result_ray_location.argtypes = [vp, i64, vp, vp, vp]
+    L.srt_result_devices.argtypes = [vp]
+    for name in ("nrays", "total_rows", "accepted_steps", "attempts", "fastforwarded_steps"):
         f = getattr(L, "srt_result_" + name)
         f.restype = i64
         f.argtypes = [vp]
@@ -96,7 +102,23 @@ def _check(rc, what):
 
 
 def init(device=-1):
+    """Selects the CUDA device of this process (device < 0: the current one)."""
     _check(lib().srt_init(device), "srt_init")
+
+
+def init_devices(devices=None):
+    """Selects the devices raytracer_run spreads a batch over (None: every visible device)."""
+    if devices is None:
+        _check(lib().srt_init_devices(None, 0), "srt_init_devices")
+    else:
+        a = np.ascontiguousarray(devices, dtype=np.int32)
+        _check(lib().srt_init_devices(_ptr(a), len(a)), "srt_init_devices")
+    return lib().srt_device_count()
+
+
+def set_rows_shm(prefix):
+    """Row buffers of the following batches in POSIX shared memory `/<prefix>.<pid>.<n>` (None: pinned memory)."""
+    _check(lib().srt_set_rows_shm(prefix.encode() if prefix else None), "srt_set_rows_shm")
 
 
 def _ptr(a):
@@ -183,6 +205,8 @@ class BatchResult:
         self.total_rows = L.srt_result_total_rows(handle)
         self.accepted_steps = L.srt_result_accepted_steps(handle)
         self.attempts = L.srt_result_attempts(handle)
+        self.fastforwarded_steps = L.srt_result_fastforwarded_steps(handle)
+        self.ndevices = L.srt_result_devices(handle)
         self.last_row = np.empty((self.nrays, ROW_DOUBLES))
         self.nsteps = np.empty(self.nrays, dtype=np.int64)
         self.nrejected = np.empty(self.nrays, dtype=np.int64)
@@ -200,6 +224,21 @@ class BatchResult:
         out = np.empty((n, ROW_DOUBLES))
         _check(L.srt_result_copy_ray(self._h, ray, _ptr(out)), "srt_result_copy_ray")
         return out
+
+    def chunks(self):
+        """[(shm_name or "", nrows, address)] of the row buffers, and per ray (chunk, first_row, nrows)."""
+        L = lib()
+        out = []
+        for c in range(L.srt_result_chunk_count(self._h)):
+            name = C.create_string_buffer(96)
+            n, p = C.c_int64(), C.c_void_p()
+            _check(L.srt_result_chunk_info(self._h, c, name, 96, C.byref(n), C.byref(p)), "srt_result_chunk_info")
+            out.append((name.value.decode(), n.value, p.value))
+        chunk = np.empty(self.nrays, dtype=np.int32)
+        first = np.empty(self.nrays, dtype=np.int64)
+        nrows = np.empty(self.nrays, dtype=np.int64)
+        _check(L.srt_result_ray_location(self._h, self.nrays, _ptr(chunk), _ptr(first), _ptr(nrows)), "srt_result_ray_location")
+        return out, chunk, first, nrows
 
     def __getitem__(self, ray):
         L = lib()

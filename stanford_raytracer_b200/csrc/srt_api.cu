@@ -3,6 +3,10 @@
 // This unit holds the one-thread-per-ray trace kernel: 256-thread blocks (one per SM, <= 255 registers)
 // that start every attempt together (SRT_BLOCK_SYNC), elementary functions inlined (SRT_INLINE_MATH in
 // build.py).  The team-of-8 kernel is compiled separately (srt_team_tu.cu).
+//
+// Devices.  The library drives every CUDA device selected by srt_init() / srt_init_devices(): one context per
+// device (stream, scratch buffers, the state of that device's __constant__ model copies), one replica of each
+// model per device (grid arrays, built lazily), one host thread per device inside srt_trace_batch().
 #ifndef SRT_BLOCK_THREADS
 #define SRT_BLOCK_THREADS 256
 #endif
@@ -20,8 +24,11 @@
 #include "../../include/srt.h"
 
 #include <atomic>
+#include <map>
+#include <memory>
 #include <mutex>
 #include <new>
+#include <thread>
 #include <vector>
 
 static_assert(SRT_ROW_DOUBLES == 20, "row layout");
@@ -31,9 +38,7 @@ namespace {
 
 thread_local char g_cuda_err[512] = "";
 std::atomic<long long> g_launches{0};
-std::mutex g_model_mutex;  // c_srt_model is one __constant__ object: launches with different models are serialised
-int g_device = -1;
-int g_num_sms = 0;
+std::atomic<uint64_t> g_model_serial{0};
 
 int cuda_fail(cudaError_t e, const char* what) {
   snprintf(g_cuda_err, sizeof g_cuda_err, "%s: %s", what, cudaGetErrorString(e));
@@ -45,8 +50,75 @@ int cuda_fail(cudaError_t e, const char* what) {
     if (e_ != cudaSuccess) return cuda_fail(e_, #call);    \
   } while (0)
 
-int ensure_device() {
-  if (g_device >= 0) return SRT_OK;
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return SRT_OK;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    cap = bytes;
+    return SRT_OK;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+struct PinBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return SRT_OK;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMallocHost(&p, bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMallocHost");
+    cap = bytes;
+    return SRT_OK;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+// Everything the library keeps per CUDA device.
+struct DevCtx {
+  int dev = -1;
+  int num_sms = 0;
+  cudaStream_t stream = nullptr;  // the host-buffer path's stream on this device
+  // The model is read by the kernels from ONE __constant__ object per translation unit and device ([0] this unit:
+  // thread kernel + eval kernel, [1] the team unit).  `resident` is the serial of the model it holds; `readers` are
+  // events recorded after every launch that reads it.  A launch with the same model uploads nothing; a launch with
+  // another model first makes its stream wait for every earlier reader, so a kernel in flight on any stream never
+  // sees the symbol change under it.
+  std::mutex sym_mutex;
+  uint64_t resident[2] = {0, 0};
+  std::vector<cudaEvent_t> readers[2];
+  // scratch of srt_trace_batch on this device (one host-buffer batch at a time per device)
+  std::mutex batch_mutex;
+  DevBuf rays, log, sorted, summary, counters, nlogged, offsets;
+  PinBuf rays_h, summary_h, small_h;
+};
+
+std::mutex g_dev_mutex;
+std::vector<std::unique_ptr<DevCtx>> g_ctx;  // every device ever used by this process
+std::vector<DevCtx*> g_active;               // the devices srt_trace_batch() spreads a batch over
+
+DevCtx* ctx_for_device(int dev) {
+  std::lock_guard<std::mutex> lk(g_dev_mutex);
+  for (auto& c : g_ctx)
+    if (c->dev == dev) return c.get();
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return nullptr;
+  std::unique_ptr<DevCtx> c(new DevCtx());
+  c->dev = dev;
+  c->num_sms = prop.multiProcessorCount;
+  g_ctx.push_back(std::move(c));
+  return g_ctx.back().get();
+}
+
+// the context of the calling thread's current device; SRT_E_NODEVICE without one
+int current_ctx(DevCtx** out) {
   int n = 0;
   cudaError_t e = cudaGetDeviceCount(&n);
   if (e != cudaSuccess || n == 0) {
@@ -55,10 +127,23 @@ int ensure_device() {
   }
   int dev = 0;
   CK(cudaGetDevice(&dev));
-  cudaDeviceProp prop;
-  CK(cudaGetDeviceProperties(&prop, dev));
-  g_device = dev;
-  g_num_sms = prop.multiProcessorCount;
+  DevCtx* c = ctx_for_device(dev);
+  if (!c) return cuda_fail(cudaGetLastError(), "cudaGetDeviceProperties");
+  *out = c;
+  return SRT_OK;
+}
+
+// the devices a host-buffer batch runs on: what srt_init*/ selected, else the current device
+int active_devices(std::vector<DevCtx*>& out) {
+  {
+    std::lock_guard<std::mutex> lk(g_dev_mutex);
+    out = g_active;
+  }
+  if (!out.empty()) return SRT_OK;
+  DevCtx* c = nullptr;
+  int rc = current_ctx(&c);
+  if (rc) return rc;
+  out.push_back(c);
   return SRT_OK;
 }
 
@@ -74,35 +159,56 @@ eval_kernel_t pick_eval(const SrtModel& M) {
   return M.use_igrf ? srt_eval_kernel<SRT_DENS_GRID, 1> : srt_eval_kernel<SRT_DENS_GRID, 0>;
 }
 
+// ---- set-up kernel of the gridded model: tricubic_compute_finite_difference_derivatives (libtricubic.f95:722-793).
+// One pass = array slot `src` -> slot `dst` of every node record along `axis` (0: x, 1: y, 2: z): one-sided
+// differences at the two ends, centred `(f(i+1) - f(i-1)) / 2 / h` inside; `enabled` = the axis (and, for the mixed
+// derivatives, every axis involved) has more than two nodes, else the slot is zero.  One thread per (node, species);
+// a pass reads only slot `src` and writes only slot `dst`, so there is no hazard inside a launch.
+__global__ void srt_fd_kernel(double* __restrict__ nodes, int nx, int ny, int nz, int nspec, int src, int dst, int axis, double h, int enabled) {
+  const long long total = (long long)nx * ny * nz * 4;
+  for (long long id = blockIdx.x * (long long)blockDim.x + threadIdx.x; id < total; id += (long long)gridDim.x * blockDim.x) {
+    const int s = (int)(id & 3);
+    if (s >= nspec) continue;
+    const long long node = id >> 2;
+    const int i = (int)(node % nx), j = (int)((node / nx) % ny), k = (int)(node / ((long long)nx * ny));
+    double* rec = nodes + node * 32;
+    if (!enabled) { rec[4 * dst + s] = 0.0; continue; }
+    const int c = axis == 0 ? i : (axis == 1 ? j : k);
+    const int m = axis == 0 ? nx : (axis == 1 ? ny : nz);
+    const long long stride = (axis == 0 ? 1ll : (axis == 1 ? (long long)nx : (long long)nx * ny)) * 32;
+    double v;
+    if (c == 0) v = (rec[stride + 4 * src + s] - rec[4 * src + s]) / h;
+    else if (c == m - 1) v = (rec[4 * src + s] - rec[-stride + 4 * src + s]) / h;
+    else v = (rec[stride + 4 * src + s] - rec[-stride + 4 * src + s]) / 2.0 / h;
+    rec[4 * dst + s] = v;
+  }
+}
+
 }  // namespace
 
-struct srt_model {
-  SrtModel M;
-  double nus[SRT_NSPEC];
-  // device copies of the grid (modelnum 3)
+// device copies of the grid arrays of a model (modelnum 3) on one device
+struct GridReplica {
   double* d_nodes = nullptr;
   double* d_axes = nullptr;
-  double* d_coef = nullptr;  // per-cell tricubic coefficients
-  int blocks_per_sm[2] = {0, 0};  // [thread-per-ray, team-of-8]
-  int grid[2] = {0, 0};
+  double* d_coef = nullptr;  // per-cell tricubic coefficients (NULL: on-the-fly path, SRT_GRID_COEF=0)
 };
 
-struct srt_result {
-  int64_t nrays = 0;
-  int outputper = 1;
-  std::vector<double> summary;    // [nrays][SRT_SUMMARY_WORDS]
-  std::vector<uint64_t> offsets;  // first row of each ray in `rows`
-  std::vector<uint32_t> nheld;    // rows held per ray
-  double* rows = nullptr;         // pinned host memory, [total_rows][20]
-  size_t rows_bytes = 0;          // capacity of `rows`
-  uint64_t total_rows = 0;
-  uint64_t accepted = 0, attempts = 0;
+struct srt_model {
+  SrtModel M;  // grid pointers are filled per device at launch time
+  uint64_t serial = 0;
+  double nus[SRT_NSPEC];
+  // host copy of the grid file: f only (derivative slots zero) unless the file carried derivatives
+  std::vector<double> h_nodes, h_axes;
+  bool file_has_derivatives = false;
+  bool use_coef = true;
+  std::mutex replica_mutex;
+  std::map<int, GridReplica> replicas;  // by device
+  std::map<int, int> blocks_per_sm;     // thread-per-ray kernel, by device
 };
 
 namespace {
 
-// 0 = one thread per ray, 1 = team of 8 lanes per ray.  SRT_KERNEL=thread|team overrides; by default
-// the team form is used while the batch cannot fill the machine with one thread per ray.
+// 0 = one thread per ray, 1 = team of 8 lanes per ray.  SRT_KERNEL=thread|team overrides.
 int pick_mode(const srt_model* m, long long nrays) {
   const char* env = getenv("SRT_KERNEL");
   if (env && !strcmp(env, "thread")) return 0;
@@ -115,24 +221,26 @@ int pick_mode(const srt_model* m, long long nrays) {
 }
 
 // persistent launch geometry of a batch: mode (0 thread / 1 team), block, grid = one resident wave at most
-int launch_config(srt_model* m, long long nrays, int* mode_out, int* block_out, int* grid_out, int* blocks_per_sm_out) {
-  if (!m->grid[0]) {
-    int nb = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pick_trace(m->M), SRT_BLOCK_THREADS, 0));
-    if (nb < 1) nb = 1;
-    m->blocks_per_sm[0] = nb;
-    m->grid[0] = nb * g_num_sms;
-  }
+int launch_config(DevCtx* c, srt_model* m, long long nrays, int* mode_out, int* block_out, int* grid_out, int* blocks_per_sm_out) {
   const int mode = pick_mode(m, nrays);
-  int block = SRT_BLOCK_THREADS, nb = m->blocks_per_sm[0];
+  int block = SRT_BLOCK_THREADS, nb = 1;
   if (mode) {
-    block = srt_team_block_threads(nrays, g_num_sms);
+    block = srt_team_block_threads(nrays, c->num_sms);
     CK(srt_team_occupancy(m->M, block, &nb));
-    if (nb < 1) nb = 1;
+  } else {
+    std::lock_guard<std::mutex> lk(m->replica_mutex);
+    auto it = m->blocks_per_sm.find(c->dev);
+    if (it == m->blocks_per_sm.end()) {
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pick_trace(m->M), SRT_BLOCK_THREADS, 0));
+      m->blocks_per_sm[c->dev] = nb;
+    } else {
+      nb = it->second;
+    }
   }
+  if (nb < 1) nb = 1;
   const long long lanes_per_ray = mode ? 8 : 1;
   long long blocks_needed = (nrays * lanes_per_ray + block - 1) / block;
-  long long resident = (long long)nb * g_num_sms;
+  long long resident = (long long)nb * c->num_sms;
   int grid = (int)(blocks_needed < resident ? blocks_needed : resident);
   if (grid < 1) grid = 1;
   *mode_out = mode; *block_out = block; *grid_out = grid;
@@ -140,11 +248,9 @@ int launch_config(srt_model* m, long long nrays, int* mode_out, int* block_out, 
   return SRT_OK;
 }
 
-// upload the model and launch the persistent trace kernel on `stream`; caller holds g_model_mutex
 // multiplier of the queue permutation (srt_queue_ray): the integer nearest nrays/golden ratio that is coprime to nrays
 unsigned long long ray_order_mul(long long nrays) {
-  const char* e = getenv("SRT_RAY_ORDER");
-  if ((e && atoi(e) == 0) || nrays < 4) return 1ull;
+  if (nrays < 4) return 1ull;
   unsigned long long n = (unsigned long long)nrays, mul = (unsigned long long)((double)nrays * 0.6180339887498949);
   for (;; ++mul) {
     unsigned long long a = n, b = mul % n;
@@ -153,24 +259,143 @@ unsigned long long ray_order_mul(long long nrays) {
   }
 }
 
-int launch_trace(srt_model* m, const SrtRunParams& P, const SrtBatch& B0, cudaStream_t stream) {
+// The grid arrays of `m` on device c->dev (current device of the caller): upload of the node records, the
+// finite-difference derivative passes and the per-cell coefficient table, once per device.
+int ensure_replica(DevCtx* c, srt_model* m, GridReplica* out) {
+  *out = GridReplica();
+  if (m->M.density != SRT_DENS_GRID) return SRT_OK;
+  std::lock_guard<std::mutex> lk(m->replica_mutex);
+  auto it = m->replicas.find(c->dev);
+  if (it != m->replicas.end()) { *out = it->second; return SRT_OK; }
+  GridReplica r;
+  const SrtGrid& g = m->M.grid;
+  const size_t nb = m->h_nodes.size() * sizeof(double), ax = m->h_axes.size() * sizeof(double);
+  const size_t ncells = (m->use_coef && g.nx > 1 && g.ny > 1 && g.nz > 1) ? srt_grid_cell_count(g) : 0;
+  if (cudaMalloc(&r.d_nodes, nb) != cudaSuccess || cudaMalloc(&r.d_axes, ax) != cudaSuccess ||
+      (ncells && cudaMalloc(&r.d_coef, ncells * 256 * sizeof(double)) != cudaSuccess)) {
+    int rc = cuda_fail(cudaGetLastError(), "cudaMalloc(grid)");
+    if (r.d_nodes) cudaFree(r.d_nodes);
+    if (r.d_axes) cudaFree(r.d_axes);
+    return rc;
+  }
+  cudaMemcpy(r.d_nodes, m->h_nodes.data(), nb, cudaMemcpyHostToDevice);
+  cudaMemcpy(r.d_axes, m->h_axes.data(), ax, cudaMemcpyHostToDevice);
+  const long long threads = (long long)g.nx * g.ny * g.nz * 4;
+  const int blocks = (int)((threads + 255) / 256 < (long long)c->num_sms * 16 ? (threads + 255) / 256 : (long long)c->num_sms * 16);
+  if (!m->file_has_derivatives) {
+    // libtricubic.f95:738-790: df/dx, df/dy, df/dz, then the mixed ones from the first derivatives
+    const bool X = g.nx > 2, Y = g.ny > 2, Z = g.nz > 2;
+    const struct { int src, dst, axis; double h; bool on; } pass[7] = {
+        {0, 1, 0, g.delx, X}, {0, 2, 1, g.dely, Y}, {0, 3, 2, g.delz, Z}, {2, 4, 0, g.delx, X && Y},
+        {3, 5, 0, g.delx, X && Z}, {3, 6, 1, g.dely, Y && Z}, {6, 7, 0, g.delx, X && Y && Z}};
+    for (int q = 0; q < 7; ++q) {
+      srt_fd_kernel<<<blocks, 256>>>(r.d_nodes, g.nx, g.ny, g.nz, g.nspec, pass[q].src, pass[q].dst, pass[q].axis, pass[q].h, pass[q].on ? 1 : 0);
+      g_launches++;
+    }
+  }
+  SrtGrid gd = g;
+  gd.nodes = r.d_nodes;
+  gd.coef = nullptr;
+  gd.xs = r.d_axes;
+  gd.ys = r.d_axes + g.nx;
+  gd.zs = r.d_axes + g.nx + g.ny;
+  if (ncells) {
+    long long ct = (long long)ncells * 4;
+    int cb = (int)((ct + 127) / 128 < (long long)c->num_sms * 16 ? (ct + 127) / 128 : (long long)c->num_sms * 16);
+    srt_coef_kernel<<<cb, 128>>>(gd, r.d_coef);
+    g_launches++;
+  }
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e == cudaSuccess) e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    cudaFree(r.d_nodes); cudaFree(r.d_axes);
+    if (r.d_coef) cudaFree(r.d_coef);
+    return cuda_fail(e, "grid set-up");
+  }
+  m->replicas[c->dev] = r;
+  *out = r;
+  return SRT_OK;
+}
+
+// SrtModel as device c->dev sees it
+int device_model(DevCtx* c, srt_model* m, SrtModel* out) {
+  *out = m->M;
+  if (m->M.density == SRT_DENS_GRID) {
+    GridReplica r;
+    int rc = ensure_replica(c, m, &r);
+    if (rc) return rc;
+    out->grid.nodes = r.d_nodes;
+    out->grid.coef = r.d_coef;
+    out->grid.xs = r.d_axes;
+    out->grid.ys = r.d_axes + m->M.grid.nx;
+    out->grid.zs = r.d_axes + m->M.grid.nx + m->M.grid.ny;
+  }
+  return SRT_OK;
+}
+
+// Makes `Md` (serial `serial`) the model of translation unit `tu` on device c->dev for a launch on `stream`.
+// Caller holds c->sym_mutex until it has called symbol_reader() for its launch.
+int symbol_prepare(DevCtx* c, int tu, uint64_t serial, const SrtModel& Md, cudaStream_t stream) {
+  if (c->resident[tu] == serial) return SRT_OK;
+  for (cudaEvent_t ev : c->readers[tu]) {
+    CK(cudaStreamWaitEvent(stream, ev, 0));
+    cudaEventDestroy(ev);  // released once it has completed; the wait above stays valid
+  }
+  c->readers[tu].clear();
+  if (tu == 0) CK(cudaMemcpyToSymbolAsync(c_srt_model, &Md, sizeof(SrtModel), 0, cudaMemcpyHostToDevice, stream));
+  else CK(srt_team_upload_model(Md, stream));
+  c->resident[tu] = serial;
+  // the upload itself must be over before a launch on ANOTHER stream with the same model may read the symbol
+  cudaEvent_t up;
+  CK(cudaEventCreateWithFlags(&up, cudaEventDisableTiming));
+  CK(cudaEventRecord(up, stream));
+  c->readers[tu].push_back(up);
+  return SRT_OK;
+}
+int symbol_reader(DevCtx* c, int tu, cudaStream_t stream) {
+  // a launch on `stream` reads the symbol: later uploads wait for it; launches on other streams wait for the upload
+  if (!c->readers[tu].empty()) CK(cudaStreamWaitEvent(stream, c->readers[tu].front(), 0));
+  if (c->readers[tu].size() > 64) {  // long runs with one model: drop the events that have completed
+    std::vector<cudaEvent_t> keep;
+    keep.push_back(c->readers[tu].front());
+    for (size_t i = 1; i < c->readers[tu].size(); ++i) {
+      if (cudaEventQuery(c->readers[tu][i]) == cudaSuccess) cudaEventDestroy(c->readers[tu][i]);
+      else keep.push_back(c->readers[tu][i]);
+    }
+    c->readers[tu].swap(keep);
+  }
+  return SRT_OK;
+}
+int symbol_launched(DevCtx* c, int tu, cudaStream_t stream) {
+  cudaEvent_t ev;
+  CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  CK(cudaEventRecord(ev, stream));
+  c->readers[tu].push_back(ev);
+  return SRT_OK;
+}
+
+// upload the model (if it is not the resident one) and launch the persistent trace kernel on `stream`
+int launch_trace(DevCtx* c, srt_model* m, const SrtRunParams& P, const SrtBatch& B0, cudaStream_t stream) {
   SrtBatch B = B0;
   B.order_mul = ray_order_mul(B.nrays);
-  { const char* e = getenv("SRT_TEAM_COMPACT"); B.compact = (e && atoi(e) == 0) ? 0 : 1; }
-  { const char* e = getenv("SRT_TEAM_PHASE_ALIGN"); B.phase_align = (e && atoi(e) != 0) ? 1 : 0; }  // off until measured (open item)
   int mode, block, grid;
-  int rc = launch_config(m, B.nrays, &mode, &block, &grid, nullptr);
+  int rc = launch_config(c, m, B.nrays, &mode, &block, &grid, nullptr);
   if (rc) return rc;
+  SrtModel Md;
+  if ((rc = device_model(c, m, &Md))) return rc;
   CK(cudaMemsetAsync(B.counters, 0, 8 * sizeof(unsigned long long), stream));
+  std::lock_guard<std::mutex> lk(c->sym_mutex);
+  const int tu = mode ? 1 : 0;
+  if ((rc = symbol_prepare(c, tu, m->serial, Md, stream))) return rc;
+  if ((rc = symbol_reader(c, tu, stream))) return rc;
   if (mode) {
-    CK(srt_team_launch(m->M, P, B, block, grid, stream));
+    CK(srt_team_launch(Md, P, B, block, grid, stream));
   } else {
-    CK(cudaMemcpyToSymbolAsync(c_srt_model, &m->M, sizeof(SrtModel), 0, cudaMemcpyHostToDevice, stream));
-    pick_trace(m->M)<<<grid, block, 0, stream>>>(P, B);
+    pick_trace(Md)<<<grid, block, 0, stream>>>(P, B);
+    CK(cudaGetLastError());
   }
   g_launches++;
-  CK(cudaGetLastError());
-  return SRT_OK;
+  return symbol_launched(c, tu, stream);
 }
 
 int finish_model(srt_model* mm, int yearday, int msec, int use_igrf, int use_tsyganenko) {
@@ -180,6 +405,7 @@ int finish_model(srt_model* mm, int yearday, int msec, int use_igrf, int use_tsy
   mm->M.use_igrf = use_igrf;
   srt_host::igrf_recalc(yearday, msec, mm->M.igrf);
   for (int i = 0; i < SRT_NSPEC; ++i) mm->nus[i] = 0.0;
+  mm->serial = ++g_model_serial;
   return SRT_OK;
 }
 
@@ -187,16 +413,53 @@ int finish_model(srt_model* mm, int yearday, int msec, int use_igrf, int use_tsy
 
 extern "C" {
 
-int srt_init(int device) {
-  if (device >= 0) {
-    cudaError_t e = cudaSetDevice(device);
-    if (e != cudaSuccess) {
-      snprintf(g_cuda_err, sizeof g_cuda_err, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
-      return SRT_E_NODEVICE;
-    }
-    g_device = -1;
+int srt_init_devices(const int* devices, int ndevices) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    snprintf(g_cuda_err, sizeof g_cuda_err, "no CUDA device: %s", cudaGetErrorString(e));
+    return SRT_E_NODEVICE;
   }
-  return ensure_device();
+  std::vector<int> want;
+  if (ndevices <= 0 || !devices) {
+    for (int d = 0; d < n; ++d) want.push_back(d);
+  } else {
+    for (int i = 0; i < ndevices; ++i) {
+      if (devices[i] < 0 || devices[i] >= n) {
+        snprintf(g_cuda_err, sizeof g_cuda_err, "device %d of %d", devices[i], n);
+        return SRT_E_NODEVICE;
+      }
+      bool dup = false;
+      for (int d : want) dup = dup || d == devices[i];
+      if (!dup) want.push_back(devices[i]);
+    }
+  }
+  std::vector<DevCtx*> act;
+  for (int d : want) {
+    DevCtx* c = ctx_for_device(d);
+    if (!c) return cuda_fail(cudaGetLastError(), "cudaGetDeviceProperties");
+    act.push_back(c);
+  }
+  CK(cudaSetDevice(want[0]));
+  std::lock_guard<std::mutex> lk(g_dev_mutex);
+  g_active = act;
+  return SRT_OK;
+}
+
+int srt_init(int device) {
+  if (device >= 0) return srt_init_devices(&device, 1);
+  // keep the calling thread's current device
+  DevCtx* c = nullptr;
+  int rc = current_ctx(&c);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> lk(g_dev_mutex);
+  g_active.assign(1, c);
+  return SRT_OK;
+}
+
+int srt_device_count(void) {
+  std::lock_guard<std::mutex> lk(g_dev_mutex);
+  return (int)g_active.size();
 }
 
 const char* srt_strerror(int code) {
@@ -231,59 +494,54 @@ int srt_model_ngo(srt_model** m, const char* cfg, int yearday, int msec, int use
 int srt_model_grid(srt_model** m, const char* path, int yearday, int msec, int use_igrf, int use_tsyganenko) {
   if (!m || !path) return SRT_E_ARG;
   *m = nullptr;
-  int rc = ensure_device();
+  std::vector<DevCtx*> devs;
+  int rc = active_devices(devs);
   if (rc) return rc;
   srt_model* mm = new (std::nothrow) srt_model();
   if (!mm) return SRT_E_NOMEM;
   memset(&mm->M, 0, sizeof mm->M);
   srt_host::HostGrid hg;
-  rc = srt_host::load_grid(path, mm->M, hg);
+  int compder = 0;
+  rc = srt_host::load_grid(path, mm->M, hg, /*host_derivatives=*/false, &compder);
   if (rc != 0) { delete mm; return rc == -3 ? SRT_E_UNSUPPORTED : SRT_E_IO; }
   rc = finish_model(mm, yearday, msec, use_igrf, use_tsyganenko);
   if (rc) { delete mm; return rc; }
-  size_t nb = hg.nodes.size() * sizeof(double);
-  size_t ax = (hg.xs.size() + hg.ys.size() + hg.zs.size()) * sizeof(double);
-  const SrtGrid& hgd = mm->M.grid;
-  // coefficient table over the extended lattice (edge and outside cells included), srt_tricubic.h
-  const size_t ncells = (hgd.nx > 1 && hgd.ny > 1 && hgd.nz > 1) ? srt_grid_cell_count(hgd) : 0;
-  if (cudaMalloc(&mm->d_nodes, nb) != cudaSuccess || cudaMalloc(&mm->d_axes, ax) != cudaSuccess ||
-      (ncells && cudaMalloc(&mm->d_coef, ncells * 256 * sizeof(double)) != cudaSuccess)) {
-    rc = cuda_fail(cudaGetLastError(), "cudaMalloc(grid)");
-    srt_model_free(mm);
-    return rc;
-  }
-  cudaMemcpy(mm->d_nodes, hg.nodes.data(), nb, cudaMemcpyHostToDevice);
-  cudaMemcpy(mm->d_axes, hg.xs.data(), hg.xs.size() * 8, cudaMemcpyHostToDevice);
-  cudaMemcpy(mm->d_axes + hg.xs.size(), hg.ys.data(), hg.ys.size() * 8, cudaMemcpyHostToDevice);
-  cudaMemcpy(mm->d_axes + hg.xs.size() + hg.ys.size(), hg.zs.data(), hg.zs.size() * 8, cudaMemcpyHostToDevice);
-  mm->M.grid.nodes = mm->d_nodes;
-  mm->M.grid.coef = nullptr;
-  mm->M.grid.xs = mm->d_axes;
-  mm->M.grid.ys = mm->d_axes + hg.xs.size();
-  mm->M.grid.zs = mm->d_axes + hg.xs.size() + hg.ys.size();
-  if (ncells) {
-    // per-cell tricubic coefficients, once (SRT_GRID_COEF=0 keeps the on-the-fly path: test hook)
+  mm->file_has_derivatives = (compder == 1);
+  mm->h_nodes.swap(hg.nodes);
+  mm->h_axes = hg.xs;
+  mm->h_axes.insert(mm->h_axes.end(), hg.ys.begin(), hg.ys.end());
+  mm->h_axes.insert(mm->h_axes.end(), hg.zs.begin(), hg.zs.end());
+  {  // per-cell tricubic coefficients unless SRT_GRID_COEF=0 (test hook: the on-the-fly path)
     const char* env = getenv("SRT_GRID_COEF");
-    if (!(env && !strcmp(env, "0"))) {
-      long long threads = (long long)ncells * 4;
-      int blocks = (int)((threads + 127) / 128 < (long long)g_num_sms * 16 ? (threads + 127) / 128 : (long long)g_num_sms * 16);
-      srt_coef_kernel<<<blocks, 128>>>(mm->M.grid, mm->d_coef);
-      g_launches++;
-      cudaDeviceSynchronize();
-      mm->M.grid.coef = mm->d_coef;
-    }
+    mm->use_coef = !(env && !strcmp(env, "0"));
   }
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) { srt_model_free(mm); return cuda_fail(e, "grid upload"); }
+  // replicas on every active device now, so that set-up is not part of the first batch
+  int prev = 0;
+  cudaGetDevice(&prev);
+  for (DevCtx* c : devs) {
+    GridReplica r;
+    if (cudaSetDevice(c->dev) != cudaSuccess) { rc = cuda_fail(cudaGetLastError(), "cudaSetDevice"); break; }
+    if ((rc = ensure_replica(c, mm, &r))) break;
+  }
+  cudaSetDevice(prev);
+  if (rc) { srt_model_free(mm); return rc; }
   *m = mm;
   return SRT_OK;
 }
 
 void srt_model_free(srt_model* m) {
   if (!m) return;
-  if (m->d_nodes) cudaFree(m->d_nodes);
-  if (m->d_axes) cudaFree(m->d_axes);
-  if (m->d_coef) cudaFree(m->d_coef);
+  int prev = 0;
+  cudaGetDevice(&prev);
+  for (auto& kv : m->replicas) {
+    cudaSetDevice(kv.first);
+    // a kernel still reading this model's arrays must finish first
+    cudaDeviceSynchronize();
+    if (kv.second.d_nodes) cudaFree(kv.second.d_nodes);
+    if (kv.second.d_axes) cudaFree(kv.second.d_axes);
+    if (kv.second.d_coef) cudaFree(kv.second.d_coef);
+  }
+  if (!m->replicas.empty()) cudaSetDevice(prev);
   delete m;
 }
 
@@ -300,37 +558,47 @@ int srt_model_species(const srt_model* m, int* nspec, double* qs, double* ms, do
 
 int srt_model_eval(const srt_model* m, int64_t n, const double* x, double* out) {
   if (!m || n < 0 || (n > 0 && (!x || !out))) return SRT_E_ARG;
-  int rc = ensure_device();
+  DevCtx* c = nullptr;
+  int rc = current_ctx(&c);
   if (rc) return rc;
   if (n == 0) return SRT_OK;
+  srt_model* mm = const_cast<srt_model*>(m);
+  SrtModel Md;
+  if ((rc = device_model(c, mm, &Md))) return rc;
   double *dx = nullptr, *dout = nullptr;
   CK(cudaMalloc(&dx, n * 3 * sizeof(double)));
   if (cudaMalloc(&dout, n * 19 * sizeof(double)) != cudaSuccess) { cudaFree(dx); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
+  cudaStream_t st = nullptr;  // legacy default stream: ordered after the copies below
   cudaMemcpy(dx, x, n * 3 * sizeof(double), cudaMemcpyHostToDevice);
   {
-    std::lock_guard<std::mutex> lk(g_model_mutex);
-    cudaMemcpyToSymbol(c_srt_model, &m->M, sizeof(SrtModel));
-    int blocks = (int)((n + 127) / 128);
-    if (blocks > g_num_sms * 8) blocks = g_num_sms * 8;
-    pick_eval(m->M)<<<blocks, 128>>>(n, dx, dout);
-    g_launches++;
-    cudaDeviceSynchronize();
+    std::lock_guard<std::mutex> lk(c->sym_mutex);
+    rc = symbol_prepare(c, 0, mm->serial, Md, st);
+    if (!rc) rc = symbol_reader(c, 0, st);
+    if (!rc) {
+      int blocks = (int)((n + 127) / 128);
+      if (blocks > c->num_sms * 8) blocks = c->num_sms * 8;
+      pick_eval(Md)<<<blocks, 128, 0, st>>>(n, dx, dout);
+      g_launches++;
+      rc = symbol_launched(c, 0, st);
+    }
   }
-  cudaMemcpy(out, dout, n * 19 * sizeof(double), cudaMemcpyDeviceToHost);
+  if (!rc) {
+    cudaError_t e = cudaMemcpy(out, dout, n * 19 * sizeof(double), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) rc = cuda_fail(e, "srt_model_eval");
+  }
   cudaFree(dx);
   cudaFree(dout);
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return cuda_fail(e, "srt_model_eval");
-  return SRT_OK;
+  return rc;
 }
 
 int srt_kernel_info(const srt_model* m, int64_t nrays, int* mode, int* regs, int* local_bytes, int* blocks_per_sm, int* grid, int* block) {
   if (!m) return SRT_E_ARG;
-  int rc = ensure_device();
+  DevCtx* c = nullptr;
+  int rc = current_ctx(&c);
   if (rc) return rc;
   srt_model* mm = const_cast<srt_model*>(m);
   int md, blk, grd, nb;
-  rc = launch_config(mm, nrays, &md, &blk, &grd, &nb);
+  rc = launch_config(c, mm, nrays, &md, &blk, &grd, &nb);
   if (rc) return rc;
   cudaFuncAttributes fa;
   if (md) CK(srt_team_attributes(m->M, blk, &fa));
@@ -347,7 +615,8 @@ int srt_kernel_info(const srt_model* m, int64_t nrays, int* mode, int* regs, int
 int srt_trace_batch_device(const srt_model* m, int64_t nrays, double* d_rays, const srt_run_params* p, double* d_log, int64_t log_capacity,
                            double* d_summary, uint64_t* d_counters, void* stream) {
   if (!m || !p || nrays < 0 || !d_rays || !d_summary || !d_counters || log_capacity < 0 || (log_capacity > 0 && !d_log)) return SRT_E_ARG;
-  int rc = ensure_device();
+  DevCtx* c = nullptr;
+  int rc = current_ctx(&c);
   if (rc) return rc;
   SrtRunParams P;
   memcpy(&P, p, sizeof P);
@@ -360,8 +629,7 @@ int srt_trace_batch_device(const srt_model* m, int64_t nrays, double* d_rays, co
   B.counters = (unsigned long long*)d_counters;
   B.nlogged = nullptr;
   B.order_mul = 1;  // set by launch_trace
-  std::lock_guard<std::mutex> lk(g_model_mutex);
-  return launch_trace(const_cast<srt_model*>(m), P, B, (cudaStream_t)stream);
+  return launch_trace(c, const_cast<srt_model*>(m), P, B, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -9,7 +9,7 @@
 // the text between the first two characters and the first '=', the first match wins.  Integers are read as reals and
 // floored, as the driver does.  Options the reference leaves uninitialised when absent are required here.
 //
-// Additions (not in the reference): --device=N (CUDA device, default current), --threads=N (formatter threads,
+// Additions (not in the reference): --device=N (one CUDA device; default: every GPU of the box), --threads=N (formatter threads,
 // default all cores), --batch=N (rays per srt_trace_batch call; default: as many as keep the worst-case
 // trajectory rows, maxsteps/outputper per ray, inside a quarter of the host's memory), --verbose=1 (timing to stderr).
 #include <chrono>
@@ -98,7 +98,7 @@ void usage() {
        "   --use_tsyganenko     must be 0 (the external field is not on the GPU path)\n"
        "\n"
        " Not in the reference:\n"
-       "   --device=N  --threads=N  --batch=N  --verbose=1");
+       "   --device=N (default: all GPUs)  --threads=N  --batch=N  --verbose=1");
 }
 
 }  // namespace
@@ -143,7 +143,8 @@ int main(int argc, char** argv) {
   const bool verbose = opt_real("verbose", 0.0) != 0.0;
   if (batch < 1) die(2, "--batch must be >= 1");
 
-  int rc = srt_init(device);
+  // one call per batch of the ray file uses every GPU of the box unless --device names one
+  int rc = device >= 0 ? srt_init(device) : srt_init_devices(nullptr, 0);
   if (rc) die(1, std::string("srt_init: ") + srt_strerror(rc));
   srt_model* model = nullptr;
   if (modelnum == 1) {

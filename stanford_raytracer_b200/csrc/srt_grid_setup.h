@@ -78,8 +78,10 @@ inline void fd_pass(std::vector<double>& nodes, int nx, int ny, int nz, int s, i
       }
 }
 
-// Returns 0, -1 cannot open, -2 garbled / truncated, -3 unsupported (nspec > 4)
-inline int load_grid(const char* path, SrtModel& M, HostGrid& hg) {
+// Returns 0, -1 cannot open, -2 garbled / truncated, -3 unsupported (nspec > 4).
+// host_derivatives = false leaves the derivative slots of a file without derivatives at zero: the library computes
+// them on the device (srt_fd_kernel, srt_api.cu); the CPU test build keeps the host passes below.
+inline int load_grid(const char* path, SrtModel& M, HostGrid& hg, bool host_derivatives = true, int* compder_out = nullptr) {
   NumberStream in;
   if (!in.open(path)) return -1;
   double v[6];
@@ -118,7 +120,8 @@ inline int load_grid(const char* path, SrtModel& M, HostGrid& hg) {
         if (!in.next(val)) return -2;
         hg.nodes[(node * 8 + q) * 4 + s] = val;
       }
-  if (compder != 1) {
+  if (compder_out) *compder_out = compder;
+  if (compder != 1 && host_derivatives) {
     for (int s = 0; s < nspec; ++s) {
       fd_pass(hg.nodes, nx, ny, nz, s, 0, 1, 0, g.delx, nx > 2);                      // df/dx
       fd_pass(hg.nodes, nx, ny, nz, s, 0, 2, 1, g.dely, ny > 2);                      // df/dy

@@ -33,10 +33,9 @@ struct SrtBatch {
   double* log;                      // [capacity][SRT_LOG_WORDS]
   unsigned long long log_capacity;
   double* summary;                  // [nrays][SRT_SUMMARY_WORDS]
-  unsigned long long* counters;     // [0] log rows, [1] accepted steps, [2] attempts, [3] dropped rays, [4] ray queue head, team kernel: [5] re-packs, [6] sum and [7] max over blocks of rounds
+  unsigned long long* counters;     // [0] log rows, [1] accepted steps (incl. [5]), [2] attempts (incl. [5]), [3] dropped rays, [4] ray queue head,
+                                    // [5] steps of all-NaN states taken by the fast-forward (srt_nan_fastforward), team kernel: [6] sum and [7] max over blocks of rounds
   unsigned* nlogged;                // optional [nrays]: rows this ray put in the log
-  int compact;                      // team kernel: re-pack live teams once the queue is empty
-  int phase_align;                  // team kernel: idle teams refill only on the block's attempt boundary (srt_team.cuh)
   unsigned long long order_mul;     // queue position q is ray (q * order_mul) mod nrays; coprime to nrays (1 = input order)
 };
 
@@ -59,6 +58,35 @@ __device__ __forceinline__ void srt_log_row(const SrtBatch& B, long long ray, in
   for (int i = 0; i < SRT_ROW_DOUBLES; ++i) dst[1 + i] = row[i];
 }
 
+// NaN fast-forward.  A state whose six components are all NaN stays so, and the reference steps it on to maxsteps or
+// tmax (tests/test_nan_rays_cpu.py pins this on the oracle; ~1 % of the config-3 rays, 5 % of its accepted steps):
+// the error estimate is NaN, so `err > maxerr` and the growth test are false and dt stays; the cone test `imsum > 0`
+// is false, so every attempt is accepted; no stop condition but `t >= tmax` and `nstep >= maxsteps` can fire (every
+// norm is NaN; dt can only have grown since the `dt < 1e-14` test of this attempt passed).  Every further row is the row
+// just recorded -- evaluated at this NaN position from this NaN wave vector -- with t advanced by dt, so the remaining
+// steps are taken here as one addition each (same bits: t = t + dt sequentially) instead of a full RK45 step each.
+// Called by the lane that writes the ray's rows, right after it recorded `row` for step nstep.  Returns the number
+// of steps taken; they are booked in counters[5] as well as in [1]/[2], so that rates can be quoted without them.
+__device__ __forceinline__ unsigned srt_nan_fastforward(const SrtRunParams& P, const SrtBatch& B, long long ray, int outputper, double row[SRT_ROW_DOUBLES],
+                                                        double& t, double dt, int& nstep, unsigned& nlog, bool& dropped) {
+  unsigned n = 0;
+  while (!dropped && !(t >= P.tmax) && !(nstep >= P.maxsteps)) {
+    t = t + dt;
+    nstep = nstep + 1;
+    ++n;
+    row[0] = t;
+    const int ri = nstep - 1;
+    if (ri % outputper == 0) {
+      srt_log_row(B, ray, ri / outputper, row, dropped);
+      if (!dropped) ++nlog;
+    }
+  }
+  return n;
+}
+__device__ __forceinline__ bool srt_all_nan6(const double x[3], const double k[3]) {
+  return x[0] != x[0] && x[1] != x[1] && x[2] != x[2] && k[0] != k[0] && k[1] != k[1] && k[2] != k[2];
+}
+
 template <int DENS, int USE_IGRF>
 __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_THREAD_MIN_BLOCKS) srt_trace_kernel(const __grid_constant__ SrtRunParams P, const __grid_constant__ SrtBatch B) {
   const unsigned full = 0xffffffffu;
@@ -69,7 +97,7 @@ __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_THREAD_MIN_BLOCKS) srt_
   bool active = false, exhausted = false, dropped = false;
   long long slot = -1, ray = -1;
   unsigned nlog = 0;
-  unsigned long long my_accepted = 0, my_attempts = 0;
+  unsigned long long my_accepted = 0, my_attempts = 0, my_ff = 0;
   const int outputper = P.outputper < 1 ? 1 : P.outputper;
 
   for (;;) {
@@ -126,6 +154,10 @@ __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_THREAD_MIN_BLOCKS) srt_
             srt_log_row(B, ray, rowidx / outputper, row, dropped);
             if (!dropped) ++nlog;
           }
+          if (srt_all_nan6(st.x, st.k)) {
+            const unsigned nff = srt_nan_fastforward(P, B, ray, outputper, row, st.t, st.dt, st.nstep, nlog, dropped);
+            my_accepted += nff; my_attempts += nff; my_ff += nff;
+          }
         }
       }
       if (r == SRT_ATTEMPT_DONE) {
@@ -147,10 +179,12 @@ __global__ void __launch_bounds__(SRT_BLOCK_THREADS, SRT_THREAD_MIN_BLOCKS) srt_
   for (int o = 16; o > 0; o >>= 1) {
     my_accepted += __shfl_down_sync(full, my_accepted, o);
     my_attempts += __shfl_down_sync(full, my_attempts, o);
+    my_ff += __shfl_down_sync(full, my_ff, o);
   }
   if (lane == 0) {
     atomicAdd(&B.counters[1], my_accepted);
     atomicAdd(&B.counters[2], my_attempts);
+    if (my_ff) atomicAdd(&B.counters[5], my_ff);
   }
 }
 

@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
   double vg[3] = {0.0, 0.0, 0.0};
   int nstep = 0, lastrefinedown = 0, stopcond = 0, cone_exit = 0;
   unsigned nrej = 0, ncone = 0, nlog = 0;
-  unsigned long long my_accepted = 0, my_attempts = 0;
+  unsigned long long my_accepted = 0, my_attempts = 0, my_ff = 0;
   // ---- owned component (meaningful on lanes 0-5; lanes 6,7 mirror component r-6 harmlessly)
   const int comp = (r < 6) ? r : (r - 6);
   double xc = 0.0;          // state component
@@ -109,13 +109,14 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
   for (;;) {
     // ================= refill: idle teams take the next ray; one atomic per warp
 #if defined(SRT_TEAM_BLOCK_SYNC)
-    // Phase alignment (B.phase_align, off by default): an attempt is `cyc` rounds (stages 2..6 + estimate; fixed step:
-    // stages 2..4 + estimate) and the first wave of a block starts at round 0, so every team's estimate round falls on
-    // a multiple of cyc for as long as no team joins in between.  A team that refills at another round would run its
-    // estimate branch while its warp neighbours run a stage branch, in every round from then on.  With the knob on,
-    // an idle team takes its next ray only at a multiple of cyc: its stage-1 stencil round coincides with the others'
-    // estimate round and the block stays in phase (at most cyc-1 idle rounds per ray).  Pure scheduling: no result changes.
-    const bool refill_round = !B.phase_align || (sync_iter % (adaptive ? 6u : 4u)) == 0u;
+    // Phase alignment: an attempt is `cyc` rounds (stages 2..6 + estimate; fixed step: stages 2..4 + estimate) and
+    // the first wave of a block starts at round 0, so every team's estimate round falls on a multiple of cyc for as
+    // long as no team joins in between.  A team that refilled at another round would run its estimate branch while its
+    // warp neighbours run a stage branch, in every round from then on (measured on config 3: +25 % at 1 000 steps per
+    // ray, +34 % at 4 000, profiles/r2a_c3_age.txt).  So an idle team takes its next ray only at a multiple of cyc:
+    // its stage-1 stencil round coincides with the others' estimate round and the block stays in phase (at most cyc-1
+    // idle rounds per ray).  Pure scheduling: no result changes.
+    const bool refill_round = (sync_iter % (adaptive ? 6u : 4u)) == 0u;
 #else
     const bool refill_round = true;
 #endif
@@ -165,17 +166,17 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
 #if defined(SRT_TEAM_BLOCK_SYNC)
     // block-synchronous rounds: the warps of a block walk the round's code in phase and share instruction lines
     // live teams of this block; a team waiting for its refill round (phase alignment) still has the queue to look at
-    const int live = __syncthreads_count(((phase != SRT_PH_IDLE || (B.phase_align && !exhausted)) && r == 0) ? 1 : 0);
+    const int live = __syncthreads_count(((phase != SRT_PH_IDLE || !exhausted) && r == 0) ? 1 : 0);
     if (live == 0) break;
     // ---- compaction.  Once the ray queue is empty, finished rays leave holes: a block whose few live teams are
     // spread over all its warps still issues every warp.  When at most half of the team slots in use are live, the
     // live teams are re-packed into the lowest warps through shared memory (pure data movement: results unchanged);
     // the emptied warps then only attend the barrier.  Config 2 spends most of its time in this regime.
-    if ((++sync_iter & 31u) == 0u && live * 2 <= cap_teams && cap_teams > 4 && B.compact) {
+    if ((++sync_iter & 31u) == 0u && live * 2 <= cap_teams && cap_teams > 4) {
       if (__syncthreads_or(exhausted ? 1 : 0)) {
         unsigned long long* pk = srt_pack_smem;
         const int nslots = (int)(blockDim.x >> 1);  // lane slots available: half a block
-        if (threadIdx.x == 0) { srt_pack_count = 0; atomicAdd(&B.counters[5], 1ull); }
+        if (threadIdx.x == 0) srt_pack_count = 0;
         __syncthreads();
         if (phase != SRT_PH_IDLE) {
           int idx = 0;
@@ -366,8 +367,10 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
   for (int o = 16; o > 0; o >>= 1) {
     my_accepted += __shfl_down_sync(full, my_accepted, o);
     my_attempts += __shfl_down_sync(full, my_attempts, o);
+    my_ff += __shfl_down_sync(full, my_ff, o);
   }
   if (lane == 0) {
+    if (my_ff) atomicAdd(&B.counters[5], my_ff);
     if (threadIdx.x == 0) { atomicAdd(&B.counters[6], (unsigned long long)sync_iter); atomicMax(&B.counters[7], (unsigned long long)sync_iter); }
     atomicAdd(&B.counters[1], my_accepted);
     atomicAdd(&B.counters[2], my_attempts);

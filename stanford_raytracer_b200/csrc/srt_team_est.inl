@@ -140,35 +140,17 @@
               }
             }
             dropped = __shfl_sync(T.tmask, (int)dropped, T.tbase) != 0;
-#if defined(SRT_NAN_FASTFWD)
-            // ---- Build variant (-DSRT_NAN_FASTFWD; not in the default build until checked on a GPU against
-            // tests/test_gpu_parity.py::test_nan_state_ray_is_stepped_like_the_reference).  A state whose six
-            // components are all NaN stays so, and the reference steps it on to maxsteps or tmax
-            // (tests/test_nan_rays_cpu.py): the error estimate is NaN, so `err > maxerr` and the growth test are
-            // false and dt stays; the cone test `imsum > 0` is false, so every attempt is accepted; no stop
-            // condition but `t >= tmax` and `nstep >= maxsteps` can fire (every norm is NaN, dt did not change since
-            // the `dt < 1e-14` test of this attempt).  Every further row is the row just recorded -- computed at
-            // this NaN position from this NaN wave vector -- with t advanced by dt, so the remaining steps are
-            // taken here as a loop of one addition each instead of 6 block rounds each.
-            if (e2[0] != e2[0] && e2[1] != e2[1] && e2[2] != e2[2] && knew[0] != knew[0] && knew[1] != knew[1] && knew[2] != knew[2]) {
-              while (!dropped && !(t >= P.tmax) && !(nstep >= P.maxsteps)) {
-                t = t + dt;
-                nstep = nstep + 1;
-                if (r == 0) {
-                  ++my_accepted;
-                  ++my_attempts;
-                  row[0] = t;
-                  const int ri = nstep - 1;
-                  if (ri % outputper == 0) {
-                    srt_log_row(B, slot, ri / outputper, row, dropped);
-                    if (!dropped) ++nlog;
-                  }
-                }
-                dropped = __shfl_sync(T.tmask, (int)dropped, T.tbase) != 0;
+            // an all-NaN state is stepped on to maxsteps / tmax by the reference: srt_nan_fastforward (srt_kernels.cuh)
+            if (srt_all_nan6(e2, knew)) {
+              if (r == 0) {
+                const unsigned nff = srt_nan_fastforward(P, B, slot, outputper, row, t, dt, nstep, nlog, dropped);
+                my_accepted += nff; my_attempts += nff; my_ff += nff;
+                B.summary[slot * SRT_SUMMARY_WORDS] = t;  // the last recorded row lives in the summary
               }
-              if (r == 0) B.summary[slot * SRT_SUMMARY_WORDS] = t;  // the last recorded row lives in the summary
+              t = __shfl_sync(T.tmask, t, T.tbase);
+              nstep = __shfl_sync(T.tmask, nstep, T.tbase);
+              dropped = __shfl_sync(T.tmask, (int)dropped, T.tbase) != 0;
             }
-#endif
             // stage 1 of the next attempt (raytracer_evalrhs at the new point): dF/dk, dF/dw just recorded,
             // dF/dx from the six displaced points lanes 0-5 evaluated in this round
             {

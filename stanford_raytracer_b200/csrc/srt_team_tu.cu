@@ -16,9 +16,7 @@
 #include "srt_team.cuh"
 #include "srt_team_tu.h"
 
-#ifndef SRT_TEAM_MAXT_SMALL
-#define SRT_TEAM_MAXT_SMALL 512  // tuning hook: 256 gives the scarce-ray kernel 255 registers
-#endif
+#define SRT_TEAM_MAXT_SMALL 512  // 255-register (block 256) and 168-register (block 320) builds measured slower on config 2 (profiles/r1i_register_budget.txt)
 
 typedef void (*team_kernel_t)(const SrtRunParams, const SrtBatch);
 
@@ -52,10 +50,13 @@ cudaError_t srt_team_occupancy(const SrtModel& M, int block, int* blocks_per_sm)
 
 cudaError_t srt_team_attributes(const SrtModel& M, int block, cudaFuncAttributes* fa) { return cudaFuncGetAttributes(fa, pick_team(M, block)); }
 
+// the model of the next launches of this translation unit's kernels (its own __constant__ copy)
+cudaError_t srt_team_upload_model(const SrtModel& M, cudaStream_t stream) {
+  return cudaMemcpyToSymbolAsync(c_srt_model, &M, sizeof(SrtModel), 0, cudaMemcpyHostToDevice, stream);
+}
+
 cudaError_t srt_team_launch(const SrtModel& M, const SrtRunParams& P, const SrtBatch& B, int block, int grid, cudaStream_t stream) {
-  cudaError_t e = cudaMemcpyToSymbolAsync(c_srt_model, &M, sizeof(SrtModel), 0, cudaMemcpyHostToDevice, stream);
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(pick_team(M, block), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)team_smem_bytes(1024));
+  cudaError_t e = cudaFuncSetAttribute(pick_team(M, block), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)team_smem_bytes(1024));
   if (e != cudaSuccess) return e;
   pick_team(M, block)<<<grid, block, team_smem_bytes(block), stream>>>(P, B);
   return cudaGetLastError();

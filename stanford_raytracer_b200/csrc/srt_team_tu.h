@@ -7,5 +7,6 @@ struct SrtBatch;
 int srt_team_block_threads(long long nrays, int num_sms);
 cudaError_t srt_team_occupancy(const SrtModel& M, int block, int* blocks_per_sm);
 cudaError_t srt_team_attributes(const SrtModel& M, int block, cudaFuncAttributes* fa);
-// uploads the model into this unit's __constant__ copy and launches the kernel on `stream`
+// the model of this unit's kernels lives in its own __constant__ copy: upload, then launch on `stream`
+cudaError_t srt_team_upload_model(const SrtModel& M, cudaStream_t stream);
 cudaError_t srt_team_launch(const SrtModel& M, const SrtRunParams& P, const SrtBatch& B, int block, int grid, cudaStream_t stream);

@@ -153,7 +153,7 @@ SRT_HDN double srt_tricubic_slow(const SrtGrid& g, int is0, int js0, int ks0, do
   return v;
 }
 
-#if defined(__CUDA_ARCH__) && defined(SRT_GRID_STAGE) && defined(SRT_TEAM_TU)
+#if defined(__CUDA_ARCH__) && defined(SRT_TEAM_TU)
 extern __shared__ unsigned long long srt_stage_smem[];  // the team kernel's dynamic shared memory (srt_team.cuh)
 #endif
 
@@ -168,8 +168,8 @@ SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT
   if (inj) yil = (x[1] - g.ys[js0 - 1]) / g.dely;
   if (ink) zil = (x[2] - g.zs[ks0 - 1]) / g.delz;
   double v[SRT_NSPEC] = {0.0, 0.0, 0.0, 0.0};
-#if defined(__CUDA_ARCH__) && defined(SRT_GRID_STAGE) && defined(SRT_TEAM_TU)
-  // ---- Build variant (-DSRT_GRID_STAGE, team translation unit only; not in the default build until measured).
+#if defined(__CUDA_ARCH__) && defined(SRT_TEAM_TU)
+  // ---- Team kernel: cooperative fetch of the cell record (+4-7 % on config 3, profiles/r2a_c3_age.txt).
   // The 8 lanes of a team evaluate points a finite-difference step apart, i.e. almost always in the same cell, and
   // each of them walks the cell's whole 2 KiB record with its own 128 LDG.128.  Here the team fetches the record of
   // the centre lane's cell together, one i-slab (64 doubles) at a time: 4 coalesced LDG.128 per lane and slab into a

@@ -36,6 +36,25 @@ static long run_one(const SrtModel& M, const SrtRunParams& P, const double* pos0
   return n;
 }
 
+// whole ray, endpoint only (the CPU-baseline leg of bench.py: "deduplicated" mode)
+template <int D, int I>
+static long run_summary(const SrtModel& M, const SrtRunParams& P, const double* pos0, double* dir0, double w0, double* last_row, int* stopcond,
+                        long* nrej) {
+  SrtRayState st;
+  double row[SRT_ROW_DOUBLES], keep[SRT_ROW_DOUBLES];
+  srt_ray_init<D, I>(SrtModelRef{&M}, P, pos0, dir0, w0, st, keep);
+  long n = 1;
+  for (;;) {
+    int r = srt_ray_attempt<D, I>(SrtModelRef{&M}, P, st, row);
+    if (r == SRT_ATTEMPT_DONE) break;
+    if (r == SRT_ATTEMPT_ACCEPTED) { memcpy(keep, row, sizeof keep); ++n; }
+  }
+  memcpy(last_row, keep, sizeof keep);
+  *stopcond = st.stopcond;
+  *nrej = (long)st.nrej + (long)st.ncone;
+  return n;
+}
+
 template <int D, int I>
 static void plasma_n(const SrtModel& M, long n, const double* x, double* out) {
   for (long i = 0; i < n; ++i) {
@@ -98,6 +117,18 @@ void emu_plasma(void* m, long n, const double* x, double* out) {
   else { if (M.use_igrf) plasma_n<1, 1>(M, n, x, out); else plasma_n<1, 0>(M, n, x, out); }
 }
 int emu_is_right_handed(double n2, double phi, double S, double D, double P) { return srt_is_right_handed(n2, phi, S, D, P) ? 1 : 0; }
+
+long emu_trace_summary(void* m, const double* pos0, double* dir0, double w0, double dt0, double dtmax, double maxerr, int maxsteps, double minalt,
+                       int root, double tmax, int fixedstep, double* last_row, int* stopcond, long* nrej) {
+  const SrtModel& M = *(SrtModel*)m;
+  SrtRunParams P = {dt0, dtmax, maxerr, minalt, tmax, maxsteps, root, fixedstep, 1};
+  if (M.density == SRT_DENS_NGO) {
+    if (M.use_igrf) return run_summary<0, 1>(M, P, pos0, dir0, w0, last_row, stopcond, nrej);
+    return run_summary<0, 0>(M, P, pos0, dir0, w0, last_row, stopcond, nrej);
+  }
+  if (M.use_igrf) return run_summary<1, 1>(M, P, pos0, dir0, w0, last_row, stopcond, nrej);
+  return run_summary<1, 0>(M, P, pos0, dir0, w0, last_row, stopcond, nrej);
+}
 
 long emu_trace(void* m, const double* pos0, double* dir0, double w0, double dt0, double dtmax, double maxerr, int maxsteps, double minalt,
                int root, double tmax, int fixedstep, double* rows, long max_rows, int* stopcond, long* nrej, long* ncone, int* cone_exit) {

@@ -131,6 +131,11 @@ class OracleModel:
         self.L.orc_trace_free(t)
         return res
 
+    def trace_summary(self, pos0, dir0, w0, **params):
+        """endpoint of one ray (last row, rows, stop code)"""
+        s = self.trace_batch_summary(np.asarray(pos0).reshape(1, 3), np.asarray(dir0).reshape(1, 3), np.array([w0]), **params)
+        return dict(last_row=s["last_row"][0], nrows=int(s["nrows"][0]), stopcond=int(s["stopcond"][0]), nrejected=int(s["nrejected"][0]))
+
     def trace_batch_summary(self, pos0, dir0, w0, dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep):
         pos0 = np.ascontiguousarray(pos0, dtype=np.float64).reshape(-1, 3)
         dir0 = np.ascontiguousarray(dir0, dtype=np.float64).reshape(-1, 3)
@@ -143,6 +148,37 @@ class OracleModel:
         acc = self.L.orc_trace_batch_summary(self.h, n, _p(pos0), _p(dir0), _p(w0), dt0, dtmax, maxerr, maxsteps, minalt, root,
                                              tmax, fixedstep, _p(last), _p(nrows), _p(stop), _p(nrej))
         return dict(accepted=acc, last_row=last, nrows=nrows, stopcond=stop, nrejected=nrej)
+
+
+class DedupModel:
+    """oracle/_build/libsrt_dedup.so: the GPU kernels' evaluation order on the host at -O3 (bench.py cpu_baseline,
+    "deduplicated" mode).  Read-only during a trace: one instance serves every worker thread."""
+
+    def __init__(self, kind, path, yearday=2010001, msec=0, use_igrf=0):
+        p = os.path.join(ORC_DIR, "_build", "libsrt_dedup.so")
+        if not os.path.exists(p):
+            build()
+        E = C.CDLL(p)
+        d, i, vp, l = C.c_double, C.c_int, C.c_void_p, C.c_long
+        for f in (E.emu_model_ngo, E.emu_model_grid):
+            f.restype = vp
+            f.argtypes = [C.c_char_p, i, i, i]
+        E.emu_trace_summary.restype = l
+        E.emu_trace_summary.argtypes = [vp, vp, vp, d, d, d, d, i, d, i, d, i, vp, vp, vp]
+        self.E = E
+        fn = E.emu_model_ngo if kind == "ngo" else E.emu_model_grid
+        self.h = fn(path.encode(), yearday, msec, use_igrf | (2 if kind != "ngo" else 0))  # grid: per-cell coefficient table, as on the GPU
+        if not self.h:
+            raise RuntimeError("dedup model setup failed: %s" % path)
+
+    def trace_summary(self, pos0, dir0, w0, dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep):
+        pos0 = np.ascontiguousarray(pos0, dtype=np.float64)
+        d0 = np.array(dir0, dtype=np.float64)
+        last = np.empty(ROW)
+        sc, nr = C.c_int(), C.c_long()
+        n = self.E.emu_trace_summary(self.h, _p(pos0), _p(d0), w0, dt0, dtmax, maxerr, maxsteps, minalt, root, tmax, fixedstep, _p(last),
+                                     C.byref(sc), C.byref(nr))
+        return dict(last_row=last, nrows=int(n), stopcond=sc.value, nrejected=nr.value)
 
 
 def launch_point(lat_deg, lon_deg=0.0, alt_km=1000.0):

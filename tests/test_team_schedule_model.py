@@ -1,5 +1,5 @@
 """Model of the team kernel's round scheduling (stanford_raytracer_b200/csrc/srt_team.cuh: refill, the block-wide live
-count, phase transitions) in plain Python, to pin the two properties the SRT_TEAM_PHASE_ALIGN knob relies on:
+count, phase transitions) in plain Python, to pin the two properties phase alignment (always on since round 2; `align=False` models the round-1 kernel) relies on:
   1. the block loop terminates and every ray of the queue is traced exactly once, knob on or off;
   2. with the knob on, every estimate round of every team falls on a block round that is a multiple of the attempt
      length (6 rounds adaptive, 4 fixed step), whatever the ray lifetimes and rejections; with it off it does not.
