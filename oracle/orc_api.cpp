@@ -81,6 +81,9 @@ void orc_solve(void* mv, const double* k, double w, const double* x, double* k1k
   k1k2[0] = k1.re; k1k2[1] = k1.im; k1k2[2] = k2.re; k1k2[3] = k2.im;
 }
 int orc_is_right_handed(double n2, double phi, double S, double D, double P) { return is_right_handed(n2, phi, S, D, P) ? 1 : 0; }
+void orc_is_right_handed_n(long n, const double* n2, const double* phi, const double* S, const double* D, const double* P, int* out) {
+  for (long i = 0; i < n; ++i) out[i] = is_right_handed(n2[i], phi[i], S[i], D[i], P[i]) ? 1 : 0;
+}
 // the float-rounded matrix of form_dispersion_matrix, for the numpy SVD cross-check: out[3][3][2]
 void orc_form_dispersion_matrix(double n2, double phi, double S, double D, double P, double* out) {
   cplx M[3][3];

@@ -263,9 +263,14 @@ int srt_set_rows_shm(const char* prefix) {
     for (const char* q = prefix; *q; ++q)
       if (*q == '/' || q - prefix > 40) return SRT_E_ARG;
   }
-  pool_clear();  // buffers of the other kind are of no use any more
+  const std::string want = prefix ? prefix : "";
+  {
+    std::lock_guard<std::mutex> lk(g_pool_mutex);
+    if (g_shm_prefix == want) return SRT_OK;
+  }
+  pool_clear();  // pooled buffers of the other kind are of no use any more
   std::lock_guard<std::mutex> lk(g_pool_mutex);
-  g_shm_prefix = prefix ? prefix : "";
+  g_shm_prefix = want;
   return SRT_OK;
 }
 

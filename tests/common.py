@@ -132,3 +132,23 @@ def cone_first_rays(oracle_model):
         ws.append(2 * np.pi * f)
         dts.append(dt0)
     return np.array(pos), np.array(dirs), np.array(ws), dts
+
+
+def stop_code_rays(oracle_model):
+    """Rays that end by each stop condition of raytracer_stopconditions (raytracer.f95:324-353):
+    [(expected code, pos0, dir0, w0, params)].  Codes 2, 3, 5 are rays of the config-2 sweep (found with the CPU oracle);
+    code 1 is a downgoing ray with minalt raised to R_E + 500 km; 6 and 0 by maxsteps / tmax."""
+    pos0, dir0, w0 = c2_grid(100, 100)
+    P = dict(C2, maxsteps=4000)
+    out = []
+    for f, lat in [(5000.0, 40.0), (2000.0, 30.0)]:
+        p = ol.launch_point(lat, 0.0, 1000.0)
+        out.append((1, p, -p / np.linalg.norm(p), 2 * np.pi * f, dict(P, minalt=R_E + 500e3)))
+    out.append((2, pos0[7033], np.zeros(3), w0[7033], P))
+    for r in (2067, 2236):
+        out.append((3, pos0[r], np.zeros(3), w0[r], P))
+    for r in (8931, 7332):
+        out.append((5, pos0[r], np.zeros(3), w0[r], P))
+    out.append((6, pos0[1001], np.zeros(3), w0[1001], dict(P, maxsteps=150)))
+    out.append((0, pos0[1755], np.zeros(3), w0[1755], dict(P, tmax=0.4)))
+    return out

@@ -118,6 +118,10 @@ void emu_plasma(void* m, long n, const double* x, double* out) {
 }
 int emu_is_right_handed(double n2, double phi, double S, double D, double P) { return srt_is_right_handed(n2, phi, S, D, P) ? 1 : 0; }
 
+void emu_is_right_handed_n(long n, const double* n2, const double* phi, const double* S, const double* D, const double* P, int* out) {
+  for (long i = 0; i < n; ++i) out[i] = srt_is_right_handed(n2[i], phi[i], S[i], D[i], P[i]) ? 1 : 0;
+}
+
 long emu_trace_summary(void* m, const double* pos0, double* dir0, double w0, double dt0, double dtmax, double maxerr, int maxsteps, double minalt,
                        int root, double tmax, int fixedstep, double* last_row, int* stopcond, long* nrej) {
   const SrtModel& M = *(SrtModel*)m;

@@ -98,6 +98,24 @@ def test_ngo_with_igrf_rays_bitwise(srt, kernel_mode):
         assert res.stopcond[r] == t["stopcond"] and np.array_equal(res[r].rows, t["rows"], equal_nan=True), r
 
 
+@pytest.mark.parametrize("yearday,msec", [(1997180, 43200000), (2024100, 3600000), (1968300, 0)])
+def test_igrf_other_epochs(srt, yearday, msec):
+    """IGRF at other epochs and times of day: different brackets of RECALC_08's coefficient interpolation
+    (geopack2008.for:890-1012: 1965-70, 1995-2000, extrapolation beyond 2020) and another GEO->GSW rotation / dipole tilt."""
+    m = srt.ngosetup(common.NGO_CFG, yearday, msec, 1, 0)
+    o = ol.OracleModel("ngo", common.NGO_CFG, yearday=yearday, msec=msec, use_igrf=1)
+    rng = np.random.default_rng(yearday)
+    x = np.array([ol.launch_point(la, lo, alt) for la, lo, alt in zip(rng.uniform(-85, 85, 1500), rng.uniform(0, 360, 1500), 10 ** rng.uniform(2.2, 4.7, 1500))])
+    assert np.array_equal(m.funcPlasmaParams(x)["raw"], o.plasma(x))
+    pos0, dir0, w0 = common.launch_grid([3000.0], [35.0], [0.0, 120.0])
+    p = dict(common.C2, maxsteps=150)
+    res = srt.raytracer_run(m, pos0, dir0, w0, **p)
+    for r in range(len(res)):
+        t = o.trace(pos0[r], [0, 0, 0], w0[r], **p)
+        assert res.stopcond[r] == t["stopcond"] and np.array_equal(res[r].rows, t["rows"], equal_nan=True), r
+    m.close()
+
+
 def test_c3_shape_reduced(srt, tmp_path):
     """Config 3 at reduced size (40^3 grid sampled from the GPU's own Ngo model = the dumpmodel / buildgrid
     role, 1000 rays): size-independent properties + a strided oracle check."""
