@@ -171,13 +171,14 @@ def cpu_run(mode, kind, path, use_igrf, pos0, dir0, w0, params, idx, threads):
                 busy_max=max(busy), busy_mean=float(np.mean(busy)))
 
 
-def cpu_baselines(kind, path, use_igrf, pos0, dir0, w0, params, n_all, n_one, threads, short):
+def cpu_baselines(kind, path, use_igrf, pos0, dir0, w0, params, n_dedup, n_all, n_one, threads, short):
     """The CPU figures of SURVEY.md 8(d) on bounded samples of one launch set (strided rays): {faithful, dedup} x
     {1 core, all cores}, plus the reference's own cost (RECALC_08 per plasma call) on a small sample.  `short`
     (e.g. {"maxsteps": 300}) shortens the rays of every run but dedup/all-cores, whose full-length rays double as the
     parity sample.  Returns (modes dict, (ray indices, dedup/all-cores run))."""
     idx_all = np.unique(np.linspace(0, len(w0) - 1, n_all).astype(int))
     idx_one = np.unique(np.linspace(0, len(w0) - 1, n_one).astype(int))
+    idx_par = np.unique(np.concatenate([idx_all, np.linspace(0, len(w0) - 1, n_dedup).astype(int)]))  # superset of idx_all
     ps = dict(params, **short)
     note = (" first %d steps of each ray" % short["maxsteps"]) if short else ""
 
@@ -188,8 +189,8 @@ def cpu_baselines(kind, path, use_igrf, pos0, dir0, w0, params, n_all, n_one, th
         return e
 
     out = {}
-    full = cpu_run("dedup", kind, path, use_igrf, pos0, dir0, w0, params, idx_all, threads)
-    out["dedup_all_cores"] = entry(full, idx_all, threads)
+    full = cpu_run("dedup", kind, path, use_igrf, pos0, dir0, w0, params, idx_par, threads)
+    out["dedup_all_cores"] = entry(full, idx_par, threads)
     out["dedup_1_core"] = dict(entry(cpu_run("dedup", kind, path, use_igrf, pos0, dir0, w0, ps, idx_one, 1), idx_one, 1), note=note)
     tf = min(threads, 8) if kind == "grid" else threads  # every faithful worker parses its own copy of the grid file
     fa = cpu_run("faithful", kind, path, use_igrf, pos0, dir0, w0, ps, idx_all, tf)
@@ -199,8 +200,9 @@ def cpu_baselines(kind, path, use_igrf, pos0, dir0, w0, params, n_all, n_one, th
     rc = cpu_run("refcost", kind, path, use_igrf, pos0, dir0, w0, ps, idx_rc, tf)
     out["reference_cost_all_cores"] = dict(entry(rc, idx_rc, threads), note="RECALC_08 and the dipole-tilt chain on every plasma call, as the Fortran adapters do;" + note)
     if not short:  # the two statements of the arithmetic must agree bit for bit
-        out["faithful_equals_dedup"] = bool(np.array_equal(fa["last_row"], full["last_row"], equal_nan=True) and np.array_equal(fa["nrows"], full["nrows"]))
-    return out, (idx_all, full)
+        at = np.searchsorted(idx_par, idx_all)
+        out["faithful_equals_dedup"] = bool(np.array_equal(fa["last_row"], full["last_row"][at], equal_nan=True) and np.array_equal(fa["nrows"], full["nrows"][at]))
+    return out, (idx_par, full)
 
 
 def parity_check(summary_rows, idx, cpu):
@@ -393,8 +395,8 @@ def measure(C, name, steps, warmup, e2e_steps, with_cpu, cpu_sizes):
                "roofline": roofline, "kernel": ki, "config": config_dict(C.world, name, nrays, nglobal)}
         if with_cpu:
             threads = os.cpu_count() or 1
-            n_all, n_one, short = cpu_sizes(threads)
-            modes, (cidx, crun) = cpu_baselines(kind, model_path, 1 if kind == "grid" else 0, pos0, dir0, w0, params, n_all, n_one, threads, short)
+            n_dedup, n_all, n_one, short = cpu_sizes(threads)
+            modes, (cidx, crun) = cpu_baselines(kind, model_path, 1 if kind == "grid" else 0, pos0, dir0, w0, params, n_dedup, n_all, n_one, threads, short)
             d = modes["dedup_all_cores"]
             out["cpu_baseline"] = {"value": d["value"], "unit": UNIT, "cores": d["cores"], "kind": "port",
                                    "sample": "%d whole rays strided out of the launch set, %.1f s, one dynamic ray queue; de-duplicated evaluation order (same algorithmic work as "
@@ -405,6 +407,56 @@ def measure(C, name, steps, warmup, e2e_steps, with_cpu, cpu_sizes):
             ok = (mine < len(idx)) & (idx[np.minimum(mine, len(idx) - 1)] == cidx)
             sel = {k: v[ok] if isinstance(v, np.ndarray) else v for k, v in crun.items()}
             out["parity_checked_rays"], out["parity_mismatches"] = parity_check(summary_h, mine[ok], sel)
+    model.close()
+    return out
+
+
+def measure_damping(C, with_cpu):
+    """BASELINE config 5: Landau damping along every ray of the C3 run (damping mode 1, Kp = 4, AE = 3, no geometric
+    factor: the defaults of damping_main.cpp:54-61).  Rank 0 only.  value = trajectory rows damped per second through
+    srt_result_damping (rows H2D + the two kernels + power D2H); the CPU figure is the REFERENCE's own binary
+    (oracle/_ref/damping, one core: it is single-threaded) on a strided sample of the same rays, whose powers are also
+    compared with the GPU's."""
+    if C.rank != 0:
+        return None
+    import subprocess
+    import tempfile as tf
+    srt = C.srt
+    from stanford_raytracer_b200 import damping
+    pos0, dir0, w0, params, cfg = lattice("c3", 1)
+    model, _ = make_model(srt, "c3", cfg, C.local_rank)
+    res = srt.raytracer_run(model, pos0, dir0.copy(), w0, outputper=100, **params)
+    damping.damp_result(res)  # warm-up
+    t0 = time.perf_counter()
+    reps = 2
+    for _ in range(reps):
+        first, power = damping.damp_result(res)
+    dt = (time.perf_counter() - t0) / reps
+    out = {"metric": "damped_trajectory_rows_per_sec", "unit": "rows/s", "value": res.total_rows / dt, "rows": int(res.total_rows), "rays": int(res.nrays),
+           "seconds_per_pass": dt, "h2d_bytes": int(res.total_rows * 160), "d2h_bytes": int(res.total_rows * 8),
+           "config": "C5: the C3 run's rows (outputper 100) -> damping mode 1, Kp 4, AE 3, geom_factor 0", "gpu_launches": 2 * reps,
+           "work": "per row 50 Gauss-Legendre nodes x 3 resonances x (8 phase-space-density evaluations + 4 Bessel functions)"}
+    ref = os.path.join(ROOT, "oracle", "_ref", "damping")
+    if with_cpu and os.path.exists(ref):
+        idx = np.unique(np.linspace(0, len(w0) - 1, 96).astype(int))
+        sub = srt.raytracer_run(model, pos0[idx], dir0[idx].copy(), w0[idx], outputper=100, **params)
+        with tf.TemporaryDirectory() as d:
+            import shutil
+            shutil.copy(os.path.join(ROOT, "oracle", "_ref", "crres_clean.bin"), os.path.join(d, "crres_clean.bin"))
+            sub.write_text(os.path.join(d, "in.ray"))
+            t0 = time.perf_counter()
+            subprocess.run([ref, "-i", "in.ray", "-o", "out.damp"], cwd=d, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            t_ref = time.perf_counter() - t0
+            a = np.loadtxt(os.path.join(d, "out.damp")).reshape(-1, 3)
+        f2, p2 = damping.damp_result(sub)
+        big = np.isfinite(a[:, 2]) & (a[:, 2] > 1e-6)
+        rel = np.abs(p2[big] / a[big, 2] - 1.0)
+        out["cpu_baseline"] = {"value": sub.total_rows / t_ref, "unit": "rows/s", "cores": 1, "kind": "reference",
+                               "sample": "%d rays strided out of the 100k (%d rows), %.1f s incl. reading the ray file; the reference's own damping binary (single-threaded)" % (len(idx), sub.total_rows, t_ref)}
+        out["parity"] = {"rows_compared": int(big.sum()), "max_relative_difference": float(rel.max()) if rel.size else 0.0, "tolerance": 1e-6,
+                         "nan_rows_agree": bool(np.array_equal(np.isfinite(a[:, 2]), np.isfinite(p2)))}
+        sub.close()
+    res.close()
     model.close()
     return out
 
@@ -469,22 +521,27 @@ def main():
     e2e_steps = 0 if args.no_e2e else max(1, min(args.steps, 3))
     with_cpu = not args.no_cpu_baseline
 
-    def c2_cpu(threads):
-        return max(threads, 256), max(8, 256 // max(threads, 1)), {}
+    def c2_cpu(threads):  # rays of: the de-duplicated all-cores run (= parity sample), the faithful all-cores runs, the 1-core runs
+        return 1024, max(threads, 256), max(8, 256 // max(threads, 1)), {}
+    # (the de-duplicated all-cores run doubles as the parity sample: cpu_baselines() takes n_all rays for it)
 
     def c3_cpu(threads):  # the faithful statement of a gridded ray is a dense 64x64 product per species and query: shortened rays there
-        return max(threads, 64), 4, {"maxsteps": 300}
+        return 256, max(threads, 64), 4, {"maxsteps": 300}
 
     main_out = measure(C, args.workload, args.steps, args.warmup, e2e_steps, with_cpu, c3_cpu if WORKLOADS[args.workload][4] == "grid" else c2_cpu)
     extras = {}
     if args.extras != "none":
-        names = ["c3", "c4_100k"] + (["c4"] if C.world >= 8 else []) if args.extras == "auto" else [s for s in args.extras.split(",") if s]
+        names = (["c3", "c4_100k"] + (["c4"] if C.world >= 8 else [])) if args.extras == "auto" else [s for s in args.extras.split(",") if s]
         for nm in names:
             if nm == args.workload or nm not in WORKLOADS:
                 continue
             o = measure(C, nm, 2, 1, 0 if args.no_e2e else 1, with_cpu and nm == "c3", c3_cpu if WORKLOADS[nm][4] == "grid" else c2_cpu)
             if C.rank == 0:
                 extras[nm] = o
+        if args.extras == "auto" or "c5" in names:
+            o = measure_damping(C, with_cpu)
+            if C.rank == 0:
+                extras["c5"] = o
     if C.rank == 0:
         m = main_out
         line = {"metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": C.world, "steps": args.steps, "warmup": args.warmup,

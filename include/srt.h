@@ -141,6 +141,23 @@ int srt_kernel_info(const srt_model* m, int64_t nrays, int* mode, int* regs, int
  * or DMUL+DADD pairs (fma=0) per thread on a full grid; returns achieved GFLOP/s in *gflops. */
 int srt_fp64_peak(int fma, int iters, double* gflops);
 
+/* ---- damping along the ray (BASELINE config 5): the reference's post-processor `damping` in its default mode 1
+ * (damping/src/damping_main.cpp:131-143 -> damping_foust, damping/src/damping_foust.cpp:15-236), for all rays of a run.
+ *   rows       [nrows][SRT_ROW_DOUBLES], the recorded rows of ray 0, then ray 1, ... (what damping reads back from the
+ *              output file, damping/src/wipp_fileutils.cpp:6-170); first_row[nrays] = index of each ray's first row
+ *   w[nrays]   wave angular frequency; qs, ms [nspec]: the species constants of the run
+ *   Kp, AE_level, yearday, msec, include_geom_factor: the options -k -a -t -u -v of damping_main.cpp:44-98
+ *   crres_table: path of the CRRES flux table (stanford_raytracer_b200/data/crres_clean.bin, tools/gen_crres_table.py)
+ *   power[nrows]: relative wave power at every row (1 at each ray's first row) -- the third column of the file
+ *              write_damping emits (wipp_fileutils.cpp:234-252). */
+int srt_damping_foust(int64_t nrays, const int64_t* first_row, int64_t nrows, const double* rows, const double* w, int nspec, const double* qs,
+                      const double* ms, double Kp, double AE_level, int yearday, int msec, int include_geom_factor, const char* crres_table,
+                      double* power);
+/* the same for every ray of a batch result, rows taken in ray order; first_row[nrays] and power[total rows] are the caller's */
+int srt_result_damping(const srt_result* r, const srt_model* m, const double* w0 /*[nrays]*/, double Kp, double AE_level, int yearday, int msec,
+                       int include_geom_factor, const char* crres_table, int64_t* first_row, double* power);
+const char* srt_damping_last_error(void);
+
 /* ---- the driver's two text formats (host side, no GPU; srt_io.cpp) ------------------------------------------------
  * Text of n doubles under the ES24.15E3 edit descriptor (driver:1197-1217), 24 characters each, no terminator. */
 int srt_format_es24(const double* v, int64_t n, char* out /*[24*n]*/);

@@ -44,13 +44,15 @@ def build(force=False, verbose=False):
         extra = (["-Xptxas", "-v"] if verbose else [])
         # two translation units, compiled concurrently: the thread-per-ray kernel + C ABI and the
         # team-of-8 kernel in two register budgets; elementary functions inlined in both; see srt_team_tu.cu
-        objs = [os.path.join(HERE, "srt_api.o"), os.path.join(HERE, "srt_team_tu.o")]
+        objs = [os.path.join(HERE, "srt_api.o"), os.path.join(HERE, "srt_team_tu.o"), os.path.join(HERE, "srt_damping.o")]
         procs = [subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-DSRT_INLINE_MATH", "-c", "-o", objs[0], os.path.join(CSRC, "srt_api.cu")]),
                  subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-DSRT_INLINE_MATH", "-DSRT_INLINE_STIX", "-DSRT_INLINE_PLASMA", "-DSRT_INLINE_ACCEPT", "-c", "-o", objs[1], os.path.join(CSRC, "srt_team_tu.cu")])]
+        # damping along the ray (config 5): its own unit
+        procs.append(subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-c", "-o", objs[2], os.path.join(CSRC, "srt_damping.cu")]))
         # host-only unit (text formats of the driver), plain g++
         gxx = shutil.which("g++") or "g++"
         objs.append(os.path.join(HERE, "srt_io.o"))
-        procs.append(subprocess.Popen([gxx, "-O2", "-std=c++17", "-fPIC", "-pthread", "-c", "-o", objs[2], os.path.join(CSRC, "srt_io.cpp")]))
+        procs.append(subprocess.Popen([gxx, "-O2", "-std=c++17", "-fPIC", "-pthread", "-c", "-o", objs[3], os.path.join(CSRC, "srt_io.cpp")]))
         for pr in procs:
             if pr.wait() != 0:
                 raise subprocess.CalledProcessError(pr.returncode, pr.args)
