@@ -8,6 +8,12 @@
 #pragma once
 #include <float.h>
 #include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "srt_damping_row.h"
 
 namespace srt_host {
 
@@ -121,6 +127,50 @@ inline void gauss_legendre_tbl(int n, double* x, double* w, double eps) {
     x[(m - 1) - (i - 1)] = x1;
     w[(m - 1) - (i - 1)] = w1;
   }
+}
+
+// The per-call constants of the kernels and the part of the CRRES table they read: Lvec[nL], MLTvec[nM], then
+// J_int[nE][nL * nM] of the energy channels of the AE level in use, in file order (psd_model.cpp:158-215).
+// Returns 0, -1 (table cannot be read), -2 (bad AE level / arguments).
+inline int damp_setup(const char* crres_table, int nspec, const double* qs, const double* ms, double Kp, double AE_level, int yearday, int msec,
+                      int include_geom_factor, DampSetup& S, std::vector<double>& tab, char* err, size_t errcap) {
+  memset(&S, 0, sizeof S);
+  FILE* f = fopen(crres_table, "rb");
+  if (!f) { snprintf(err, errcap, "cannot open CRRES table %s", crres_table); return -1; }
+  int hdr[4];
+  if (fread(hdr, 4, 4, f) != 4 || hdr[0] != 0x53525443) { fclose(f); snprintf(err, errcap, "%s is not a CRRES table", crres_table); return -1; }
+  const int n = hdr[1], nL = hdr[2], nM = hdr[3];
+  const size_t per = 2 + (size_t)nL + nM + (size_t)nL * nM;
+  std::vector<double> raw(per * n);
+  const size_t got = fread(raw.data(), 8, raw.size(), f);
+  fclose(f);
+  if (got != raw.size()) { snprintf(err, errcap, "%s is truncated", crres_table); return -1; }
+  gauss_legendre_tbl(50, S.glx, S.glw, 1e-10);
+  int itime[2] = {yearday, msec};
+  sm_to_mag_matrix(itime, S.sm2mag);
+  S.greenwich_lon_deg = greenwich_mag_lon_deg(itime);
+  S.ut_hr = msec / 1000.0 / 60.0;
+  S.Kp = Kp;
+  S.AE_target = round(AE_level);
+  if (S.AE_target < 1 || S.AE_target > 3) { snprintf(err, errcap, "AE level must round to 1, 2 or 3"); return -2; }
+  S.include_geom = include_geom_factor ? 1 : 0;
+  S.nspec = nspec;
+  for (int i = 0; i < nspec; ++i) { S.qs[i] = qs[i]; S.ms[i] = ms[i]; }
+  S.nL = nL; S.nM = nM; S.nE = 0;
+  std::vector<double> J;
+  tab.clear();
+  for (int k = 0; k < n; ++k) {
+    const double* e = raw.data() + per * k;
+    if (e[1] != S.AE_target) continue;
+    if (S.nE == 0) tab.assign(e + 2, e + 2 + nL + nM);
+    if (S.nE < 4) {
+      S.logE[S.nE++] = log(e[0]);
+      J.insert(J.end(), e + 2 + nL + nM, e + per);
+    }
+  }
+  if (S.nE < 2) { snprintf(err, errcap, "CRRES table has no entries for AE level %g", S.AE_target); return -1; }
+  tab.insert(tab.end(), J.begin(), J.end());
+  return 0;
 }
 
 }  // namespace srt_host

@@ -16,8 +16,15 @@ import common
 
 REF = os.path.join(common.ROOT, "oracle", "_ref", "damping")
 GOLD = os.path.join(common.ROOT, "tests", "golden")
-CASES = [("damping_ref_AE3_Kp4_geom0.damp", ["-a", "3", "-k", "4", "-v", "0", "-u", "0"]),
-         ("damping_ref_AE1_Kp2.5_geom1.damp", ["-a", "1", "-k", "2.5", "-v", "1", "-u", "43200000"])]
+# (the reference's getopt string "i:o:m:a:k:t:u:" lacks v, so `-v 1` is ignored by damping_main.cpp:80: the long option works)
+CASES = [("damping_ref_AE3_Kp4_geom0.damp", ["-a", "3", "-k", "4", "--geom_factor", "0", "-u", "0"]),
+         ("damping_ref_AE1_Kp2.5_geom1.damp", ["-a", "1", "-k", "2.5", "--geom_factor", "1", "-u", "43200000"]),
+         ("damping_ref_AE2_Kp5.5_geom0.damp", ["-a", "2", "-k", "5.5", "--geom_factor", "0", "-u", "21600000"])]
+
+
+def case_options(args):
+    kw = dict(zip(args[0::2], args[1::2]))
+    return dict(AE_level=float(kw["-a"]), Kp=float(kw["-k"]), geom_factor=kw["--geom_factor"] == "1", msec=int(kw["-u"]), yearday=2010001)
 
 
 def run_reference_damping(inp, out, args, cwd):
@@ -60,7 +67,78 @@ def probe():
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", out, srcs[0], srcs[1]])
     L = C.CDLL(out)
     L.probe_greenwich.restype = C.c_double
+    L.probe_set_perturbation.argtypes = [C.c_double] * 3
+    L.probe_damping.argtypes = [C.c_long, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_int,
+                                C.c_int, C.c_char_p, C.c_void_p]
     return L
+
+
+def load_rows(path):
+    """rows of an output file as the damping entry points take them: (first[nrays], rows[n][20], w[nrays], qs, ms, raynums, times)"""
+    from stanford_raytracer_b200 import rayfile
+    rays = rayfile.read_output(path)
+    nums = sorted(rays)
+    rows = []
+    for k in nums:
+        r = rays[k]
+        ns = np.zeros((len(r["time"]), 4))
+        ns[:, :r["nspec"]] = r["Ns"]
+        rows.append(np.concatenate([r["time"][:, None], r["pos"], r["vprel"], r["vgrel"], r["n"], r["B0"], ns], axis=1))
+    n = [len(r) for r in rows]
+    first = np.concatenate([[0], np.cumsum(n)[:-1]]).astype(np.int64)
+    return first, np.ascontiguousarray(np.concatenate(rows)), np.array([rays[k]["w"] for k in nums]), np.ascontiguousarray(rays[nums[0]]["qs"]), np.ascontiguousarray(rays[nums[0]]["ms"])
+
+
+def host_damping(probe, path, AE_level, Kp, geom_factor, msec, yearday, perturb=(0.0, 0.0, 0.0)):
+    """the GPU path's arithmetic (csrc/srt_damping_row.h) run on the host with glibc (tests/csrc/damping_probe.cpp)"""
+    first, rows, w, qs, ms = load_rows(path)
+    power = np.zeros(len(rows))
+    table = os.path.join(common.ROOT, "stanford_raytracer_b200", "data", "crres_clean.bin")
+    probe.probe_set_perturbation(*perturb)
+    rc = probe.probe_damping(len(first), first.ctypes.data, len(rows), rows.ctypes.data, w.ctypes.data, len(qs), qs.ctypes.data, ms.ctypes.data, Kp, AE_level,
+                             yearday, msec, int(geom_factor), table.encode(), power.ctypes.data)
+    probe.probe_set_perturbation(0.0, 0.0, 0.0)
+    assert rc == 0
+    return power
+
+
+def conditioning(probe, path, **opts):
+    """Per row: the largest relative change of the power when ONE fitted density parameter (power-law exponent, its
+    amplitude, the plasmapause L) is moved by one unit in the last place -- how well the reference's own answer is
+    determined.  The integrand differentiates the density with a relative step of 1e-8 (integrand.cpp:99-160), so this is
+    1e-8 for benign rows and reaches 1e-2 for rays that cross the plasmapause region far out (measured)."""
+    base = host_damping(probe, path, **opts)
+    cond = np.zeros(len(base))
+    eps = 2.220446049250313e-16
+    for pert in ((eps, 0, 0), (0, eps, 0), (0, 0, eps), (-eps, 0, 0)):
+        p = host_damping(probe, path, perturb=pert, **opts)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            c = np.abs(p / base - 1.0)
+        cond = np.maximum(cond, np.where(np.isfinite(c), c, 0.0))
+    return base, cond
+
+
+def assert_power_agrees(got, ref, cond, what, slack=100.0, floor=1e-6):
+    """|got / ref - 1| <= floor + slack * (1-ulp conditioning of the row) wherever the reference's power is above its own
+    cut-off 1e-6 (WAVE_PWR_THRESH, consts.h); NaN rows agree."""
+    assert np.array_equal(np.isfinite(got), np.isfinite(ref)), what
+    big = np.isfinite(ref) & (ref > 1e-6)
+    rel = np.abs(got[big] / ref[big] - 1.0)
+    bound = floor + slack * cond[big]
+    bad = rel > bound
+    assert not bad.any(), (what, int(bad.sum()), float(rel[bad].max()), float(bound[bad].min()))
+    return rel
+
+
+@pytest.mark.parametrize("name,args", CASES)
+def test_gpu_arithmetic_on_the_host_against_the_reference(ref_binary, probe, name, args):
+    """same inputs, same libm, two statements of the algorithm (the reference's; the kernels' row arithmetic run sequentially):
+    they agree to the rows' own conditioning, and to 1e-8 in the median"""
+    path = os.path.join(GOLD, "damping_in.ray")
+    ref = np.loadtxt(os.path.join(GOLD, name)).reshape(-1, 3)[:, 2]
+    base, cond = conditioning(probe, path, **case_options(args))
+    rel = assert_power_agrees(base, ref, cond, name)
+    assert np.median(rel) < 1e-5 and ref.min() < 0.9  # one ill-conditioned row moves every later row of its ray (running product)
 
 
 def test_gauss_legendre_table(probe):
