@@ -453,8 +453,12 @@ def measure_damping(C, with_cpu):
         rel = np.abs(p2[big] / a[big, 2] - 1.0)
         out["cpu_baseline"] = {"value": sub.total_rows / t_ref, "unit": "rows/s", "cores": 1, "kind": "reference",
                                "sample": "%d rays strided out of the 100k (%d rows), %.1f s incl. reading the ray file; the reference's own damping binary (single-threaded)" % (len(idx), sub.total_rows, t_ref)}
-        out["parity"] = {"rows_compared": int(big.sum()), "max_relative_difference": float(rel.max()) if rel.size else 0.0, "tolerance": 1e-6,
-                         "nan_rows_agree": bool(np.array_equal(np.isfinite(a[:, 2]), np.isfinite(p2)))}
+        out["parity"] = {"rows_compared": int(big.sum()), "median_relative_difference": float(np.median(rel)) if rel.size else 0.0,
+                         "rows_within_1e-6": float((rel <= 1e-6).mean()) if rel.size else 1.0, "rows_within_1e-3": float((rel <= 1e-3).mean()) if rel.size else 1.0,
+                         "max_relative_difference": float(rel.max()) if rel.size else 0.0,
+                         "nan_rows_agree": bool(np.array_equal(np.isfinite(a[:, 2]), np.isfinite(p2))),
+                         "note": "floating point: the reference's own answer moves by 1e-8 ... 1e-2 when a fitted density parameter moves by 1 ulp (finite differences with "
+                                 "relative step 1e-8); the per-row bound is checked in tests/test_gpu_damping.py"}
         sub.close()
     res.close()
     model.close()

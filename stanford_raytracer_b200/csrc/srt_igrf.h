@@ -5,6 +5,7 @@
 #include "srt_physics.h"
 
 SRT_HDN void srt_igrf_gsw(const SrtIgrf& ig, float xgsw, float ygsw, float zgsw, float& hxgsw, float& hygsw, float& hzgsw) {
+  SRT_COUNT(SRT_T_IGRF);
   // GEOGSW_08, J < 0
   float xgeo = ig.a11 * xgsw + ig.a21 * ygsw + ig.a31 * zgsw;
   float ygeo = ig.a12 * xgsw + ig.a22 * ygsw + ig.a32 * zgsw;

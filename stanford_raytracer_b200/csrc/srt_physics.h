@@ -273,6 +273,7 @@ SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT
 //   grid: fortran/interp_dens_model_adapter.f95:148-269
 template <int DENS, int USE_IGRF>
 SRT_HDP void srt_plasma(SrtModelRef MR, const double x[3], SrtPlasma& o) {
+  SRT_COUNT(SRT_T_PLASMA);
   const SrtModel& M = MR.get();
   double p[3] = {0.0, 0.0, 0.0};
   double sph = 0.0, cph = 0.0, sth = 0.0, cth = 0.0;
@@ -306,6 +307,7 @@ SRT_HDP void srt_plasma(SrtModelRef MR, const double x[3], SrtPlasma& o) {
 // plasma-only parts of stix_parameters (raytracer.f95:92-93) and of the free-space
 // test (raytracer.f95:65)
 SRT_HDS void srt_plasma_derive(SrtModelRef MR, const SrtPlasma& pl, SrtPlasmaDerived& d) {
+  SRT_COUNT(SRT_T_DERIVE);
   const SrtModel& M = MR.get();
   d.B0[0] = pl.B0[0]; d.B0[1] = pl.B0[1]; d.B0[2] = pl.B0[2];
   d.B0sq = srt_dot3(pl.B0, pl.B0);
@@ -322,6 +324,7 @@ SRT_HDS void srt_plasma_derive(SrtModelRef MR, const SrtPlasma& pl, SrtPlasmaDer
 
 // stix_parameters, raytracer.f95:96-100
 SRT_HDS void srt_stix(const SrtPlasmaDerived& d, double w, SrtStix& s) {
+  SRT_COUNT(SRT_T_STIX);
   double sr = 0.0, sl = 0.0, sp = 0.0;
 #pragma unroll
   for (int i = 0; i < SRT_NSPEC; ++i) sr = sr + d.wps2[i] / (w * (w + d.wcs[i]));
@@ -339,6 +342,7 @@ SRT_HDS void srt_stix(const SrtPlasmaDerived& d, double w, SrtStix& s) {
 
 // dispersion_relation after the Stix parameters are known (raytracer.f95:50-68)
 SRT_HDS double srt_F(const double n[3], double w, const SrtPlasmaDerived& d, const SrtStix& s) {
+  SRT_COUNT(SRT_T_FTAIL);
   double nmag2 = srt_dot3(n, n);
   double nb = srt_dot3(n, d.B0);
   double cos2phi = (nb * nb) / (nmag2 * d.B0sq);
@@ -492,6 +496,7 @@ SRT_HD SrtCplx srt_cmul(SrtCplx a, SrtCplx b) {
 // magnitude, and the reference's angle has the sign of v1*v2.  Mr is diagonalised by
 // cyclic Jacobi rotations.
 SRT_HDE bool srt_is_right_handed(double n2, double phi_deg, double S, double D, double P) {
+  SRT_COUNT(SRT_T_HAND);
   double sphi, cphi;
   srt_sincos(phi_deg, sphi, cphi);
   double d0 = (double)(float)(S - n2 * (cphi * cphi));
@@ -557,6 +562,7 @@ SRT_HDE bool srt_is_right_handed(double n2, double phi_deg, double S, double D, 
 // the Stix set at (x, w) supplied.  Returns the complex root selected by `root`
 // (1: k1, else k2), i.e. what raytracer_run picks at :685-689 / :828-836.
 SRT_HDE SrtCplx srt_solve_root(const double k[3], double w, const SrtPlasmaDerived& d, const SrtStix& s, int root) {
+  SRT_COUNT(SRT_T_ROOT);
   const double C = srt_c_light();
   double kb = srt_dot3(k, d.B0);
   double cos2phi = (kb * kb) / (srt_dot3(k, k) * d.B0sq);

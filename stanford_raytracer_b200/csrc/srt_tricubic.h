@@ -159,6 +159,7 @@ extern __shared__ unsigned long long srt_stage_smem[];  // the team kernel's dyn
 
 // Ns(1:4) = exp(tricubic(log-density)) at x (SM, metres)
 SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT_NSPEC]) {
+  SRT_COUNT(SRT_T_TRICUBIC);
   const int is0 = srt_grid_locate(g.xs, g.nx, g.minx, g.delx, x[0]);
   const int js0 = srt_grid_locate(g.ys, g.ny, g.miny, g.dely, x[1]);
   const int ks0 = srt_grid_locate(g.zs, g.nz, g.minz, g.delz, x[2]);

@@ -12,6 +12,29 @@
 #include "../../stanford_raytracer_b200/csrc/srt_igrf_setup.h"
 #endif
 
+#if defined(SRT_TALLY)
+thread_local long long srt_tally[SRT_T_COUNT];
+// per-attempt tallies of the current thread's last emu_trace_tally call: [accepted | rejected+cone][SRT_T_COUNT], attempts of each kind
+static thread_local long long g_tally_sum[2][SRT_T_COUNT], g_tally_n[2];
+template <int D, int I>
+static void run_tally(const SrtModel& M, const SrtRunParams& P, const double* pos0, double* dir0, double w0) {
+  SrtRayState st;
+  double row[SRT_ROW_DOUBLES];
+  srt_ray_init<D, I>(SrtModelRef{&M}, P, pos0, dir0, w0, st, row);
+  for (;;) {
+    long long before[SRT_T_COUNT];
+    memcpy(before, srt_tally, sizeof before);
+    const bool nan_state = st.x[0] != st.x[0] && st.k[0] != st.k[0];  // fast-forwarded on the GPU: not integrated work
+    int r = srt_ray_attempt<D, I>(SrtModelRef{&M}, P, st, row);
+    if (r == SRT_ATTEMPT_DONE) break;
+    if (nan_state) continue;
+    const int kind = (r == SRT_ATTEMPT_ACCEPTED) ? 0 : 1;
+    for (int i = 0; i < SRT_T_COUNT; ++i) g_tally_sum[kind][i] += srt_tally[i] - before[i];
+    ++g_tally_n[kind];
+  }
+}
+#endif
+
 template <int D, int I>
 static long run_one(const SrtModel& M, const SrtRunParams& P, const double* pos0, double* dir0, double w0, double* rows, long max_rows,
                     int* stopcond, long* nrej, long* ncone, int* cone_exit) {
@@ -121,6 +144,24 @@ int emu_is_right_handed(double n2, double phi, double S, double D, double P) { r
 void emu_is_right_handed_n(long n, const double* n2, const double* phi, const double* S, const double* D, const double* P, int* out) {
   for (long i = 0; i < n; ++i) out[i] = srt_is_right_handed(n2[i], phi[i], S[i], D[i], P[i]) ? 1 : 0;
 }
+
+#if defined(SRT_TALLY)
+// out[2][SRT_T_COUNT + 1]: per kind (accepted, rejected) the summed counts of this ray's attempts and the number of attempts
+void emu_trace_tally(void* m, const double* pos0, double* dir0, double w0, double dt0, double dtmax, double maxerr, int maxsteps, double minalt, int root,
+                     double tmax, int fixedstep, long long* out) {
+  const SrtModel& M = *(SrtModel*)m;
+  SrtRunParams P = {dt0, dtmax, maxerr, minalt, tmax, maxsteps, root, fixedstep, 1};
+  memset(g_tally_sum, 0, sizeof g_tally_sum);
+  g_tally_n[0] = g_tally_n[1] = 0;
+  if (M.density == SRT_DENS_NGO) { if (M.use_igrf) run_tally<0, 1>(M, P, pos0, dir0, w0); else run_tally<0, 0>(M, P, pos0, dir0, w0); }
+  else { if (M.use_igrf) run_tally<1, 1>(M, P, pos0, dir0, w0); else run_tally<1, 0>(M, P, pos0, dir0, w0); }
+  for (int k = 0; k < 2; ++k) {
+    for (int i = 0; i < SRT_T_COUNT; ++i) out[k * (SRT_T_COUNT + 1) + i] = g_tally_sum[k][i];
+    out[k * (SRT_T_COUNT + 1) + SRT_T_COUNT] = g_tally_n[k];
+  }
+}
+int emu_tally_slots(void) { return SRT_T_COUNT; }
+#endif
 
 long emu_trace_summary(void* m, const double* pos0, double* dir0, double w0, double dt0, double dtmax, double maxerr, int maxsteps, double minalt,
                        int root, double tmax, int fixedstep, double* last_row, int* stopcond, long* nrej) {
