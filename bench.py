@@ -353,19 +353,27 @@ def measure(C, name, steps, warmup, e2e_steps, with_cpu, cpu_sizes):
             res.close()
             return acc, rws
 
-        one()  # warm-up (page-locked row buffers are created once and pooled)
-        barrier()
-        t0 = time.perf_counter()
-        acc = rws = 0
-        for _ in range(e2e_steps):
-            a, r_ = one()
-            acc += a
-            rws = r_
-        torch.cuda.synchronize()
-        t_e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        try:
+            one()  # warm-up (page-locked row buffers are created once and pooled)
+            barrier()
+            t0 = time.perf_counter()
+            acc = rws = 0
+            for _ in range(e2e_steps):
+                a, r_ = one()
+                acc += a
+                rws = r_
+            torch.cuda.synchronize()
+            t_e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            failed = None
+        except Exception as ex:  # (raised on every rank together, shard.run_sharded) e.g. no room for the row buffers in host memory
+            failed = "%s: %s" % (type(ex).__name__, ex)
+            t_e = torch.tensor([1.0], dtype=torch.float64, device=dev)
+            acc = rws = 0
         if C.world > 1:
             dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
-        if C.rank == 0:
+        if C.rank == 0 and failed:
+            e2e["error"] = failed
+        elif C.rank == 0:
             e2e = {"value": acc / float(t_e.item()), "unit": UNIT, "h2d_bytes_per_step": int(nglobal * 56),
                    "d2h_bytes_per_step": int(rws * 160 + nglobal * (srt.SUMMARY_WORDS * 8 + 4 + 56) + 64 * C.world),
                    "gather": "per-ray records (256 B) over gloo, rows mapped from the owners' shared-memory segments" if C.world > 1 else "single process"}

@@ -137,6 +137,9 @@ int64_t srt_launch_count(void);
 /* which trace kernel a batch of nrays rays runs (mode 0: one thread per ray, 1: team of 8 lanes per ray;
  * SRT_KERNEL=thread|team overrides), its registers/thread, local bytes/thread, blocks/SM, persistent grid, block */
 int srt_kernel_info(const srt_model* m, int64_t nrays, int* mode, int* regs, int* local_bytes, int* blocks_per_sm, int* grid, int* block);
+/* Self-test: the interleaved IEEE division of the kernels (srt_divn, csrc/srt_math.h) against the compiler's `/` on
+ * 4 * ngroups pseudo-random operand pairs incl. zeros, infinities, NaNs and subnormals; *mismatches = results that differ. */
+int srt_selftest_div(int64_t ngroups, uint64_t seed, uint64_t* mismatches);
 /* FP64 pipe micro-benchmark used as the roofline denominator: runs `iters` dependent-free DFMA (fma=1)
  * or DMUL+DADD pairs (fma=0) per thread on a full grid; returns achieved GFLOP/s in *gflops. */
 int srt_fp64_peak(int fma, int iters, double* gflops);

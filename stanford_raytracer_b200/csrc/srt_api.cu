@@ -184,6 +184,47 @@ __global__ void srt_fd_kernel(double* __restrict__ nodes, int nx, int ny, int nz
   }
 }
 
+// Self-test of srt_divn (srt_math.h) against the compiler's own IEEE division: groups of four pseudo-random operand
+// pairs -- random bit patterns, i.e. every exponent incl. subnormals, infinities and NaNs, plus zeros, equal operands,
+// powers of two and mantissas of all ones -- one group in eight with an operand that forces the group onto the slow path.
+__device__ __forceinline__ unsigned long long srt_mix64(unsigned long long z) {
+  z += 0x9e3779b97f4a7c15ull;
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+  z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+  return z ^ (z >> 31);
+}
+__global__ void srt_divtest_kernel(long long ngroups, unsigned long long seed, unsigned long long* mismatches) {
+  unsigned long long bad = 0;
+  for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < ngroups; g += (long long)gridDim.x * blockDim.x) {
+    double a[4], b[4], q[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      unsigned long long ua = srt_mix64(seed + 8ull * (unsigned long long)g + 2 * i), ub = srt_mix64(seed + 8ull * (unsigned long long)g + 2 * i + 1);
+      const unsigned kind = (unsigned)(srt_mix64(ua ^ ub) & 63ull);
+      if (kind < 40) {  // moderate exponents (what the ray tracer divides): 2^-300 .. 2^300
+        ua = (ua & 0x800fffffffffffffull) | ((unsigned long long)(723 + (ua >> 52) % 600) << 52);
+        ub = (ub & 0x800fffffffffffffull) | ((unsigned long long)(723 + (ub >> 52) % 600) << 52);
+      } else if (kind == 40) ub = ua;                                   // equal operands
+      else if (kind == 41) ua &= 0xfff0000000000000ull;                 // power of two numerator
+      else if (kind == 42) ub |= 0x000fffffffffffffull;                 // divisor mantissa all ones
+      else if (kind == 43) ua = 0ull;                                   // zero numerator
+      else if (kind == 44) ub = (ub & 0x8000000000000000ull);           // zero divisor
+      else if (kind == 45) ua |= 0x000fffffffffffffull;
+      // else: raw random bit patterns (any exponent, NaN, Inf, subnormal)
+      a[i] = __longlong_as_double((long long)ua);
+      b[i] = __longlong_as_double((long long)ub);
+    }
+    srt_divn(a, b, q);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const double r = a[i] / b[i];
+      const bool same = (__double_as_longlong(r) == __double_as_longlong(q[i])) || (r != r && q[i] != q[i]);
+      bad += same ? 0ull : 1ull;
+    }
+  }
+  if (bad) atomicAdd(mismatches, bad);
+}
+
 }  // namespace
 
 // device copies of the grid arrays of a model (modelnum 3) on one device
@@ -589,6 +630,24 @@ int srt_model_eval(const srt_model* m, int64_t n, const double* x, double* out) 
   cudaFree(dx);
   cudaFree(dout);
   return rc;
+}
+
+int srt_selftest_div(int64_t ngroups, uint64_t seed, uint64_t* mismatches) {
+  if (!mismatches || ngroups < 0) return SRT_E_ARG;
+  DevCtx* c = nullptr;
+  int rc = current_ctx(&c);
+  if (rc) return rc;
+  unsigned long long* d = nullptr;
+  CK(cudaMalloc(&d, 8));
+  cudaMemset(d, 0, 8);
+  srt_divtest_kernel<<<c->num_sms * 8, 256>>>(ngroups, seed, d);
+  g_launches++;
+  unsigned long long h = 0;
+  cudaError_t e = cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) return cuda_fail(e, "srt_selftest_div");
+  *mismatches = h;
+  return SRT_OK;
 }
 
 int srt_kernel_info(const srt_model* m, int64_t nrays, int* mode, int* regs, int* local_bytes, int* blocks_per_sm, int* grid, int* block) {

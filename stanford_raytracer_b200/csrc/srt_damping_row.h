@@ -6,6 +6,7 @@
 #include <float.h>
 #include <math.h>
 #include <stddef.h>
+#include <string.h>
 #if defined(__CUDACC__)
 #define DMP_HD __host__ __device__
 #else
@@ -48,7 +49,27 @@ DMP_HD inline double psd_crres(const PsdState& s, double vperp, double vpar) {  
   double f = s.An_fit / pow(v, s.n_fit);
   return f * pow(100., 6.0);
 }
-DMP_HD inline double psd_hybrid(const PsdState& s, double vperp, double vpar) {  // :308-341
+#if defined(DMP_TEST_NOISE)
+// test hook (tests/csrc/damping_probe.cpp only): multiplies every density value by 1 +- amp, the sign a hash of the
+// arguments -- a stand-in for the last-place differences between two math libraries, to measure how well a row's
+// result is determined at all
+extern double dmp_test_noise_amp;
+extern unsigned long long dmp_test_noise_seed;
+inline double dmp_noise(double a, double b) {
+  unsigned long long x, y;
+  memcpy(&x, &a, 8); memcpy(&y, &b, 8);
+  unsigned long long z = (x * 0x9e3779b97f4a7c15ull) ^ (y + dmp_test_noise_seed);
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull; z = (z ^ (z >> 27)) * 0x94d049bb133111ebull; z ^= z >> 31;
+  return 1.0 + ((z & 1ull) ? dmp_test_noise_amp : -dmp_test_noise_amp);
+}
+#define DMP_NOISE(f, a, b) ((f) * dmp_noise(a, b))
+#else
+#define DMP_NOISE(f, a, b) (f)
+#endif
+
+DMP_HD inline double psd_hybrid_exact(const PsdState& s, double vperp, double vpar);
+DMP_HD inline double psd_hybrid(const PsdState& s, double vperp, double vpar) { return DMP_NOISE(psd_hybrid_exact(s, vperp, vpar), vperp, vpar); }
+DMP_HD inline double psd_hybrid_exact(const PsdState& s, double vperp, double vpar) {  // :308-341
   if (s.L_pp - s.L_sh > 1) return psd_suprathermal(vperp, vpar);
   if (s.L_sh - s.L_pp > 1) return psd_crres(s, vperp, vpar);
   double f_polar = psd_suprathermal(vperp, vpar);

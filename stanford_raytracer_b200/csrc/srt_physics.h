@@ -313,12 +313,19 @@ SRT_HDS void srt_plasma_derive(SrtModelRef MR, const SrtPlasma& pl, SrtPlasmaDer
   d.B0sq = srt_dot3(pl.B0, pl.B0);
   double B0mag = srt_sqrt(d.B0sq);
   double maxNs = pl.Ns[0];
+  // wps2 = (Ns*qs**2/ms/EPS0), wcs = (qs*B0mag)/ms: the divisions of the four species are independent (srt_divn)
+  double num[SRT_NSPEC], den[SRT_NSPEC], t1[SRT_NSPEC], eps0[SRT_NSPEC], qb[SRT_NSPEC];
 #pragma unroll
   for (int i = 0; i < SRT_NSPEC; ++i) {
-    d.wps2[i] = (pl.Ns[i] * M.q2[i] / M.ms[i] / SRT_EPS0);
-    d.wcs[i] = ((M.qs[i] * B0mag) / M.ms[i]);
+    num[i] = pl.Ns[i] * M.q2[i];
+    den[i] = M.ms[i];
+    eps0[i] = SRT_EPS0;
+    qb[i] = (M.qs[i] * B0mag);
     if (i > 0 && pl.Ns[i] > maxNs) maxNs = pl.Ns[i];
   }
+  srt_divn(num, den, t1);
+  srt_divn(t1, eps0, d.wps2);
+  srt_divn(qb, den, d.wcs);
   d.fs_thr = 100.0 * srt_sqrt((maxNs * M.fs_q2)) / M.fs_den;
 }
 
@@ -326,13 +333,24 @@ SRT_HDS void srt_plasma_derive(SrtModelRef MR, const SrtPlasma& pl, SrtPlasmaDer
 SRT_HDS void srt_stix(const SrtPlasmaDerived& d, double w, SrtStix& s) {
   SRT_COUNT(SRT_T_STIX);
   double sr = 0.0, sl = 0.0, sp = 0.0;
-#pragma unroll
-  for (int i = 0; i < SRT_NSPEC; ++i) sr = sr + d.wps2[i] / (w * (w + d.wcs[i]));
-#pragma unroll
-  for (int i = 0; i < SRT_NSPEC; ++i) sl = sl + d.wps2[i] / (w * (w - d.wcs[i]));
+  // the twelve quotients are independent of each other (srt_divn); the sums run in index order as Fortran's sum()
+  double dr[SRT_NSPEC], dl[SRT_NSPEC], dp[SRT_NSPEC], qr[SRT_NSPEC], ql[SRT_NSPEC], qp[SRT_NSPEC];
   double w2 = w * w;
 #pragma unroll
-  for (int i = 0; i < SRT_NSPEC; ++i) sp = sp + d.wps2[i] / w2;
+  for (int i = 0; i < SRT_NSPEC; ++i) {
+    dr[i] = (w * (w + d.wcs[i]));
+    dl[i] = (w * (w - d.wcs[i]));
+    dp[i] = w2;
+  }
+  srt_divn(d.wps2, dr, qr);
+  srt_divn(d.wps2, dl, ql);
+  srt_divn(d.wps2, dp, qp);
+#pragma unroll
+  for (int i = 0; i < SRT_NSPEC; ++i) sr = sr + qr[i];
+#pragma unroll
+  for (int i = 0; i < SRT_NSPEC; ++i) sl = sl + ql[i];
+#pragma unroll
+  for (int i = 0; i < SRT_NSPEC; ++i) sp = sp + qp[i];
   s.R = 1.0 - sr;
   s.L = 1.0 - sl;
   s.P = 1.0 - sp;

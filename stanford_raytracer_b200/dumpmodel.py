@@ -46,7 +46,13 @@ def dump(model, nx, ny, nz, extent, chunk=1 << 22):
     out = np.empty((len(P), 4 * NSPEC + 3))
     for i in range(0, len(P), chunk):
         out[i:i + chunk] = model.funcPlasmaParams(P[i:i + chunk])["raw"]
-    return out.reshape(int(nz), int(ny), int(nx), 4 * NSPEC + 3)
+    n = int(getattr(model, "nspec", NSPEC))
+    if n < NSPEC:
+        # the reference allocates f(nspec*4+3, nx, ny, nz) with the model's own nspec (dumpmodel.f95:1284-1289): a gridded
+        # file with fewer than four species dumps nspec columns per quantity, not four with phantom zeros
+        cols = [c + q * NSPEC for q in range(4) for c in range(n)] + [4 * NSPEC, 4 * NSPEC + 1, 4 * NSPEC + 2]
+        out = out[:, cols]
+    return out.reshape(int(nz), int(ny), int(nx), 4 * n + 3)
 
 
 def _es24_block(values):

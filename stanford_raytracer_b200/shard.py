@@ -123,7 +123,22 @@ def run_sharded(trace_fn, pos0, dir0, w0, rank=0, world=1, group=None):
     w0 = np.asarray(w0, dtype=np.float64).reshape(-1)
     nrays = len(w0)
     idx = shard_indices(nrays, rank, world)
-    mine = trace_fn(pos0[idx], dir0[idx].copy(), w0[idx])
+    err, mine = None, None
+    try:
+        mine = trace_fn(pos0[idx], dir0[idx].copy(), w0[idx])
+    except Exception as e:  # the gather below is collective: a rank that failed must not leave the others waiting
+        err = e
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        okay = torch.tensor([0 if err else 1], dtype=torch.int32)
+        dist.all_reduce(okay, op=dist.ReduceOp.MIN, group=group)
+        if int(okay.item()) == 0:
+            if mine is not None:
+                mine["keep"].close()
+            raise err if err else RuntimeError("the sharded trace failed on another rank")
+    elif err:
+        raise err
     if world == 1:
         metas, names, totals = [mine["meta"]], [[(s[0], s[1]) for s in mine["segments"]]], [mine["totals"]]
     else:

@@ -1,6 +1,9 @@
 // tests/csrc/damping_probe.cpp -- TEST-ONLY: the host set-up of the damping kernels (csrc/srt_damping_setup.h) next to the
 // stand-ins of the Fortran transforms the reference build links (oracle/ref_stubs/xform_d.cpp), for tests/test_damping_cpu.py.
+#define DMP_TEST_NOISE 1
 #include "../../stanford_raytracer_b200/csrc/srt_damping_setup.h"
+double dmp_test_noise_amp = 0.0;
+unsigned long long dmp_test_noise_seed = 0;
 extern "C" {
 void sm_to_mag_d_(int* itime, double* x_in, double* x_out);
 void geo_to_mag_d_(int* itime, double* x_in, double* x_out);
@@ -8,6 +11,7 @@ void geo_to_mag_d_(int* itime, double* x_in, double* x_out);
 // srt_damping_foust
 // test hook: relative perturbations applied to the fitted density parameters of every row (conditioning measurement)
 static double g_perturb[3] = {0.0, 0.0, 0.0};
+void probe_set_noise(double amp, unsigned long long seed) { dmp_test_noise_amp = amp; dmp_test_noise_seed = seed; }
 void probe_set_perturbation(double n_fit_rel, double An_fit_rel, double L_pp_rel) { g_perturb[0] = n_fit_rel; g_perturb[1] = An_fit_rel; g_perturb[2] = L_pp_rel; }
 int probe_damping(long nrays, const long* first, long nrows, const double* rows, const double* w, int nspec, const double* qs, const double* ms,
                   double Kp, double AE, int yearday, int msec, int geom, const char* table, double* power) {

@@ -68,6 +68,7 @@ def probe():
     L = C.CDLL(out)
     L.probe_greenwich.restype = C.c_double
     L.probe_set_perturbation.argtypes = [C.c_double] * 3
+    L.probe_set_noise.argtypes = [C.c_double, C.c_uint64]
     L.probe_damping.argtypes = [C.c_long, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_int,
                                 C.c_int, C.c_char_p, C.c_void_p]
     return L
@@ -89,29 +90,33 @@ def load_rows(path):
     return first, np.ascontiguousarray(np.concatenate(rows)), np.array([rays[k]["w"] for k in nums]), np.ascontiguousarray(rays[nums[0]]["qs"]), np.ascontiguousarray(rays[nums[0]]["ms"])
 
 
-def host_damping(probe, path, AE_level, Kp, geom_factor, msec, yearday, perturb=(0.0, 0.0, 0.0)):
+def host_damping(probe, path, AE_level, Kp, geom_factor, msec, yearday, perturb=(0.0, 0.0, 0.0), noise=(0.0, 0)):
     """the GPU path's arithmetic (csrc/srt_damping_row.h) run on the host with glibc (tests/csrc/damping_probe.cpp)"""
     first, rows, w, qs, ms = load_rows(path)
     power = np.zeros(len(rows))
     table = os.path.join(common.ROOT, "stanford_raytracer_b200", "data", "crres_clean.bin")
     probe.probe_set_perturbation(*perturb)
+    probe.probe_set_noise(*noise)
     rc = probe.probe_damping(len(first), first.ctypes.data, len(rows), rows.ctypes.data, w.ctypes.data, len(qs), qs.ctypes.data, ms.ctypes.data, Kp, AE_level,
                              yearday, msec, int(geom_factor), table.encode(), power.ctypes.data)
     probe.probe_set_perturbation(0.0, 0.0, 0.0)
+    probe.probe_set_noise(0.0, 0)
     assert rc == 0
     return power
 
 
 def conditioning(probe, path, **opts):
-    """Per row: the largest relative change of the power when ONE fitted density parameter (power-law exponent, its
-    amplitude, the plasmapause L) is moved by one unit in the last place -- how well the reference's own answer is
-    determined.  The integrand differentiates the density with a relative step of 1e-8 (integrand.cpp:99-160), so this is
-    1e-8 for benign rows and reaches 1e-2 for rays that cross the plasmapause region far out (measured)."""
+    """Per row: how well the reference's own answer is determined.  The largest relative change of the power when (a) ONE
+    fitted density parameter (power-law exponent, its amplitude, the plasmapause L) is moved by one unit in the last place,
+    (b) every phase-space-density value gets a +-1 ulp error (what separates two math libraries).  The integrand
+    differentiates the density with a relative step of 1e-8 (integrand.cpp:99-160), so this is ~1e-8 for benign rows and
+    reaches 1e-2 for rays that cross the plasmapause region far out (measured)."""
     base = host_damping(probe, path, **opts)
     cond = np.zeros(len(base))
     eps = 2.220446049250313e-16
-    for pert in ((eps, 0, 0), (0, eps, 0), (0, 0, eps), (-eps, 0, 0)):
-        p = host_damping(probe, path, perturb=pert, **opts)
+    runs = [dict(perturb=p) for p in ((eps, 0, 0), (0, eps, 0), (0, 0, eps), (-eps, 0, 0))] + [dict(noise=(eps, seed)) for seed in (1, 2, 3)]
+    for kw in runs:
+        p = host_damping(probe, path, **kw, **opts)
         with np.errstate(divide="ignore", invalid="ignore"):
             c = np.abs(p / base - 1.0)
         cond = np.maximum(cond, np.where(np.isfinite(c), c, 0.0))

@@ -46,6 +46,26 @@ def test_dump_file_format_round_trip(built, tmp_path):
     assert again.read_bytes() == p.read_bytes() or np.allclose(dm.read_dump(str(again))["f"], back["f"], rtol=1e-15, atol=0)
 
 
+def test_dump_of_a_three_species_model_has_three_columns_per_quantity(built, tmp_path):
+    """dumpmodel.f95:1284-1289 writes f(nspec*4+3, ...) with the model's own nspec: no phantom fourth species"""
+    from stanford_raytracer_b200 import dumpmodel as dm
+
+    class Fake:
+        nspec = 3
+
+        def funcPlasmaParams(self, x):
+            raw = np.tile(np.arange(19.0), (len(x), 1))
+            return {"raw": raw}
+
+    f = dm.dump(Fake(), 2, 2, 1, (0.0, 1.0, 0.0, 1.0, 0.0, 0.0))
+    assert f.shape == (1, 2, 2, 15)
+    assert f[0, 0, 0].tolist() == [0, 1, 2, 4, 5, 6, 8, 9, 10, 12, 13, 14, 16, 17, 18]
+    p = tmp_path / "d3.txt"
+    dm.write_dump(str(p), f, (0.0, 1.0, 0.0, 1.0, 0.0, 0.0))
+    assert p.read_text().split("\n")[0] == "%10d%10d%10d%10d" % (3, 2, 2, 1)
+    assert dm.read_dump(str(p))["f"].shape == (1, 2, 2, 15)
+
+
 @pytest.mark.gpu
 def test_dumpmodel_matches_oracle_through_the_file(built, tmp_path):
     import stanford_raytracer_b200 as srt
