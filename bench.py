@@ -389,7 +389,7 @@ def measure(C, name, steps, warmup, e2e_steps, with_cpu, cpu_sizes):
         hbm_ach = (rows * ROW_BYTES + nrays * (56 + srt.SUMMARY_WORDS * 8)) / avg_launch_s / 1e9
         ki = model.kernel_info(nrays)
         roofline = {"bound": "fp64", "achieved": achieved, "peak": C.peak_fma, "unit": "TFLOP/s", "frac": achieved / C.peak_fma,
-                    "traffic": traffic_from_profiles(name, ki),
+                    "traffic": traffic_from_profiles(name, ki, accepted),
                     "bound_note": "FP64 (non-tensor) pipe: the path is scalar FP64 with no dense contraction and ~1e-4 of HBM bandwidth, so neither 'hbm' nor 'tensor' applies",
                     "peak_source": "DFMA micro-kernel measured live (srt_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
                     "peak_no_fma": C.peak_nofma, "frac_no_fma": achieved / C.peak_nofma,
@@ -473,14 +473,17 @@ def measure_damping(C, with_cpu):
     return out
 
 
-def traffic_from_profiles(name, ki):
-    """DRAM bytes per launch of the trace kernel on this workload, from a committed ncu pass -- only if that pass
-    measured the kernel this library would launch now (same mode, block, registers, local bytes), else null."""
+def traffic_from_profiles(name, ki, accepted_per_launch):
+    """DRAM bytes per launch of the trace kernel on this workload (dram__bytes_read.sum + dram__bytes_write.sum of a
+    committed `ncu --set full` capture, profiles/traffic.json).  The captures run the workload's own launch set with
+    fewer steps per ray (ncu replays a launch ~40 times), so the figure is bytes per accepted step of the capture x the
+    accepted steps of this launch -- and only if the capture measured the kernel this library would launch now (same
+    mode, block, registers, local bytes); else null."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
         e = t.get(name)
         if e and all(e["kernel"].get(k) == ki.get(k) for k in ("mode", "block", "regs", "local_bytes")):
-            return e["dram_bytes_per_launch"]
+            return float(e["dram_bytes_per_accepted_step"]) * float(accepted_per_launch)
     except Exception:
         pass
     return None

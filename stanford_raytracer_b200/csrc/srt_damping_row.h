@@ -37,22 +37,9 @@ struct PsdState {  // psd_model after set_params
   double L_sh, L_pp, n_fit, An_fit;
 };
 
-DMP_HD inline double psd_suprathermal(double vperp, double vpar) {  // psd_model.cpp:259-278
-  const double a = 4.9e5, b = 8.3e14, c = 5.4e23, v0 = 1;
-  double v = 100. * sqrt(vperp * vperp + vpar * vpar + v0);
-  double f = (a / pow(v, 4.0) - b / pow(v, 5.0) + c / pow(v, 6.0));
-  return f * pow(100., 6.0);
-}
-DMP_HD inline double psd_crres(const PsdState& s, double vperp, double vpar) {  // :281-305
-  const double v0 = 1;
-  double v = 100. * sqrt(vperp * vperp + vpar * vpar + v0);
-  double f = s.An_fit / pow(v, s.n_fit);
-  return f * pow(100., 6.0);
-}
 #if defined(DMP_TEST_NOISE)
-// test hook (tests/csrc/damping_probe.cpp only): multiplies every density value by 1 +- amp, the sign a hash of the
-// arguments -- a stand-in for the last-place differences between two math libraries, to measure how well a row's
-// result is determined at all
+// test hook (tests/csrc/damping_probe.cpp only): a factor 1 +- amp, the sign a hash of the arguments -- a stand-in for
+// the last-place differences between two math libraries, to measure how well a row's result is determined at all
 extern double dmp_test_noise_amp;
 extern unsigned long long dmp_test_noise_seed;
 inline double dmp_noise(double a, double b) {
@@ -66,17 +53,34 @@ inline double dmp_noise(double a, double b) {
 #else
 #define DMP_NOISE(f, a, b) (f)
 #endif
+// the transcendentals of the density model: with the test hook, each result carries a last-place error of its own, which is
+// what separates two math libraries -- note that the suprathermal density a/v^4 - b/v^5 + c/v^6 cancels around
+// v = b/a = 1.7e7 m/s and the blended density is exp(mean of logs), so an error of one place in a pow or log is many
+// places of the density there
+#define DMP_POW(x, y) DMP_NOISE(pow((x), (y)), (x), (y))
+#define DMP_LOG(x) DMP_NOISE(log(x), (x), 1.0)
+#define DMP_EXP(x) DMP_NOISE(exp(x), (x), 2.0)
 
-DMP_HD inline double psd_hybrid_exact(const PsdState& s, double vperp, double vpar);
-DMP_HD inline double psd_hybrid(const PsdState& s, double vperp, double vpar) { return DMP_NOISE(psd_hybrid_exact(s, vperp, vpar), vperp, vpar); }
-DMP_HD inline double psd_hybrid_exact(const PsdState& s, double vperp, double vpar) {  // :308-341
+DMP_HD inline double psd_suprathermal(double vperp, double vpar) {  // psd_model.cpp:259-278
+  const double a = 4.9e5, b = 8.3e14, c = 5.4e23, v0 = 1;
+  double v = 100. * sqrt(vperp * vperp + vpar * vpar + v0);
+  double f = (a / DMP_POW(v, 4.0) - b / DMP_POW(v, 5.0) + c / DMP_POW(v, 6.0));
+  return f * pow(100., 6.0);
+}
+DMP_HD inline double psd_crres(const PsdState& s, double vperp, double vpar) {  // :281-305
+  const double v0 = 1;
+  double v = 100. * sqrt(vperp * vperp + vpar * vpar + v0);
+  double f = s.An_fit / DMP_POW(v, s.n_fit);
+  return f * pow(100., 6.0);
+}
+DMP_HD inline double psd_hybrid(const PsdState& s, double vperp, double vpar) {  // :308-341
   if (s.L_pp - s.L_sh > 1) return psd_suprathermal(vperp, vpar);
   if (s.L_sh - s.L_pp > 1) return psd_crres(s, vperp, vpar);
   double f_polar = psd_suprathermal(vperp, vpar);
   double f_crres = psd_crres(s, vperp, vpar);
   double w_polar = exp(5 * (s.L_pp - s.L_sh)) / (1 + exp(5 * (s.L_pp - s.L_sh)));
   double w_crres = exp(5 * (s.L_sh - s.L_pp)) / (1 + exp(5 * (s.L_sh - s.L_pp)));
-  return exp((log(f_polar) * w_polar + log(f_crres) * w_crres) / (w_polar + w_crres));
+  return DMP_EXP((DMP_LOG(f_polar) * w_polar + DMP_LOG(f_crres) * w_crres) / (w_polar + w_crres));
 }
 
 DMP_HD inline double bessel_jn(int n, double x) {

@@ -108,9 +108,11 @@ def host_damping(probe, path, AE_level, Kp, geom_factor, msec, yearday, perturb=
 def conditioning(probe, path, **opts):
     """Per row: how well the reference's own answer is determined.  The largest relative change of the power when (a) ONE
     fitted density parameter (power-law exponent, its amplitude, the plasmapause L) is moved by one unit in the last place,
-    (b) every phase-space-density value gets a +-1 ulp error (what separates two math libraries).  The integrand
-    differentiates the density with a relative step of 1e-8 (integrand.cpp:99-160), so this is ~1e-8 for benign rows and
-    reaches 1e-2 for rays that cross the plasmapause region far out (measured)."""
+    (b) every pow / log / exp of the density model gets a +-1 ulp error of its own (what separates two math libraries).
+    The integrand differentiates the density with a relative step of 1e-8 (integrand.cpp:99-160), the suprathermal
+    density a/v^4 - b/v^5 + c/v^6 cancels around v = 1.7e7 m/s, and the blended density is exp(mean of logs): the result
+    is determined to ~1e-8 for benign rows, ~1e-5 for rays whose resonant velocities sit in the cancellation, and up to
+    1e-2 for rays that cross the plasmapause region far out (measured)."""
     base = host_damping(probe, path, **opts)
     cond = np.zeros(len(base))
     eps = 2.220446049250313e-16
@@ -123,8 +125,8 @@ def conditioning(probe, path, **opts):
     return base, cond
 
 
-def assert_power_agrees(got, ref, cond, what, slack=100.0, floor=1e-6):
-    """|got / ref - 1| <= floor + slack * (1-ulp conditioning of the row) wherever the reference's power is above its own
+def assert_power_agrees(got, ref, cond, what, slack=20.0, floor=1e-6):
+    """|got / ref - 1| <= floor + slack * (1-ulp conditioning of the row; slack = 20: CUDA documents up to 2 ulp for pow) wherever the reference's power is above its own
     cut-off 1e-6 (WAVE_PWR_THRESH, consts.h); NaN rows agree."""
     assert np.array_equal(np.isfinite(got), np.isfinite(ref)), what
     big = np.isfinite(ref) & (ref > 1e-6)
