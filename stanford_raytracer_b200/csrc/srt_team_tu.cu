@@ -28,6 +28,8 @@ static team_kernel_t pick_team_t(const SrtModel& M) {
   if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_NGO, 1, MAXT> : srt_trace_team_kernel<SRT_DENS_NGO, 0, MAXT>;
   return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_GRID, 1, MAXT> : srt_trace_team_kernel<SRT_DENS_GRID, 0, MAXT>;
 }
+// (a third budget, 768 threads at 80 registers, measured 5-7 % slower than 1024 at 64 on the 40 000-ray, 100 000-ray and config-3
+// cases: profiles/r2h_damping_ab768_traffic.txt)
 static team_kernel_t pick_team(const SrtModel& M, int block) { return block > SRT_TEAM_MAXT_SMALL ? pick_team_t<1024>(M) : pick_team_t<SRT_TEAM_MAXT_SMALL>(M); }
 
 // block size for a batch: the largest power of two <= 1024 that still gives every SM at least one block
