@@ -59,7 +59,10 @@ def summarise(tot, kind):
     for k, label in enumerate(("accepted", "rejected")):
         nat = max(int(tot[k, -1]), 1)
         per = {nm: tot[k, i] / nat for i, nm in enumerate(NAMES)}
-        T = per["exp"] + per["pow"] + per["atan2"] + per["acos"] + per["csqrt"] + 1.5 * per["sincos"]
+        # one srt_sincos call stands for the reference's separate sin() and cos() of that angle: 2 calls where both values are
+        # used, 1 where only the cosine is (Ngo adapter: sin+cos of the polar angle, cos of the latitude, sin+cos in dens,
+        # sin+cos of the azimuth = 7 calls from 4; is_right_handed: 2 from 1)
+        T = per["exp"] + per["pow"] + per["atan2"] + per["acos"] + per["csqrt"] + (1.75 if kind == "ngo" else 2.0) * per["sincos"]
         flops = (per["plasma"] * UNIT_FLOPS["plasma_" + kind] + per["igrf"] * UNIT_FLOPS["igrf_fp32"] + per["derive"] * UNIT_FLOPS["derive"] +
                  per["stix"] * UNIT_FLOPS["stix"] + per["ftail"] * UNIT_FLOPS["ftail"] + per["root"] * UNIT_FLOPS["root"] + per["hand"] * UNIT_FLOPS["hand"] +
                  UNIT_FLOPS["attempt"])
