@@ -39,6 +39,7 @@ extern "C" {
 #define SRT_E_UNSUPPORTED -4 /* e.g. use_tsyganenko != 0 */
 #define SRT_E_CUDA -5       /* CUDA runtime error (srt_last_cuda_error()) */
 #define SRT_E_NOMEM -6      /* trajectory log cannot hold even one ray */
+#define SRT_E_TOOBIG -7     /* more points than the static scratch of srt_model_eval_noalloc holds */
 
 /* one recorded trajectory row: the non-constant columns that driver:1197-1217 writes */
 #define SRT_ROW_DOUBLES 20
@@ -83,6 +84,17 @@ int srt_model_species(const srt_model* m, int* nspec, double* qs, double* ms, do
 /* funcPlasmaParams at n points (host arrays): out[n][19] = qs4, Ns4, ms4, nus4, B0(3).
  * The parity surface of fortran/dumpmodel.f95:374-378,649-653. */
 int srt_model_eval(const srt_model* m, int64_t n, const double* x /*[n][3]*/, double* out /*[n][19]*/);
+/* srt_model_eval for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  Same arguments
+ * and results as srt_model_eval; calls no cudaMalloc / cudaFree / allocating routine: points and results are staged in
+ * a static device array of srt_model_eval_noalloc_max_points() = 16384 points (2.75 MiB, held by every GPU that loads
+ * the library until exit).  n beyond that returns SRT_E_TOOBIG (text in srt_last_cuda_error()).  A gridded model must
+ * already be on the device (any earlier ordinary call with it), else SRT_E_UNSUPPORTED.  All calls on a device share
+ * the array, which keeps the last call's contents; the call is synchronous and serialised per device inside this
+ * library, but calls from several PROCESSES do not share the array, and device work of this call overlapping other work
+ * that used the same array would race. */
+int srt_model_eval_noalloc(const srt_model* m, int64_t n, const double* x /*[n][3]*/, double* out /*[n][19]*/);
+int64_t srt_model_eval_noalloc_max_points(void);
 
 /* raytracer_run for nrays rays, host buffers.  pos0[nrays][3], dir0[nrays][3] (inout: an all-zero
  * direction is replaced by the field-aligned one, raytracer.f95:661-674), w0[nrays]. */

@@ -54,6 +54,9 @@ def lib():
     L.srt_model_free.restype = None
     L.srt_model_species.argtypes = [vp, C.POINTER(i), vp, vp, vp]
     L.srt_model_eval.argtypes = [vp, i64, vp, vp]
+    L.srt_model_eval_noalloc.argtypes = [vp, i64, vp, vp]
+    L.srt_model_eval_noalloc_max_points.restype = i64
+    L.srt_model_eval_noalloc_max_points.argtypes = []
     L.srt_trace_batch.argtypes = [vp, i64, vp, vp, vp, C.POINTER(RunParams), C.POINTER(vp)]
     L.srt_init_devices.argtypes = [vp, i]
     L.srt_set_rows_shm.argtypes = [C.c_char_p]

@@ -98,7 +98,15 @@ struct DevCtx {
   std::mutex batch_mutex;
   DevBuf rays, log, sorted, summary, counters, nlogged, offsets;
   PinBuf rays_h, summary_h, small_h;
+  // device address of g_eval_static on this device (srt_model_eval_noalloc); taken once, by cudaGetSymbolAddress
+  double* eval_static = nullptr;
 };
+
+// Scratch of srt_model_eval_noalloc: the staged points ([n][3]) and results ([n][19]) of one call, in static device
+// memory, so that the call allocates nothing.  Every device that loads the library holds these 2.75 MiB until exit.
+// In host code this name is a stand-in, not an address: the kernels get the pointer cudaGetSymbolAddress returns.
+#define SRT_EVAL_STATIC_MAX_POINTS 16384
+static __device__ __align__(256) double g_eval_static[(size_t)SRT_EVAL_STATIC_MAX_POINTS * 22];
 
 std::mutex g_dev_mutex;
 std::vector<std::unique_ptr<DevCtx>> g_ctx;  // every device ever used by this process
@@ -512,6 +520,7 @@ const char* srt_strerror(int code) {
     case SRT_E_UNSUPPORTED: return "unsupported option (use_tsyganenko must be 0)";
     case SRT_E_CUDA: return "CUDA runtime error";
     case SRT_E_NOMEM: return "trajectory log too small for a single ray";
+    case SRT_E_TOOBIG: return "more points than the static scratch of srt_model_eval_noalloc holds (16384)";
   }
   return "unknown error";
 }
@@ -630,6 +639,74 @@ int srt_model_eval(const srt_model* m, int64_t n, const double* x, double* out) 
   cudaFree(dx);
   cudaFree(dout);
   return rc;
+}
+
+int64_t srt_model_eval_noalloc_max_points(void) { return SRT_EVAL_STATIC_MAX_POINTS; }
+
+// srt_model_eval without any allocation: points and results are staged in g_eval_static (shared by every call on the
+// device; two calls that overlap on one GPU race, so the whole call runs under the device's batch mutex and is
+// synchronous).  Nothing in the array has to start at zero: the kernel writes all 19 words of each of the n points
+// before they are copied out, and words beyond n are never read.
+int srt_model_eval_noalloc(const srt_model* m, int64_t n, const double* x, double* out) {
+  if (!m || n < 0 || (n > 0 && (!x || !out))) return SRT_E_ARG;
+  if (n > SRT_EVAL_STATIC_MAX_POINTS) {
+    snprintf(g_cuda_err, sizeof g_cuda_err, "srt_model_eval_noalloc: %lld points exceed the static scratch of %d points; split the call or use srt_model_eval",
+             (long long)n, SRT_EVAL_STATIC_MAX_POINTS);
+    return SRT_E_TOOBIG;
+  }
+  DevCtx* c = nullptr;
+  int rc = current_ctx(&c);
+  if (rc) return rc;
+  if (n == 0) return SRT_OK;
+  srt_model* mm = const_cast<srt_model*>(m);
+  SrtModel Md = mm->M;
+  if (mm->M.density == SRT_DENS_GRID) {
+    // the grid arrays of a model are placed on a device by its first ordinary call there (ensure_replica allocates)
+    std::lock_guard<std::mutex> lk(mm->replica_mutex);
+    auto it = mm->replicas.find(c->dev);
+    if (it == mm->replicas.end()) {
+      snprintf(g_cuda_err, sizeof g_cuda_err, "srt_model_eval_noalloc: the gridded model is not yet on device %d; one srt_model_eval or trace call places it", c->dev);
+      return SRT_E_UNSUPPORTED;
+    }
+    Md.grid.nodes = it->second.d_nodes;
+    Md.grid.coef = it->second.d_coef;
+    Md.grid.xs = it->second.d_axes;
+    Md.grid.ys = it->second.d_axes + mm->M.grid.nx;
+    Md.grid.zs = it->second.d_axes + mm->M.grid.nx + mm->M.grid.ny;
+  }
+  std::lock_guard<std::mutex> bl(c->batch_mutex);
+  if (!c->eval_static) {  // once per device, with that device current (current_ctx)
+    double* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_eval_static);
+    if (e != cudaSuccess || !p) return cuda_fail(e, "cudaGetSymbolAddress(g_eval_static)");
+    c->eval_static = p;
+  }
+  double* dx = c->eval_static;
+  double* dout = c->eval_static + (size_t)SRT_EVAL_STATIC_MAX_POINTS * 3;
+  cudaStream_t st = nullptr;  // legacy default stream: copies and kernel are ordered
+  CK(cudaMemcpy(dx, x, n * 3 * sizeof(double), cudaMemcpyHostToDevice));
+  std::lock_guard<std::mutex> lk(c->sym_mutex);
+  if (c->resident[0] != mm->serial) {
+    // as symbol_prepare, without creating an event: the upload is synchronous and the kernel has finished (copy below)
+    // before the mutex is released, so nobody needs an event to wait for either
+    for (cudaEvent_t ev : c->readers[0]) {
+      CK(cudaStreamWaitEvent(st, ev, 0));
+      cudaEventDestroy(ev);
+    }
+    c->readers[0].clear();
+    CK(cudaMemcpyToSymbol(c_srt_model, &Md, sizeof(SrtModel), 0, cudaMemcpyHostToDevice));
+    c->resident[0] = mm->serial;
+  } else if ((rc = symbol_reader(c, 0, st))) {
+    return rc;
+  }
+  int blocks = (int)((n + 127) / 128);
+  if (blocks > c->num_sms * 8) blocks = c->num_sms * 8;
+  pick_eval(Md)<<<blocks, 128, 0, st>>>(n, dx, dout);
+  CK(cudaGetLastError());
+  g_launches++;
+  cudaError_t e = cudaMemcpy(out, dout, n * 19 * sizeof(double), cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) return cuda_fail(e, "srt_model_eval_noalloc");
+  return SRT_OK;
 }
 
 int srt_selftest_div(int64_t ngroups, uint64_t seed, uint64_t* mismatches) {
