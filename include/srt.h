@@ -78,6 +78,12 @@ const char* srt_last_cuda_error(void);
 int srt_model_ngo(srt_model** m, const char* ngo_configfile, int yearday, int milliseconds_day, int use_igrf, int use_tsyganenko);
 /* modelnum 3 -- interpsetup + interpStateData (driver:497-615; interp_dens_model_adapter.f95:16-39,52-134) */
 int srt_model_grid(srt_model** m, const char* interp_interpfile, int yearday, int milliseconds_day, int use_igrf, int use_tsyganenko);
+/* use_tsyganenko = 1 (fortran/ngo_dens_model_adapter.f95:157-166,183-187): the TS05 external field T04_s
+ * (tsyganenko/TS05_aka_TS04.for:5-116) is added to the base field.  parmod[10] = Pdyn, Dst, ByIMF, BzIMF, W1..W6, the
+ * driver's --tsyganenko_* options (fortran/raytracer_driver.f95:262-291).  Also switches the term on for a model that
+ * was set up with use_tsyganenko = 0.  The tilt argument is what the adapters pass (word 1 of Geopack's /GEOPACK1/).
+ * Batches of such a model run the thread-per-ray kernel. */
+int srt_model_tsyganenko(srt_model* m, const double* parmod /*[10]*/);
 void srt_model_free(srt_model* m);
 /* qs, ms, nus as the adapter returns them on every call (constant per model) */
 int srt_model_species(const srt_model* m, int* nspec, double* qs, double* ms, double* nus);

@@ -45,6 +45,15 @@ void* orc_model_grid(const char* gridfile, int yearday, int msec, int use_igrf, 
 }
 #endif
 
+// use_tsyganenko = 1: parmod = Pdyn, Dst, ByIMF, BzIMF, W1..W6; t04_s = address of ts05_ref_t04_s in oracle/_ref/libts05_ref*.so
+void orc_model_tsyganenko(void* mv, const double* parmod, void* t04_s) {
+  Model* m = (Model*)mv;
+  FieldBlock* f = (FieldBlock*)m->field_block_ptr();
+  for (int i = 0; i < 10; ++i) f->parmod[i] = (float)parmod[i];  // real(parmod)
+  f->t04_s = (void (*)(const float*, float, float, float, float, float*))t04_s;
+}
+double orc_model_psi(void* mv) { return ((FieldBlock*)((Model*)mv)->field_block_ptr())->psi; }
+
 void orc_model_free(void* m) { delete (Model*)m; }
 
 double orc_model_del(void* m) { return ((Model*)m)->del; }

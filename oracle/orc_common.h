@@ -100,6 +100,7 @@ struct Plasma {
 struct Model {
   virtual ~Model() {}
   virtual void plasma(const double x[3], Plasma& p) = 0;
+  virtual void* field_block_ptr() { return nullptr; }  // FieldBlock of the adapter (orc_models.h)
   double del;  // dF/dx step: delSP (1e-4) for modelnum 1, delDP (1e-6) for modelnum 3
   long n_plasma_calls = 0;
 };

@@ -197,6 +197,7 @@ struct GridModel : Model {
   // (nspec, nx, ny, nz), species fastest
   std::vector<double> f, dfdx, dfdy, dfdz, d2fdxdy, d2fdxdz, d2fdydz, d3fdxdydz;
   FieldBlock field;
+  void* field_block_ptr() override { return &field; }
   bool dense_matmul = false;
 
   int setup(const char* filename) {

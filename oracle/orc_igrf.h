@@ -292,6 +292,7 @@ inline bool orc_attach_igrf(FieldBlock& f, int yearday, int msec, int faithful_c
   c->sec = (msec - c->hour * (1000 * 60 * 60) - c->min * (1000 * 60)) / (1000);
   TSY_RECALC(*c, c->year, c->day, c->hour, c->min, c->sec);
   f.igrf_ctx = c;
+  f.psi = c->ST0;  // `PSI` of the adapters = word 1 of /GEOPACK1/ (Q25)
   f.igrf_gsm = orc_igrf_gsm_cb;
   f.recalc_each_call = faithful_cost ? orc_igrf_recalc_cb : nullptr;
   return true;

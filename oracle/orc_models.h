@@ -123,6 +123,12 @@ struct FieldBlock {
   void (*igrf_gsm)(void* ctx, float x, float y, float z, float& bx, float& by, float& bz) = nullptr;
   void* igrf_ctx = nullptr;
   void (*recalc_each_call)(void* ctx) = nullptr;  // faithful-cost mode: tsy_recalc on every call
+  // use_tsyganenko = 1 (adapter :183-187): T04_s is the reference's own source, translated at build time into
+  // oracle/_ref (f77_to_cpp.py); the tests hand its entry point in.  `psi` is what the adapter's `PSI` names: word 1 of
+  // COMMON /GEOPACK1/, which in the compiled Geopack-2008 holds ST0 (Q25).
+  void (*t04_s)(const float* parmod, float ps, float x, float y, float z, float* b) = nullptr;
+  float parmod[10] = {0};
+  float psi = 0.0f;
   void eval(const double x[3], double B0[3]) const {
     double x_gsm[3];
     tilt.sm_to_gsm(x, x_gsm);
@@ -139,6 +145,11 @@ struct FieldBlock {
       bz = (float)(1.0e9 * B0tmp2[2]);
     }
     float tx = 0.0f, ty = 0.0f, tz = 0.0f;  // use_tsyganenko = 0
+    if (t04_s) {
+      float b[3];
+      t04_s(parmod, psi, (float)(x_gsm[0] / R_E), (float)(x_gsm[1] / R_E), (float)(x_gsm[2] / R_E), b);
+      tx = b[0]; ty = b[1]; tz = b[2];
+    }
     double Bt[3];
     Bt[0] = (double)(bx + tx) * 1.0e-9;
     Bt[1] = (double)(by + ty) * 1.0e-9;
@@ -484,6 +495,7 @@ struct NgoState {
 struct NgoModel : Model {
   NgoState st;
   FieldBlock field;
+  void* field_block_ptr() override { return &field; }
   void plasma(const double x[3], Plasma& o) override {
     ++n_plasma_calls;
     o.nspec = 4;

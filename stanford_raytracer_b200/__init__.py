@@ -54,6 +54,7 @@ def lib():
     L.srt_model_free.restype = None
     L.srt_model_species.argtypes = [vp, C.POINTER(i), vp, vp, vp]
     L.srt_model_eval.argtypes = [vp, i64, vp, vp]
+    L.srt_model_tsyganenko.argtypes = [vp, vp]
     L.srt_model_eval_noalloc.argtypes = [vp, i64, vp, vp]
     L.srt_model_eval_noalloc_max_points.restype = i64
     L.srt_model_eval_noalloc_max_points.argtypes = []
@@ -157,6 +158,13 @@ class Model:
         out = np.empty((len(x), 19))
         _check(lib().srt_model_eval(self._h, len(x), _ptr(x), _ptr(out)), "srt_model_eval")
         return dict(qs=out[:, 0:4], Ns=out[:, 4:8], ms=out[:, 8:12], nus=out[:, 12:16], B0=out[:, 16:19], raw=out)
+
+    def tsyganenko(self, Pdyn, Dst, ByIMF, BzIMF, W=(0, 0, 0, 0, 0, 0)):
+        """use_tsyganenko = 1 with the driver's --tsyganenko_* parameters (TS05 external field, T04_s)."""
+        parmod = np.array([Pdyn, Dst, ByIMF, BzIMF] + list(W), dtype=np.float64)
+        assert parmod.shape == (10,)
+        _check(lib().srt_model_tsyganenko(self._h, _ptr(parmod)), "srt_model_tsyganenko")
+        return self
 
     def kernel_info(self, nrays):
         v = [C.c_int() for _ in range(6)]

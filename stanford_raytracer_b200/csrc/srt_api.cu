@@ -16,6 +16,8 @@
 #ifndef SRT_BLOCK_SYNC
 #define SRT_BLOCK_SYNC 1
 #endif
+// the TS05 external field is compiled into this unit only (thread-per-ray and evaluation kernels); the team unit stays without it
+#define SRT_WITH_TS05 1
 #include "srt_kernels.cuh"
 #include "srt_team_tu.h"
 #include "srt_host_setup.h"
@@ -260,6 +262,7 @@ namespace {
 // 0 = one thread per ray, 1 = team of 8 lanes per ray.  SRT_KERNEL=thread|team overrides.
 int pick_mode(const srt_model* m, long long nrays) {
   const char* env = getenv("SRT_KERNEL");
+  if (m->M.ts.on) return 0;  // use_tsyganenko = 1: the external field exists in the thread-per-ray kernels only
   if (env && !strcmp(env, "thread")) return 0;
   if (env && !strcmp(env, "team")) return 1;
   // Since the team form steps block-synchronously with 6 equal rounds per attempt it is the faster one at every
@@ -448,11 +451,15 @@ int launch_trace(DevCtx* c, srt_model* m, const SrtRunParams& P, const SrtBatch&
 }
 
 int finish_model(srt_model* mm, int yearday, int msec, int use_igrf, int use_tsyganenko) {
-  if (use_tsyganenko != 0) return SRT_E_UNSUPPORTED;
+  if (use_tsyganenko != 0 && use_tsyganenko != 1) return SRT_E_ARG;
   if (use_igrf != 0 && use_igrf != 1) return SRT_E_ARG;
   srt_host::set_time(mm->M, yearday, msec);
   mm->M.use_igrf = use_igrf;
-  srt_host::igrf_recalc(yearday, msec, mm->M.igrf);
+  // use_tsyganenko = 1: T04_s with the parameters of srt_model_tsyganenko() (all zero until then, like the
+  // reference's state before its --tsyganenko_* options are read) and the `PSI` the adapters pass (Q25)
+  memset(&mm->M.ts, 0, sizeof mm->M.ts);
+  mm->M.ts.on = use_tsyganenko;
+  srt_host::igrf_recalc(yearday, msec, mm->M.igrf, &mm->M.ts.ps);
   for (int i = 0; i < SRT_NSPEC; ++i) mm->nus[i] = 0.0;
   mm->serial = ++g_model_serial;
   return SRT_OK;
@@ -517,7 +524,7 @@ const char* srt_strerror(int code) {
     case SRT_E_NODEVICE: return "no usable CUDA device (libsrt has no CPU path)";
     case SRT_E_IO: return "cannot open or parse model file";
     case SRT_E_ARG: return "invalid argument";
-    case SRT_E_UNSUPPORTED: return "unsupported option (use_tsyganenko must be 0)";
+    case SRT_E_UNSUPPORTED: return "unsupported option or state";
     case SRT_E_CUDA: return "CUDA runtime error";
     case SRT_E_NOMEM: return "trajectory log too small for a single ray";
     case SRT_E_TOOBIG: return "more points than the static scratch of srt_model_eval_noalloc holds (16384)";
@@ -593,6 +600,14 @@ void srt_model_free(srt_model* m) {
   }
   if (!m->replicas.empty()) cudaSetDevice(prev);
   delete m;
+}
+
+int srt_model_tsyganenko(srt_model* m, const double* parmod) {
+  if (!m || !parmod) return SRT_E_ARG;
+  for (int i = 0; i < 10; ++i) m->M.ts.parmod[i] = (float)parmod[i];  // real(parmod), adapter :184
+  m->M.ts.on = 1;
+  m->serial = ++g_model_serial;  // the copies of the model on the devices are stale
+  return SRT_OK;
 }
 
 int srt_model_species(const srt_model* m, int* nspec, double* qs, double* ms, double* nus) {

@@ -95,7 +95,12 @@ void usage() {
        "   --yearday            year and day, e.g., 1999098\n"
        "   --milliseconds_day   milliseconds of day\n"
        "   --use_igrf           (1=use, 0=do not use)\n"
-       "   --use_tsyganenko     must be 0 (the external field is not on the GPU path)\n"
+       "   --use_tsyganenko     (1=use, 0=do not use)\n"
+       "   --tsyganenko_Pdyn    between 0.5 and 10 nPa\n"
+       "   --tsyganenko_Dst     between -100 and +20 in nT\n"
+       "   --tsyganenko_ByIMF   between -10 and +10 nT\n"
+       "   --tsyganenko_BzIMF   between -10 and +10 nT\n"
+       "   --tsyganenko_W1 .. --tsyganenko_W6   TS04_s W1 .. W6\n"
        "\n"
        " Not in the reference:\n"
        "   --device=N (default: all GPUs)  --threads=N  --batch=N  --verbose=1");
@@ -155,6 +160,13 @@ int main(int argc, char** argv) {
     rc = srt_model_grid(&model, modelfile.c_str(), yearday, msec, use_igrf, use_tsy);
   } else {
     die(3, "--modelnum=" + std::to_string(modelnum) + " is not available on the GPU path (1 = Ngo, 3 = gridded)");
+  }
+  if (!rc && use_tsy == 1) {  // the parameters the driver reads into the adapter's state (raytracer_driver.f95:291-340)
+    static const char* names[10] = {"tsyganenko_Pdyn", "tsyganenko_Dst", "tsyganenko_ByIMF", "tsyganenko_BzIMF", "tsyganenko_W1",
+                                    "tsyganenko_W2",   "tsyganenko_W3",  "tsyganenko_W4",    "tsyganenko_W5",    "tsyganenko_W6"};
+    double parmod[10];
+    for (int i = 0; i < 10; ++i) parmod[i] = opt_real(names[i], 0.0);
+    rc = srt_model_tsyganenko(model, parmod);
   }
   if (rc) die(1, std::string("model set-up (") + modelfile + "): " + srt_strerror(rc) + (rc == SRT_E_CUDA ? std::string(": ") + srt_last_cuda_error() : ""));
 

@@ -39,7 +39,7 @@ inline void sun_08(int iyear, int iday, int ihour, int min, int isec, float& gst
 }
 
 // RECALC_08 with VGSE = (-400, 0, 0) (TSY_RECALC).  g/h/rec are 1-based like the Fortran arrays.
-inline void recalc_08(int iyear, int iday, int ihour, int min, int isec, SrtIgrf& ig) {
+inline void recalc_08(int iyear, int iday, int ihour, int min, int isec, SrtIgrf& ig, float* st0_out = nullptr) {
   using namespace srt_igrf_tables;
   memset(&ig, 0, sizeof ig);
   float* G = ig.g;
@@ -105,6 +105,7 @@ inline void recalc_08(int iyear, int iday, int ihour, int min, int isec, SrtIgrf
   float sl0 = -h_11 / sqq;
   float cl0 = -g_11 / sqq;
   float st0 = sqq / sqr;
+  if (st0_out) *st0_out = st0;  // word 1 of COMMON /GEOPACK1/: what the adapters' `PSI` aliases (Q25)
   float ct0 = g_10 / sqr;
   float stcl = st0 * cl0;
   float stsl = st0 * sl0;
@@ -160,13 +161,13 @@ inline void recalc_08(int iyear, int iday, int ihour, int min, int isec, SrtIgrf
 
 // itime = (yyyyddd, milliseconds of day) -> the five integers the adapters pass to tsy_recalc
 // (ngo_dens_model_adapter.f95:149-153)
-inline void igrf_recalc(int yearday, int msec, SrtIgrf& ig) {
+inline void igrf_recalc(int yearday, int msec, SrtIgrf& ig, float* st0_out = nullptr) {
   int year = yearday / 1000;
   int day = yearday % 1000;
   int hour = msec / (1000 * 60 * 60);
   int min = (msec - hour * (1000 * 60 * 60)) / (1000 * 60);
   int sec = (msec - hour * (1000 * 60 * 60) - min * (1000 * 60)) / 1000;
-  recalc_08(year, day, hour, min, sec, ig);
+  recalc_08(year, day, hour, min, sec, ig, st0_out);
 }
 
 }  // namespace srt_host

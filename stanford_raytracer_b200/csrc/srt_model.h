@@ -66,6 +66,13 @@ struct SrtIgrf {
   float a11, a21, a31, a12, a22, a32, a13, a23, a33;
 };
 
+// TS05 external field (csrc/srt_ts05.h), use_tsyganenko = 1
+struct SrtTs05 {
+  int on;            // use_tsyganenko
+  float parmod[10];  // Pdyn, Dst, ByIMF, BzIMF, W1..W6 as `real(parmod)` (ngo_dens_model_adapter.f95:184)
+  float ps;          // the tilt argument `real(psi)` as the adapter passes it: word 1 of COMMON /GEOPACK1/ = ST0 (Q25)
+};
+
 struct SrtModel {
   int density;   // SrtDensityKind
   int use_igrf;  // 0: centred dipole, 1: IGRF
@@ -80,4 +87,5 @@ struct SrtModel {
   SrtNgo ngo;
   SrtGrid grid;
   SrtIgrf igrf;
+  SrtTs05 ts;
 };

@@ -21,6 +21,9 @@
 #pragma once
 #include "srt_math.h"
 #include "srt_model.h"
+#if defined(SRT_WITH_TS05)
+#include "srt_ts05.h"
+#endif
 
 // fortran/constants.f95:4-12
 #define SRT_EPS0 8.854187817e-12
@@ -257,10 +260,18 @@ SRT_HD void srt_field_sm(SrtModelRef MR, const double x[3], const double p[3], d
     by = (float)(1.0e9 * Bg[1]);
     bz = (float)(1.0e9 * Bg[2]);
   }
+  float tx = 0.0f, ty = 0.0f, tz = 0.0f;
+#if defined(SRT_WITH_TS05)
+  if (M.ts.on) {  // use_tsyganenko = 1: T04_s at the GSM position in R_E (adapter :183-187)
+    double xg[3];
+    srt_rot_y(M.cos_mu, -M.sin_mu, x, xg);
+    srt_ts05(M.ts, (float)(xg[0] / SRT_R_E), (float)(xg[1] / SRT_R_E), (float)(xg[2] / SRT_R_E), tx, ty, tz);
+  }
+#endif
   double Bt[3];
-  Bt[0] = (double)(bx + 0.0f) * 1.0e-9;
-  Bt[1] = (double)(by + 0.0f) * 1.0e-9;
-  Bt[2] = (double)(bz + 0.0f) * 1.0e-9;
+  Bt[0] = (double)(bx + tx) * 1.0e-9;
+  Bt[1] = (double)(by + ty) * 1.0e-9;
+  Bt[2] = (double)(bz + tz) * 1.0e-9;
   srt_rot_y(M.cos_mu, M.sin_mu, Bt, B0);  // GSM_TO_SM_d: rotate_y(+mu)
 }
 

@@ -13,13 +13,9 @@
 // the elliptic-integral polynomials, `DELTADY=4.7`, the exponents `**0.37`), x**3.D0 goes through pow().
 #pragma once
 #include "srt_math.h"
+#include "srt_model.h"
 #include "srt_ts05_tables.h"
 
-struct SrtTs05 {
-  int on;            // use_tsyganenko
-  float parmod[10];  // Pdyn, Dst, ByIMF, BzIMF, W1..W6 as `real(parmod)` (adapter :184)
-  float ps;          // the tilt argument `real(psi)` as the adapter passes it (Q25: word 1 of /GEOPACK1/)
-};
 
 SRT_HD double ts05_sq(double x) { return x * x; }
 SRT_HD double ts05_tan(double x) { double s, c; srt_sincos(x, s, c); return s / c; }

@@ -34,6 +34,10 @@ def build_hostemu():
     if _newer(out, srcs):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-fno-fast-math", "-DEMU_HAVE_GRID", "-Wno-attributes", "-shared", "-o", out,
                                os.path.join(ROOT, "tests", "csrc", "hostemu.cpp")])
+    out3 = os.path.join(BUILD, "ts05_probe.so")
+    src3 = os.path.join(ROOT, "tests", "csrc", "ts05_probe.cpp")
+    if _newer(out3, [src3] + [os.path.join(csrc, f) for f in ("srt_ts05.h", "srt_ts05_tables.h", "srt_math.h")]):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-fno-fast-math", "-Wno-attributes", "-I" + csrc, "-shared", "-o", out3, src3])
     out2 = os.path.join(BUILD, "math_probe.so")
     src2 = os.path.join(ROOT, "tests", "csrc", "math_probe.cpp")
     if _newer(out2, [src2, os.path.join(csrc, "srt_math.h")]):
@@ -80,6 +84,8 @@ class HostEmu:
         E.emu_model_grid.restype = vp
         E.emu_model_grid.argtypes = [C.c_char_p, i, i, i]
         E.emu_plasma.argtypes = [vp, l, vp, vp]
+        E.emu_model_tsyganenko.argtypes = [vp, vp, i, i]
+        self.yearday, self.msec = yearday, msec
         E.emu_is_right_handed.restype = i
         E.emu_is_right_handed.argtypes = [d] * 5
         E.emu_trace.restype = l
@@ -89,6 +95,11 @@ class HostEmu:
         self.h = fn(path.encode(), yearday, msec, use_igrf | (2 if (precomputed_coef and kind != "ngo") else 0))
         if not self.h:
             raise RuntimeError("hostemu model setup failed")
+
+    def tsyganenko(self, parmod):
+        pm = np.ascontiguousarray(parmod, dtype=np.float64)
+        self.E.emu_model_tsyganenko(self.h, pm.ctypes.data, self.yearday, self.msec)
+        return self
 
     def plasma(self, x):
         x = np.ascontiguousarray(x, dtype=np.float64).reshape(-1, 3)

@@ -3,6 +3,7 @@
 // GPU, that the de-duplicated evaluation order of the kernels reproduces the oracle's
 // faithful call structure bit for bit.  Not shipped, not a fallback: libsrt.so has no
 // CPU path.
+#define SRT_WITH_TS05 1
 #include "../../stanford_raytracer_b200/csrc/srt_physics.h"
 #include "../../stanford_raytracer_b200/csrc/srt_igrf.h"
 #include "../../stanford_raytracer_b200/csrc/srt_tricubic.h"
@@ -128,6 +129,16 @@ void* emu_model_grid(const char* path, int yearday, int msec, int use_igrf) {
   return M;  // hg leaks with the model: test-only
 }
 #endif
+// use_tsyganenko = 1 with the given parameters; the tilt argument as finish_model (csrc/srt_api.cu) sets it
+void emu_model_tsyganenko(void* m, const double* parmod, int yearday, int msec) {
+  SrtModel* M = (SrtModel*)m;
+  for (int i = 0; i < 10; ++i) M->ts.parmod[i] = (float)parmod[i];
+  M->ts.on = 1;
+#ifdef EMU_HAVE_GRID
+  SrtIgrf tmp;
+  srt_host::igrf_recalc(yearday, msec, tmp, &M->ts.ps);
+#endif
+}
 void emu_model_free(void* m) { delete (SrtModel*)m; }
 void emu_model_get(void* m, double* out /* ane0, cos_mu, sin_mu, del */) {
   SrtModel* M = (SrtModel*)m;

@@ -36,6 +36,9 @@ def lib(libm=False):
         L.orc_model_grid.restype = vp
         L.orc_model_grid.argtypes = [C.c_char_p, i, i, i, i]
     L.orc_model_free.argtypes = [vp]
+    L.orc_model_tsyganenko.argtypes = [vp, vp, vp]
+    L.orc_model_psi.restype = d
+    L.orc_model_psi.argtypes = [vp]
     L.orc_model_del.restype = d
     L.orc_model_del.argtypes = [vp]
     L.orc_plasma.argtypes = [vp, l, vp, vp]
@@ -66,6 +69,24 @@ def lib(libm=False):
     return L
 
 
+def ts05_ref(srt_math=True):
+    """oracle/_ref/libts05_ref*.so: the reference's TS05 source, translated at build time (oracle/f77_to_cpp.py).
+    srt_math: the build on the elementary functions of csrc/srt_math.h (bit-for-bit yardstick); else glibc's."""
+    name = "libts05_ref_srtmath.so" if srt_math else "libts05_ref.so"
+    if name not in _libs:
+        path = os.path.join(ORC_DIR, "_ref", name)
+        if not os.path.exists(path):
+            subprocess.check_call(["make", "-s", "-C", ORC_DIR, "ref"])
+        if not os.path.exists(path):
+            return None
+        R = C.CDLL(path)
+        d, f = C.c_double, C.c_float
+        R.ts05_ref_extern.argtypes = [C.c_void_p, d, d, d, d, C.c_void_p]
+        R.ts05_ref_t04_s.argtypes = [C.c_void_p, f, f, f, f, C.c_void_p]
+        _libs[name] = R
+    return _libs[name]
+
+
 def _p(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None else None
 
@@ -78,6 +99,14 @@ class OracleModel:
         if not self.h:
             raise RuntimeError("oracle model setup failed: %s" % path)
         self.del_ = self.L.orc_model_del(self.h)
+
+    def tsyganenko(self, parmod, srt_math=True):
+        """use_tsyganenko = 1: T04_s is the reference's own source as translated into oracle/_ref (ts05_ref())."""
+        R = ts05_ref(srt_math)
+        pm = np.ascontiguousarray(parmod, dtype=np.float64)
+        assert pm.shape == (10,)
+        self.L.orc_model_tsyganenko(self.h, _p(pm), C.cast(R.ts05_ref_t04_s, C.c_void_p))
+        return self
 
     def close(self):
         if self.h:

@@ -53,7 +53,7 @@ def test_argument_errors(built):
     with pytest.raises(srt.SrtError):
         srt.ngosetup("/nonexistent/newray.in")
     with pytest.raises(srt.SrtError):
-        srt.ngosetup(common.NGO_CFG, 2010001, 0, 0, 1)  # use_tsyganenko unsupported
+        srt.ngosetup(common.NGO_CFG, 2010001, 0, 0, 2)  # use_tsyganenko is 0 or 1
     L = srt.lib()
     assert L.srt_trace_batch(None, 1, None, None, None, None, None) == -3
     assert L.srt_result_nrays(None) == 0

@@ -1,0 +1,66 @@
+"""TS05 external field on the GPU (use_tsyganenko = 1), through the C ABI, against the CPU
+oracle whose T04_s is the reference's own source translated into oracle/_ref: BIT-EXACT (both sides on csrc/srt_math.h)."""
+import os
+
+import numpy as np
+import pytest
+
+import common
+import oracle_lib as ol
+from test_ts05_cpu import PARMOD, points
+
+pytestmark = pytest.mark.gpu
+GRID13 = os.path.join(common.ROOT, "tests", "golden", "grid13.txt")
+
+
+@pytest.fixture(scope="module")
+def srt(built):
+    import stanford_raytracer_b200 as s
+    s.init(0)
+    if ol.ts05_ref(True) is None:
+        pytest.skip("oracle/_ref/libts05_ref_srtmath.so not built")
+    return s
+
+
+@pytest.mark.parametrize("kind,use_igrf", [("ngo", 0), ("ngo", 1), ("grid", 1)])
+def test_plasma_parameters_with_the_external_field(srt, kind, use_igrf):
+    path = common.NGO_CFG if kind == "ngo" else GRID13
+    setup = srt.ngosetup if kind == "ngo" else srt.interpsetup
+    m = setup(path, 2010001, 3600000, use_igrf, 1).tsyganenko(*PARMOD[:4], W=PARMOD[4:])
+    o = ol.OracleModel(kind, path, 2010001, 3600000, use_igrf).tsyganenko(PARMOD)
+    off = setup(path, 2010001, 3600000, use_igrf, 0)
+    x = points(3000, 11)
+    a, b = m.funcPlasmaParams(x)["raw"], o.plasma(x)
+    assert np.array_equal(a.view(np.uint64), b.view(np.uint64))
+    c = off.funcPlasmaParams(x)["raw"]
+    assert not np.array_equal(a[:, 16:19], c[:, 16:19]) and np.array_equal(a[:, :16].view(np.uint64), c[:, :16].view(np.uint64))
+
+
+def test_switching_the_term_on_after_setup_and_parameter_change(srt):
+    """srt_model_tsyganenko on a model set up without the term, then with other parameters: the device copy follows"""
+    m = srt.ngosetup(common.NGO_CFG, 2010001, 0, 0, 0)
+    x = points(200, 12)
+    base = m.funcPlasmaParams(x)["raw"]
+    m.tsyganenko(*PARMOD[:4], W=PARMOD[4:])
+    o = ol.OracleModel("ngo", common.NGO_CFG).tsyganenko(PARMOD)
+    assert np.array_equal(m.funcPlasmaParams(x)["raw"].view(np.uint64), o.plasma(x).view(np.uint64))
+    other = [1.5, -5.0, 0.0, 3.0, 0, 0, 0, 0, 0, 0]
+    m.tsyganenko(*other[:4], W=other[4:])
+    o2 = ol.OracleModel("ngo", common.NGO_CFG).tsyganenko(other)
+    got = m.funcPlasmaParams(x)["raw"]
+    assert np.array_equal(got.view(np.uint64), o2.plasma(x).view(np.uint64)) and not np.array_equal(got, base)
+    assert m.kernel_info(1000)["mode"] == "thread"
+
+
+def test_rays_through_the_external_field(srt):
+    m = srt.ngosetup(common.NGO_CFG, 2010001, 0, 0, 1).tsyganenko(*PARMOD[:4], W=PARMOD[4:])
+    o = ol.OracleModel("ngo", common.NGO_CFG).tsyganenko(PARMOD)
+    pos0, dir0, w0 = common.c2_grid(4, 4)
+    params = dict(common.C2, maxsteps=400)
+    res = srt.raytracer_run(m, pos0, dir0, w0, **params)
+    for r in range(len(res)):
+        t = o.trace(pos0[r], [0, 0, 0], w0[r], **params)
+        rows = res[r].rows
+        assert rows.shape == t["rows"].shape and res.stopcond[r] == t["stopcond"], r
+        assert np.array_equal(rows.view(np.uint64), t["rows"].view(np.uint64)), r
+        assert res.nrejected[r] == t["nrejected"] + t["ncone"]
