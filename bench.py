@@ -473,6 +473,83 @@ def measure_damping(C, with_cpu):
     return out
 
 
+def measure_ts05(C, with_cpu):
+    """the C2 launch set with use_tsyganenko = 1 (TS05 external field added to the dipole), the first
+    300 steps of every ray -- a bounded sample: the external field is ~100 x the arithmetic of the rest of a plasma
+    evaluation.  Rank 0 only.  value = accepted ray-steps/s, rays resident on the device; e2e through raytracer_run with
+    host buffers.  CPU: the oracle's adapter with the REFERENCE'S OWN T04_s (tsyganenko/TS05_aka_TS04.for translated at build
+    time into oracle/_ref) on a strided sample of the same rays, all host cores; the same rays are compared bit for bit."""
+    if C.rank != 0:
+        return None
+    import torch
+    import common
+    srt = C.srt
+    parmod = [3.0, -45.0, 2.5, -4.0, 0.4, 0.7, 0.3, 0.9, 0.6, 1.1]
+    pos0, dir0, w0, params, cfg = lattice("c2", 1)
+    params = dict(params, maxsteps=300)
+    n = len(w0)
+    model = srt.ngosetup(cfg, 2010001, 0, 0, 1).tsyganenko(*parmod[:4], W=parmod[4:])
+    P = srt.RunParams(params["dt0"], params["dtmax"], params["maxerr"], params["minalt"], params["tmax"], params["maxsteps"], params["root"], params["fixedstep"], 1)
+    rays0 = torch.from_numpy(np.ascontiguousarray(np.concatenate([pos0.T, dir0.T, w0[None, :]], axis=0))).cuda()
+    summary = torch.zeros((n, 24), dtype=torch.float64, device="cuda")
+    counters = torch.zeros(8, dtype=torch.int64, device="cuda")
+    l0 = srt.lib().srt_launch_count()
+    times = []
+    for rep in range(3):  # 1 warm + 2 timed
+        rays = rays0.clone()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        srt.trace_batch_device(model, n, rays.data_ptr(), P, 0, 0, summary.data_ptr(), counters.data_ptr(), 0)
+        e1.record()
+        torch.cuda.synchronize()
+        times.append(e0.elapsed_time(e1) * 1e-3)
+    c = counters.cpu().numpy()
+    sec = float(np.mean(times[1:]))
+    out = {"metric": METRIC, "unit": UNIT, "value": float(c[1]) / sec, "ms_per_step": sec * 1e3, "steps": 2, "warmup": 1,
+           "accepted_steps_per_sweep": int(c[1]), "attempts_per_sweep": int(c[2]), "gpu_launches": int(srt.lib().srt_launch_count() - l0),
+           "config": {"workload": "C2 launch set (10k rays), use_tsyganenko = 1: TS05 external field (Pdyn 3 nPa, Dst -45 nT, By 2.5, Bz -4 nT, W1-6 0.3-1.1) on the dipole, "
+                                  "first 300 steps of every ray", "rays": n, "maxsteps": 300},
+           "kernel": model.kernel_info(n),
+           "work": "per plasma evaluation one T04_s call: ~1e5 flop-equivalents (timed: 43 us on one host core), against ~7e2 for Ngo density + dipole"}
+    t0 = time.perf_counter()
+    res = srt.raytracer_run(model, pos0, dir0, w0, **params)
+    dt = time.perf_counter() - t0
+    out["e2e"] = {"value": res.accepted_steps / dt, "unit": UNIT, "h2d_bytes_per_step": int(n * 56), "d2h_bytes_per_step": int(res.total_rows * 160 + n * 192)}
+    if with_cpu:
+        import oracle_lib as ol
+        if ol.ts05_ref(True) is None:
+            out["cpu_baseline"] = {"unavailable": "oracle/_ref/libts05_ref_srtmath.so not built"}
+            return out
+        threads = os.cpu_count() or 1
+        idx = np.unique(np.linspace(0, n - 1, max(threads, 16)).astype(int))
+        models = [ol.OracleModel("ngo", cfg).tsyganenko(parmod) for _ in range(min(threads, len(idx)))]
+        last, nrows, lock, head = np.zeros((len(idx), 20)), np.zeros(len(idx), dtype=np.int64), threading.Lock(), [0]
+
+        def work(t):
+            while True:
+                with lock:
+                    j = head[0]
+                    head[0] += 1
+                if j >= len(idx):
+                    return
+                r = int(idx[j])
+                sm = models[t].trace_summary(pos0[r], dir0[r], w0[r], **params)
+                last[j], nrows[j] = sm["last_row"], sm["nrows"]
+
+        t0 = time.perf_counter()
+        ts = [threading.Thread(target=work, args=(i,)) for i in range(len(models))]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        dt = time.perf_counter() - t0
+        g = summary.cpu().numpy()[idx]
+        bad = sum(0 if (np.array_equal(g[j, :20], last[j], equal_nan=True) and int(g[j, 20]) == int(nrows[j])) else 1 for j in range(len(idx)))
+        out["cpu_baseline"] = {"value": float((nrows - 1).sum()) / dt, "unit": UNIT, "cores": len(models), "kind": "port + reference",
+                               "sample": "%d rays strided out of the 10k, first 300 steps, %.1f s: the oracle's adapter and integrator (faithful call structure) around the "
+                                         "reference's own T04_s as translated into oracle/_ref" % (len(idx), dt)}
+        out["parity_checked_rays"], out["parity_mismatches"] = len(idx), int(bad)
+    return out
+
+
 def traffic_from_profiles(name, ki, accepted_per_launch):
     """DRAM bytes per launch of the trace kernel on this workload (dram__bytes_read.sum + dram__bytes_write.sum of a
     committed `ncu --set full` capture, profiles/traffic.json).  The captures run the workload's own launch set with
@@ -498,7 +575,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="c2 is the bench line; the others run as `extra`")
-    ap.add_argument("--extras", default="auto", help="auto (c3, c4_100k, and c4 at 8 GPUs), none, or a comma list of workloads")
+    ap.add_argument("--extras", default="auto", help="auto (c3, c4_100k, c5, ts05, and c4 at 8 GPUs), none, or a comma list of workloads")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -557,6 +634,13 @@ def main():
             o = measure_damping(C, with_cpu)
             if C.rank == 0:
                 extras["c5"] = o
+        if args.extras == "auto" or "ts05" in names:
+            try:
+                o = measure_ts05(C, with_cpu)
+            except Exception as e:  # an extra must not take the line down
+                o = {"error": repr(e)}
+            if C.rank == 0:
+                extras["ts05"] = o
     if C.rank == 0:
         m = main_out
         line = {"metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": C.world, "steps": args.steps, "warmup": args.warmup,

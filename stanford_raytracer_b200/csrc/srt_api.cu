@@ -16,8 +16,6 @@
 #ifndef SRT_BLOCK_SYNC
 #define SRT_BLOCK_SYNC 1
 #endif
-// the TS05 external field is compiled into this unit only (thread-per-ray and evaluation kernels); the team unit stays without it
-#define SRT_WITH_TS05 1
 #include "srt_kernels.cuh"
 #include "srt_team_tu.h"
 #include "srt_host_setup.h"
@@ -160,13 +158,18 @@ int active_devices(std::vector<DevCtx*>& out) {
 typedef void (*trace_kernel_t)(const SrtRunParams, const SrtBatch);
 typedef void (*eval_kernel_t)(long long, const double*, double*);
 
+// kernels are instantiated per density kind and field code (bit 0 IGRF, bit 1 TS05 external field)
 trace_kernel_t pick_trace(const SrtModel& M) {
-  if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_trace_kernel<SRT_DENS_NGO, 1> : srt_trace_kernel<SRT_DENS_NGO, 0>;
-  return M.use_igrf ? srt_trace_kernel<SRT_DENS_GRID, 1> : srt_trace_kernel<SRT_DENS_GRID, 0>;
+  static const trace_kernel_t k[2][4] = {
+      {srt_trace_kernel<SRT_DENS_NGO, 0>, srt_trace_kernel<SRT_DENS_NGO, 1>, srt_trace_kernel<SRT_DENS_NGO, 2>, srt_trace_kernel<SRT_DENS_NGO, 3>},
+      {srt_trace_kernel<SRT_DENS_GRID, 0>, srt_trace_kernel<SRT_DENS_GRID, 1>, srt_trace_kernel<SRT_DENS_GRID, 2>, srt_trace_kernel<SRT_DENS_GRID, 3>}};
+  return k[M.density == SRT_DENS_NGO ? 0 : 1][(M.use_igrf ? 1 : 0) | (M.ts.on ? 2 : 0)];
 }
 eval_kernel_t pick_eval(const SrtModel& M) {
-  if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_eval_kernel<SRT_DENS_NGO, 1> : srt_eval_kernel<SRT_DENS_NGO, 0>;
-  return M.use_igrf ? srt_eval_kernel<SRT_DENS_GRID, 1> : srt_eval_kernel<SRT_DENS_GRID, 0>;
+  static const eval_kernel_t k[2][4] = {
+      {srt_eval_kernel<SRT_DENS_NGO, 0>, srt_eval_kernel<SRT_DENS_NGO, 1>, srt_eval_kernel<SRT_DENS_NGO, 2>, srt_eval_kernel<SRT_DENS_NGO, 3>},
+      {srt_eval_kernel<SRT_DENS_GRID, 0>, srt_eval_kernel<SRT_DENS_GRID, 1>, srt_eval_kernel<SRT_DENS_GRID, 2>, srt_eval_kernel<SRT_DENS_GRID, 3>}};
+  return k[M.density == SRT_DENS_NGO ? 0 : 1][(M.use_igrf ? 1 : 0) | (M.ts.on ? 2 : 0)];
 }
 
 // ---- set-up kernel of the gridded model: tricubic_compute_finite_difference_derivatives (libtricubic.f95:722-793).
@@ -262,7 +265,6 @@ namespace {
 // 0 = one thread per ray, 1 = team of 8 lanes per ray.  SRT_KERNEL=thread|team overrides.
 int pick_mode(const srt_model* m, long long nrays) {
   const char* env = getenv("SRT_KERNEL");
-  if (m->M.ts.on) return 0;  // use_tsyganenko = 1: the external field exists in the thread-per-ray kernels only
   if (env && !strcmp(env, "thread")) return 0;
   if (env && !strcmp(env, "team")) return 1;
   // Since the team form steps block-synchronously with 6 equal rounds per attempt it is the faster one at every
@@ -278,6 +280,7 @@ int launch_config(DevCtx* c, srt_model* m, long long nrays, int* mode_out, int* 
   int block = SRT_BLOCK_THREADS, nb = 1;
   if (mode) {
     block = srt_team_block_threads(nrays, c->num_sms);
+    if (m->M.ts.on && block > 512) block = 512;  // the kernels with the external field exist in the 128-register budget only
     CK(srt_team_occupancy(m->M, block, &nb));
   } else {
     std::lock_guard<std::mutex> lk(m->replica_mutex);

@@ -21,9 +21,7 @@
 #pragma once
 #include "srt_math.h"
 #include "srt_model.h"
-#if defined(SRT_WITH_TS05)
 #include "srt_ts05.h"
-#endif
 
 // fortran/constants.f95:4-12
 #define SRT_EPS0 8.854187817e-12
@@ -248,7 +246,7 @@ SRT_HD void srt_field_sm(SrtModelRef MR, const double x[3], const double p[3], d
                          double B0[3]) {
   const SrtModel& M = MR.get();
   float bx, by, bz;
-  if (USE_IGRF) {
+  if (USE_IGRF & 1) {
     double xg[3];
     srt_rot_y(M.cos_mu, -M.sin_mu, x, xg);  // SM_TO_GSM_d: rotate_y(-mu)
     srt_igrf_gsw(M.igrf, (float)(xg[0] / SRT_R_E), (float)(xg[1] / SRT_R_E), (float)(xg[2] / SRT_R_E), bx, by, bz);
@@ -261,13 +259,11 @@ SRT_HD void srt_field_sm(SrtModelRef MR, const double x[3], const double p[3], d
     bz = (float)(1.0e9 * Bg[2]);
   }
   float tx = 0.0f, ty = 0.0f, tz = 0.0f;
-#if defined(SRT_WITH_TS05)
-  if (M.ts.on) {  // use_tsyganenko = 1: T04_s at the GSM position in R_E (adapter :183-187)
+  if (USE_IGRF & 2) {  // use_tsyganenko = 1: T04_s at the GSM position in R_E (adapter :183-187)
     double xg[3];
     srt_rot_y(M.cos_mu, -M.sin_mu, x, xg);
     srt_ts05(M.ts, (float)(xg[0] / SRT_R_E), (float)(xg[1] / SRT_R_E), (float)(xg[2] / SRT_R_E), tx, ty, tz);
   }
-#endif
   double Bt[3];
   Bt[0] = (double)(bx + tx) * 1.0e-9;
   Bt[1] = (double)(by + ty) * 1.0e-9;
@@ -279,7 +275,7 @@ SRT_HD void srt_field_sm(SrtModelRef MR, const double x[3], const double p[3], d
 SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT_NSPEC]);
 
 // ------------------------------------------------------------------ funcPlasmaParams
-// DENS = SrtDensityKind, USE_IGRF = 0/1.
+// DENS = SrtDensityKind, USE_IGRF = the field code: bit 0 IGRF instead of the dipole, bit 1 TS05 external field added.
 //   Ngo:  fortran/ngo_dens_model_adapter.f95:63-207
 //   grid: fortran/interp_dens_model_adapter.f95:148-269
 template <int DENS, int USE_IGRF>
@@ -288,7 +284,7 @@ SRT_HDP void srt_plasma(SrtModelRef MR, const double x[3], SrtPlasma& o) {
   const SrtModel& M = MR.get();
   double p[3] = {0.0, 0.0, 0.0};
   double sph = 0.0, cph = 0.0, sth = 0.0, cth = 0.0;
-  if (DENS == SRT_DENS_NGO || !USE_IGRF) {
+  if (DENS == SRT_DENS_NGO || !(USE_IGRF & 1)) {
     srt_cart_to_sph(x, p);
     srt_sincos(p[2], sph, cph);
   }
@@ -310,7 +306,7 @@ SRT_HDP void srt_plasma(SrtModelRef MR, const double x[3], SrtPlasma& o) {
   } else {
     srt_grid_density(M.grid, x, o.Ns);
   }
-  if (!USE_IGRF) srt_sincos(p[1], sth, cth);
+  if (!(USE_IGRF & 1)) srt_sincos(p[1], sth, cth);
   srt_field_sm<USE_IGRF>(MR, x, p, sph, cph, sth, cth, o.B0);
 }
 

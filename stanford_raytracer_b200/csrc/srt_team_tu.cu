@@ -30,7 +30,16 @@ static team_kernel_t pick_team_t(const SrtModel& M) {
 }
 // (a third budget, 768 threads at 80 registers, measured 5-7 % slower than 1024 at 64 on the 40 000-ray, 100 000-ray and config-3
 // cases: profiles/r2h_damping_ab768_traffic.txt)
-static team_kernel_t pick_team(const SrtModel& M, int block) { return block > SRT_TEAM_MAXT_SMALL ? pick_team_t<1024>(M) : pick_team_t<SRT_TEAM_MAXT_SMALL>(M); }
+// use_tsyganenko = 1 (field code bit 1): the TS05 external field is ~100 x the work of the rest of a plasma evaluation and wants
+// registers, so these kernels exist in the 128-register budget only (launch_config keeps their blocks at <= 512 threads)
+static team_kernel_t pick_team_ts(const SrtModel& M) {
+  if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_NGO, 3, SRT_TEAM_MAXT_SMALL> : srt_trace_team_kernel<SRT_DENS_NGO, 2, SRT_TEAM_MAXT_SMALL>;
+  return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_GRID, 3, SRT_TEAM_MAXT_SMALL> : srt_trace_team_kernel<SRT_DENS_GRID, 2, SRT_TEAM_MAXT_SMALL>;
+}
+static team_kernel_t pick_team(const SrtModel& M, int block) {
+  if (M.ts.on) return pick_team_ts(M);
+  return block > SRT_TEAM_MAXT_SMALL ? pick_team_t<1024>(M) : pick_team_t<SRT_TEAM_MAXT_SMALL>(M);
+}
 
 // block size for a batch: the largest power of two <= 1024 that still gives every SM at least one block
 int srt_team_block_threads(long long nrays, int num_sms) {

@@ -3,7 +3,6 @@
 // GPU, that the de-duplicated evaluation order of the kernels reproduces the oracle's
 // faithful call structure bit for bit.  Not shipped, not a fallback: libsrt.so has no
 // CPU path.
-#define SRT_WITH_TS05 1
 #include "../../stanford_raytracer_b200/csrc/srt_physics.h"
 #include "../../stanford_raytracer_b200/csrc/srt_igrf.h"
 #include "../../stanford_raytracer_b200/csrc/srt_tricubic.h"
@@ -89,6 +88,20 @@ static void plasma_n(const SrtModel& M, long n, const double* x, double* out) {
     for (int c = 0; c < 3; ++c) o[16 + c] = p.B0[c];
   }
 }
+// model -> template arguments <D, I>: D = density kind, I = field code (bit 0 IGRF, bit 1 TS05 external field)
+#define EMU_DISPATCH(M, CALL)                                                                      \
+  do {                                                                                             \
+    const int f_ = ((M).use_igrf ? 1 : 0) | ((M).ts.on ? 2 : 0);                                   \
+    if ((M).density == SRT_DENS_NGO) {                                                             \
+      constexpr int D = 0;                                                                         \
+      if (f_ == 0) { constexpr int I = 0; CALL; } else if (f_ == 1) { constexpr int I = 1; CALL; } \
+      else if (f_ == 2) { constexpr int I = 2; CALL; } else { constexpr int I = 3; CALL; }         \
+    } else {                                                                                       \
+      constexpr int D = 1;                                                                         \
+      if (f_ == 0) { constexpr int I = 0; CALL; } else if (f_ == 1) { constexpr int I = 1; CALL; } \
+      else if (f_ == 2) { constexpr int I = 2; CALL; } else { constexpr int I = 3; CALL; }         \
+    }                                                                                              \
+  } while (0)
 extern "C" {
 void* emu_model_ngo(const char* cfg, int yearday, int msec, int use_igrf) {
   SrtModel* M = new SrtModel();
@@ -147,8 +160,7 @@ void emu_model_get(void* m, double* out /* ane0, cos_mu, sin_mu, del */) {
 
 void emu_plasma(void* m, long n, const double* x, double* out) {
   const SrtModel& M = *(SrtModel*)m;
-  if (M.density == SRT_DENS_NGO) { if (M.use_igrf) plasma_n<0, 1>(M, n, x, out); else plasma_n<0, 0>(M, n, x, out); }
-  else { if (M.use_igrf) plasma_n<1, 1>(M, n, x, out); else plasma_n<1, 0>(M, n, x, out); }
+  EMU_DISPATCH(M, (plasma_n<D, I>(M, n, x, out)));
 }
 int emu_is_right_handed(double n2, double phi, double S, double D, double P) { return srt_is_right_handed(n2, phi, S, D, P) ? 1 : 0; }
 
@@ -164,8 +176,7 @@ void emu_trace_tally(void* m, const double* pos0, double* dir0, double w0, doubl
   SrtRunParams P = {dt0, dtmax, maxerr, minalt, tmax, maxsteps, root, fixedstep, 1};
   memset(g_tally_sum, 0, sizeof g_tally_sum);
   g_tally_n[0] = g_tally_n[1] = 0;
-  if (M.density == SRT_DENS_NGO) { if (M.use_igrf) run_tally<0, 1>(M, P, pos0, dir0, w0); else run_tally<0, 0>(M, P, pos0, dir0, w0); }
-  else { if (M.use_igrf) run_tally<1, 1>(M, P, pos0, dir0, w0); else run_tally<1, 0>(M, P, pos0, dir0, w0); }
+  EMU_DISPATCH(M, (run_tally<D, I>(M, P, pos0, dir0, w0)));
   for (int k = 0; k < 2; ++k) {
     for (int i = 0; i < SRT_T_COUNT; ++i) out[k * (SRT_T_COUNT + 1) + i] = g_tally_sum[k][i];
     out[k * (SRT_T_COUNT + 1) + SRT_T_COUNT] = g_tally_n[k];
@@ -178,23 +189,15 @@ long emu_trace_summary(void* m, const double* pos0, double* dir0, double w0, dou
                        int root, double tmax, int fixedstep, double* last_row, int* stopcond, long* nrej) {
   const SrtModel& M = *(SrtModel*)m;
   SrtRunParams P = {dt0, dtmax, maxerr, minalt, tmax, maxsteps, root, fixedstep, 1};
-  if (M.density == SRT_DENS_NGO) {
-    if (M.use_igrf) return run_summary<0, 1>(M, P, pos0, dir0, w0, last_row, stopcond, nrej);
-    return run_summary<0, 0>(M, P, pos0, dir0, w0, last_row, stopcond, nrej);
-  }
-  if (M.use_igrf) return run_summary<1, 1>(M, P, pos0, dir0, w0, last_row, stopcond, nrej);
-  return run_summary<1, 0>(M, P, pos0, dir0, w0, last_row, stopcond, nrej);
+  EMU_DISPATCH(M, return (run_summary<D, I>(M, P, pos0, dir0, w0, last_row, stopcond, nrej)));
+  return -1;
 }
 
 long emu_trace(void* m, const double* pos0, double* dir0, double w0, double dt0, double dtmax, double maxerr, int maxsteps, double minalt,
                int root, double tmax, int fixedstep, double* rows, long max_rows, int* stopcond, long* nrej, long* ncone, int* cone_exit) {
   const SrtModel& M = *(SrtModel*)m;
   SrtRunParams P = {dt0, dtmax, maxerr, minalt, tmax, maxsteps, root, fixedstep, 1};
-  if (M.density == SRT_DENS_NGO) {
-    if (M.use_igrf) return run_one<0, 1>(M, P, pos0, dir0, w0, rows, max_rows, stopcond, nrej, ncone, cone_exit);
-    return run_one<0, 0>(M, P, pos0, dir0, w0, rows, max_rows, stopcond, nrej, ncone, cone_exit);
-  }
-  if (M.use_igrf) return run_one<1, 1>(M, P, pos0, dir0, w0, rows, max_rows, stopcond, nrej, ncone, cone_exit);
-  return run_one<1, 0>(M, P, pos0, dir0, w0, rows, max_rows, stopcond, nrej, ncone, cone_exit);
+  EMU_DISPATCH(M, return (run_one<D, I>(M, P, pos0, dir0, w0, rows, max_rows, stopcond, nrej, ncone, cone_exit)));
+  return -1;
 }
 }
