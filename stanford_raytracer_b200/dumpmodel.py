@@ -109,7 +109,10 @@ def main(argv=None):
     ap.add_argument("--interp_interpfile", default="")
     for k in ("yearday", "milliseconds_day", "use_tsyganenko", "use_igrf"):
         ap.add_argument("--" + k, type=int, default=0)  # unset options are 0 in the reference build (-finit-local-zero)
-    a, _ = ap.parse_known_args(argv)  # the Tsyganenko/GCPM options are accepted and unused (out of scope)
+    TSY = ("Pdyn", "Dst", "ByIMF", "BzIMF", "W1", "W2", "W3", "W4", "W5", "W6")
+    for k in TSY:
+        ap.add_argument("--tsyganenko_" + k, type=float, default=0.0)
+    a, _ = ap.parse_known_args(argv)  # the GCPM options are accepted and unused (out of scope)
     if min(a.nx, a.ny, a.nz) < 1 or not a.filename:
         ap.error("--nx --ny --nz (>= 1) and --filename are required")
     import stanford_raytracer_b200 as srt
@@ -121,6 +124,9 @@ def main(argv=None):
     else:
         print("dumpmodel: modelnum %d is not supported (1 = Ngo, 3 = gridded interpolation)" % a.modelnum, file=sys.stderr)
         return 2
+    if a.use_tsyganenko == 1:
+        pm = [getattr(a, "tsyganenko_" + k) for k in TSY]
+        model.tsyganenko(*pm[:4], W=pm[4:])
     extent = (a.minx, a.maxx, a.miny, a.maxy, a.minz, a.maxz)
     write_dump(a.filename, dump(model, a.nx, a.ny, a.nz, extent), extent)
     return 0

@@ -66,3 +66,24 @@ def test_rays_through_the_external_field(srt, mode, monkeypatch):
         assert rows.shape == t["rows"].shape and res.stopcond[r] == t["stopcond"], r
         assert np.array_equal(rows.view(np.uint64), t["rows"].view(np.uint64)), r
         assert res.nrejected[r] == t["nrejected"] + t["ncone"]
+
+
+def test_command_line_with_the_drivers_tsyganenko_options(srt, tmp_path):
+    """raytracer --use_tsyganenko=1 --tsyganenko_Pdyn=... (raytracer_driver.f95:262-340): output file byte-identical to the oracle's rows"""
+    import subprocess
+    import test_gpu_cli as cli
+    om = ol.OracleModel("ngo", common.NGO_CFG).tsyganenko(PARMOD)
+    m = srt.ngosetup(common.NGO_CFG, 2010001, 0, 0, 0)
+    pos0, dir0, w0 = common.launch_grid([800.0, 5000.0], [25.0, 50.0])
+    rays, outp = tmp_path / "rays.txt", tmp_path / "out.ray"
+    cli._write_rays(rays, pos0, dir0, w0)
+    params = dict(common.C2, maxsteps=120)
+    names = ("Pdyn", "Dst", "ByIMF", "BzIMF", "W1", "W2", "W3", "W4", "W5", "W6")
+    args = [cli.EXE, "--dt0=%r" % params["dt0"], "--dtmax=%r" % params["dtmax"], "--tmax=%r" % params["tmax"], "--root=%d" % params["root"],
+            "--fixedstep=%d" % params["fixedstep"], "--maxerr=%r" % params["maxerr"], "--maxsteps=%d" % params["maxsteps"],
+            "--minalt=%r" % params["minalt"], "--inputraysfile=%s" % rays, "--outputfile=%s" % outp, "--yearday=2010001", "--milliseconds_day=0",
+            "--modelnum=1", "--ngo_configfile=%s" % common.NGO_CFG, "--use_igrf=0", "--use_tsyganenko=1"] + ["--tsyganenko_%s=%r" % (k, v) for k, v in zip(names, PARMOD)]
+    r = subprocess.run(args, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    want = cli._oracle_text(om, pos0, w0, params, 1, m.qs, m.ms, m.nus)
+    assert open(outp, "rb").read() == want
