@@ -19,7 +19,8 @@ import sys
 
 LOGOPS = {".LT.": "<", ".GT.": ">", ".LE.": "<=", ".GE.": ">=", ".EQ.": "==", ".NE.": "!=", ".AND.": "&&", ".OR.": "||", ".NOT.": "!"}
 INTRINSICS = {"DSIN": "M_sin", "DCOS": "M_cos", "DSQRT": "M_sqrt", "SQRT": "M_sqrt", "DEXP": "M_exp", "DLOG": "M_log", "DATAN2": "M_atan2",
-              "DABS": "M_abs", "DTAN": "M_tan", "TAN": "M_tan", "SIN": "M_sin", "COS": "M_cos", "EXP": "M_exp", "ABS": "M_abs", "ATAN2": "M_atan2"}
+              "DABS": "M_abs", "DTAN": "M_tan", "TAN": "M_tan", "SIN": "M_sin", "COS": "M_cos", "EXP": "M_exp", "ABS": "M_abs", "ATAN2": "M_atan2",
+              "ATAN": "M_atan", "ASIN": "M_asin", "FLOAT": "M_float", "DFLOAT": "M_dfloat", "DMOD": "M_mod", "AMOD": "M_mod"}
 
 
 def read_statements(path):
@@ -352,7 +353,14 @@ def parse_units(stmts):
                 declare(cur, None, s[9:]); continue
             if s.startswith("COMMON/"):
                 m = re.fullmatch(r"COMMON/([A-Z0-9_]+)/(.+)", s)
-                cur.commons.append((m.group(1), m.group(2).split(",")))
+                items = split_top(m.group(2))
+                declare(cur, None, m.group(2))
+                cur.commons.append((m.group(1), [it.split("(")[0] for it in items]))
+                continue
+            if s.startswith("FORMAT(") or s.startswith("WRITE(") or s.startswith("PRINT"):
+                if s.startswith("FORMAT("):
+                    continue
+                cur.body.append((lab, "CONTINUE"))  # output statements are dropped (a label on them stays)
                 continue
             if s.startswith("DATA"):
                 rest = s[4:]
@@ -456,8 +464,20 @@ static inline double M_powr(double x, double y) { return pow(x, y); }
 static inline double M_sqrt(double x) { return sqrt(x); }
 static inline float M_sqrt(float x) { return sqrtf(x); }
 static inline double M_abs(double x) { return fabs(x); }
+// REAL*4 intrinsics: libm's single-precision functions, what gfortran calls for default REAL
+static inline float M_sin(float x) { return sinf(x); }
+static inline float M_cos(float x) { return cosf(x); }
+static inline float M_atan2(float y, float x) { return atan2f(y, x); }
+static inline float M_atan(float x) { return atanf(x); }
+static inline double M_atan(double x) { return atan(x); }
+static inline float M_asin(float x) { return asinf(x); }
+static inline float M_abs(float x) { return fabsf(x); }
+static inline float M_float(int i) { return (float)i; }
+static inline double M_dfloat(int i) { return (double)i; }
+static inline double M_mod(double a, double p) { return fmod(a, p); }
+static inline float M_mod(float a, float p) { return fmodf(a, p); }
 // x**n, literal n: the multiplication tree of gcc's powi table (gfc_conv_cst_int_power); table[n] for n <= 8
-template <int N> static inline double F_powc(double x) {
+template <int N, class T> static inline T F_powc(T x) {
   constexpr int tbl[9] = {0, 1, 1, 2, 2, 3, 3, 4, 4};
   static_assert(N >= 1 && N <= 8, "exponent");
   if constexpr (N == 1) return x;
@@ -507,12 +527,15 @@ def emit_unit(u, units, common_types):
     if do_stack:
         raise ValueError("unterminated DO in %s" % u.name)
     in_common = {}
+    size_of = {"int": 4, "float": 4, "bool": 4, "double": 8}
     for block, names in u.commons:
-        for pos, n in enumerate(names):
-            in_common[n] = (block, pos)
-            common_types.setdefault(block, {})
-            if common_types[block].setdefault(pos, u.type_of(n)) != u.type_of(n):
-                raise ValueError("COMMON /%s/ word %d changes type" % (block, pos))
+        off = 0
+        for n in names:
+            sz = size_of[u.type_of(n)]
+            off = (off + sz - 1) // sz * sz
+            in_common[n] = (block, off)
+            off += sz * (int(u.dims[n]) if n in u.dims else 1)
+        common_types[block] = max(common_types.get(block, 0), off)
     names = set(u.names) | set(u.dims) | {n for ns, _ in u.data for n in ns}
     if u.kind == "FUNCTION":
         names.add(u.name)
@@ -538,8 +561,10 @@ def emit_unit(u, units, common_types):
         if n in u.args:
             continue
         t = u.type_of(n)
-        if n in in_common:
-            decl.append("%s& v_%s = C_%s.w%d;" % (t, n, in_common[n][0], in_common[n][1]))
+        if n in in_common and n in u.dims:
+            decl.append("%s* v_%s = (%s*)(C_%s + %d) - 1;" % (t, n, t, in_common[n][0], in_common[n][1]))
+        elif n in in_common:
+            decl.append("%s& v_%s = *(%s*)(C_%s + %d);" % (t, n, t, in_common[n][0], in_common[n][1]))
         elif n in u.dims:
             size = int(u.dims[n])
             decl.append("TL %s v_%s[%d] = {0%s};" % (t, n, size + 1, "".join(", " + v for v in init.get(n, []))))
@@ -560,19 +585,7 @@ def emit_unit(u, units, common_types):
     return proto, text
 
 
-def main(src, dst):
-    units = parse_units(read_statements(src))
-    common_types, protos, texts = {}, [], []
-    for u in units.values():
-        p, t = emit_unit(u, units, common_types)
-        protos.append(p)
-        texts.append(t)
-    commons = []
-    for block, words in sorted(common_types.items()):
-        commons.append("TL struct { %s } C_%s;" % (" ".join("%s w%d = 0;" % (t, pos) for pos, t in sorted(words.items())), block))
-    with open(dst, "w") as f:
-        f.write(PRELUDE + "\n" + "\n".join(commons) + "\ndouble* ts05_ref_A();\n\n" + "\n".join(protos) + "\n\n" + "\n".join(texts))
-        f.write("""
+TS05_WRAPPERS = """
 // C entry points for the tests (ctypes): the model as the adapters call it, and its modules one by one
 extern "C" void ts05_ref_t04_s(const float* parmod, float ps, float x, float y, float z, float* b) {
   int iopt = 0; float p[11]; for (int i = 0; i < 10; ++i) p[i + 1] = parmod[i];
@@ -594,8 +607,42 @@ extern "C" void ts05_ref_extern(const double* par, double ps, double x, double y
            o[21], o[22], o[23], o[24], o[25], o[26], o[27], o[28], o[29], o[30], o[31], o[32], o[0], o[1], o[2]);
   for (int i = 0; i < 30; ++i) out[i] = o[i];
 }
-""")
+"""
+
+GEOPACK_WRAPPERS = """
+// C entry points for the tests (ctypes): RECALC_08 as TSY_RECALC calls it (geopack0508_adapter.for:21-30), then the state of
+// COMMON /GEOPACK1/ (34 words) and /GEOPACK2/ (G, H, REC: 3 x 105), and IGRF_GSW_08 (the adapters' IGRF_GSM)
+extern "C" void geopack_ref_recalc(int iyear, int iday, int ihour, int min, int isec, float* geopack1, float* geopack2) {
+  float vx = -400.0f, vy = 0.0f, vz = 0.0f;
+  f_RECALC_08(iyear, iday, ihour, min, isec, vx, vy, vz);
+  for (int i = 0; i < 34; ++i) geopack1[i] = ((float*)C_GEOPACK1)[i];
+  for (int i = 0; i < 315; ++i) geopack2[i] = ((float*)C_GEOPACK2)[i];
+}
+extern "C" void geopack_ref_igrf_gsw(float x, float y, float z, float* b) {
+  float bx = 0, by = 0, bz = 0;
+  f_IGRF_GSW_08(x, y, z, bx, by, bz);
+  b[0] = bx; b[1] = by; b[2] = bz;
+}
+"""
+
+
+def main(src, dst, only=None, wrappers="ts05"):
+    units = parse_units(read_statements(src))
+    if only:
+        units = {k: v for k, v in units.items() if k in only}
+    common_types, protos, texts = {}, [], []
+    for u in units.values():
+        p, t = emit_unit(u, units, common_types)
+        protos.append(p)
+        texts.append(t)
+    commons = []
+    for block, size in sorted(common_types.items()):  # storage sequences: members are matched by byte offset, as in Fortran
+        commons.append("alignas(8) TL unsigned char C_%s[%d] = {0};" % (block, (size + 7) // 8 * 8))
+    with open(dst, "w") as f:
+        f.write(PRELUDE + "\n" + "\n".join(commons) + ("\ndouble* ts05_ref_A();\n\n" if wrappers == "ts05" else "\n\n") + "\n".join(protos) + "\n\n" + "\n".join(texts))
+        f.write(TS05_WRAPPERS if wrappers == "ts05" else GEOPACK_WRAPPERS)
 
 
 if __name__ == "__main__":
-    main(sys.argv[1], sys.argv[2])
+    opts = dict(a[2:].split("=", 1) for a in sys.argv[3:] if a.startswith("--"))
+    main(sys.argv[1], sys.argv[2], only=set(opts["units"].split(",")) if "units" in opts else None, wrappers=opts.get("wrappers", "ts05"))

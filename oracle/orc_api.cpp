@@ -54,6 +54,21 @@ void orc_model_tsyganenko(void* mv, const double* parmod, void* t04_s) {
 }
 double orc_model_psi(void* mv) { return ((FieldBlock*)((Model*)mv)->field_block_ptr())->psi; }
 
+#ifdef ORC_HAVE_GRID
+// the oracle's Geopack state after TSY_RECALC, in the layout of COMMON /GEOPACK1/ (34 words) and /GEOPACK2/ (G, H, REC: 3 x 105),
+// and IGRF_GSW_08 with it: compared with the reference's own geopack2008.for as translated into oracle/_ref
+void orc_model_geopack(void* mv, float* geopack1, float* geopack2) {
+  const Geopack& c = *(const Geopack*)((FieldBlock*)((Model*)mv)->field_block_ptr())->igrf_ctx;
+  const float* w = &c.ST0;
+  for (int i = 0; i < 34; ++i) geopack1[i] = w[i];
+  for (int i = 0; i < 105; ++i) { geopack2[i] = c.G[i + 1]; geopack2[105 + i] = c.H[i + 1]; geopack2[210 + i] = c.REC[i + 1]; }
+}
+void orc_model_igrf_gsw(void* mv, float x, float y, float z, float* b) {
+  const Geopack& c = *(const Geopack*)((FieldBlock*)((Model*)mv)->field_block_ptr())->igrf_ctx;
+  IGRF_GSW_08(c, x, y, z, b[0], b[1], b[2]);
+}
+#endif
+
 void orc_model_free(void* m) { delete (Model*)m; }
 
 double orc_model_del(void* m) { return ((Model*)m)->del; }

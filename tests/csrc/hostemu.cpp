@@ -152,6 +152,17 @@ void emu_model_tsyganenko(void* m, const double* parmod, int yearday, int msec) 
   srt_host::igrf_recalc(yearday, msec, tmp, &M->ts.ps);
 #endif
 }
+#ifdef EMU_HAVE_GRID
+// the IGRF state the device code reads (SrtIgrf: G, H, REC and the GEO->GSW matrix) and the device statement of IGRF_GSW_08
+void emu_model_igrf(void* m, float* a9, float* ghrec) {
+  const SrtIgrf& ig = ((SrtModel*)m)->igrf;
+  const float a[9] = {ig.a11, ig.a21, ig.a31, ig.a12, ig.a22, ig.a32, ig.a13, ig.a23, ig.a33};
+  for (int i = 0; i < 9; ++i) a9[i] = a[i];
+  for (int i = 0; i < 105; ++i) { ghrec[i] = ig.g[i + 1]; ghrec[105 + i] = ig.h[i + 1]; ghrec[210 + i] = ig.rec[i + 1]; }
+}
+void emu_igrf_gsw(void* m, float x, float y, float z, float* b) { srt_igrf_gsw(((SrtModel*)m)->igrf, x, y, z, b[0], b[1], b[2]); }
+float emu_model_ts_ps(void* m) { return ((SrtModel*)m)->ts.ps; }
+#endif
 void emu_model_free(void* m) { delete (SrtModel*)m; }
 void emu_model_get(void* m, double* out /* ane0, cos_mu, sin_mu, del */) {
   SrtModel* M = (SrtModel*)m;
