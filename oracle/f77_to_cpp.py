@@ -20,7 +20,7 @@ import sys
 LOGOPS = {".LT.": "<", ".GT.": ">", ".LE.": "<=", ".GE.": ">=", ".EQ.": "==", ".NE.": "!=", ".AND.": "&&", ".OR.": "||", ".NOT.": "!"}
 INTRINSICS = {"DSIN": "M_sin", "DCOS": "M_cos", "DSQRT": "M_sqrt", "SQRT": "M_sqrt", "DEXP": "M_exp", "DLOG": "M_log", "DATAN2": "M_atan2",
               "DABS": "M_abs", "DTAN": "M_tan", "TAN": "M_tan", "SIN": "M_sin", "COS": "M_cos", "EXP": "M_exp", "ABS": "M_abs", "ATAN2": "M_atan2",
-              "ATAN": "M_atan", "ASIN": "M_asin", "FLOAT": "M_float", "DFLOAT": "M_dfloat", "DMOD": "M_mod", "AMOD": "M_mod"}
+              "ATAN": "M_atan", "ASIN": "M_asin", "FLOAT": "M_float", "DFLOAT": "M_dfloat", "DMOD": "M_mod", "AMOD": "M_mod", "MOD": "M_mod"}
 
 
 def read_statements(path):
@@ -40,6 +40,34 @@ def read_statements(path):
             continue
         out.append([line[:5].strip(), line[6:72]])
     return [(lab, re.sub(r"\s+", "", txt).upper()) for lab, txt in out]
+
+
+def read_statements_free(path):
+    """free source form (Fortran 90): `!` comments, `&` continuation, label = leading digits; same output as read_statements"""
+    out, pending = [], None
+    for raw in open(path, errors="replace"):
+        line, q = "", None
+        for ch in raw.rstrip("\n").rstrip("\r"):
+            if q:
+                q = None if ch == q else q
+            elif ch in "'\"":
+                q = ch
+            elif ch == "!":
+                break
+            line += ch
+        line = line.strip()
+        if not line:
+            continue
+        if pending is not None:
+            line = pending + line.lstrip("&")
+            pending = None
+        if line.endswith("&"):
+            pending = line[:-1]
+            continue
+        m = re.match(r"^(\d+)\s+(.*)$", line)
+        lab, txt = (m.group(1), m.group(2)) if m else ("", line)
+        out.append((lab, re.sub(r"\s+", "", txt).upper()))
+    return out
 
 
 TOKEN = re.compile(r"(\.(?:LT|GT|LE|GE|EQ|NE|AND|OR|NOT|TRUE|FALSE)\.)|(\*\*)|([A-Z][A-Z0-9_]*)|([(),+\-*/=])")
@@ -90,6 +118,8 @@ class Unit:
     def __init__(self, kind, name, args, rtype):
         self.kind, self.name, self.args, self.rtype = kind, name, args, rtype
         self.implicit_double = False
+        self.implicit = {}       # letter -> type (IMPLICIT REAL(KIND=DP) (A-H))
+        self.module_vars = set() # names that live in the enclosing module (free form)
         self.types = {}    # explicit types
         self.dims = {}     # array name -> dimension text (1-D only)
         self.commons = []  # (block, [names])
@@ -100,6 +130,8 @@ class Unit:
     def type_of(self, name):
         if name in self.types:
             return self.types[name]
+        if name[0] in self.implicit:
+            return self.implicit[name[0]]
         if name[0] in "IJKLMN":
             return "int"
         return "double" if self.implicit_double else "float"
@@ -292,6 +324,10 @@ def split_top(s, sep=","):
     return out
 
 
+def eq_inside_parens_only(s):
+    return top_level_eq(s) < 0
+
+
 def top_level_eq(s):
     depth = 0
     for i, ch in enumerate(s):
@@ -304,7 +340,9 @@ def top_level_eq(s):
     return -1
 
 
-HEAD = re.compile(r"^(SUBROUTINE|DOUBLEPRECISIONFUNCTION|REALFUNCTION|FUNCTION)([A-Z][A-Z0-9_]*)\((.*)\)$")
+HEAD = re.compile(r"^(SUBROUTINE|DOUBLEPRECISIONFUNCTION|REALFUNCTION|FUNCTION)([A-Z][A-Z0-9_]*)(?:\((.*)\))?$")
+F90_TYPES = (("REAL(KIND=DP)", "double"), ("REAL(KIND=SP)", "float"), ("DOUBLEPRECISION", "double"), ("INTEGER", "int"), ("LOGICAL", "bool"),
+             ("CHARACTER(LEN=*)", "const char*"), ("REAL", "float"))
 DO = re.compile(r"^DO(\d+)([A-Z][A-Z0-9_]*)=(.+)$")
 
 
@@ -320,24 +358,56 @@ def declare(unit, typ, rest):
 
 
 def parse_units(stmts):
-    units, cur = {}, None
+    units, cur, module = {}, None, None
     for lab, s in stmts:
+        if re.fullmatch(r"MODULE[A-Z][A-Z0-9_]*", s) and cur is None:
+            module = cur = Unit("MODULE", s[6:], [], None)  # its specification part: variables shared by the contained units
+            units["MODULE " + module.name] = module
+            continue
+        if s == "CONTAINS":
+            cur = None
+            continue
+        if s.startswith("ENDMODULE"):
+            module = cur = None
+            continue
+        if s.startswith("USE") and top_level_eq(s) < 0:
+            continue
         m = HEAD.match(s)
-        if m and top_level_eq(s) < 0:
+        if m and top_level_eq(s) < 0 and (cur is None or cur.kind == "MODULE"):
             kind = "SUBROUTINE" if m.group(1) == "SUBROUTINE" else "FUNCTION"
             rtype = {"DOUBLEPRECISIONFUNCTION": "double", "REALFUNCTION": "float"}.get(m.group(1))
-            cur = Unit(kind, m.group(2), [a for a in m.group(3).split(",") if a], rtype)
+            cur = Unit(kind, m.group(2), [a for a in (m.group(3) or "").split(",") if a], rtype)
+            if module is not None:  # host association: the module's names, unless the unit declares its own
+                cur.types, cur.dims, cur.implicit = dict(module.types), dict(module.dims), dict(module.implicit)
+                cur.module_vars = set(module.types) | set(module.dims)
             units[cur.name] = cur
             continue
         if cur is None:
             raise ValueError("statement outside a program unit: %r" % s)
-        if s == "END":
+        if s == "END" or s.startswith("ENDSUBROUTINE") or s.startswith("ENDFUNCTION"):
             cur = None
             continue
         is_assign = top_level_eq(s) >= 0 and not s.startswith("IF(") and not (DO.match(s) and len(split_top(DO.match(s).group(3))) >= 2)
         if not is_assign:
             if s.startswith("IMPLICITREAL*8"):
                 cur.implicit_double = True
+                continue
+            if s == "IMPLICITNONE":
+                continue
+            m = re.fullmatch(r"IMPLICIT(REAL\(KIND=DP\)|REAL\(KIND=SP\)|INTEGER)\(([A-Z])-([A-Z])\)", s)
+            if m:
+                t = dict(F90_TYPES)[m.group(1)]
+                for c in range(ord(m.group(2)), ord(m.group(3)) + 1):
+                    cur.implicit[chr(c)] = t
+                continue
+            if "::" in s:
+                spec, rest = s.split("::", 1)
+                t = [ty for key, ty in F90_TYPES if spec == key]
+                if not t:
+                    raise ValueError("declaration %r" % s)
+                declare(cur, t[0], rest)
+                for item in split_top(rest):
+                    cur.module_vars.discard(item.split("(")[0])
                 continue
             if s.startswith("REAL*8"):
                 declare(cur, "double", s[6:]); continue
@@ -350,7 +420,12 @@ def parse_units(stmts):
             if s.startswith("INTEGER"):
                 declare(cur, "int", s[7:]); continue
             if s.startswith("DIMENSION"):
-                declare(cur, None, s[9:]); continue
+                declare(cur, None, s[9:])
+                for item in split_top(s[9:]):  # a local array hides a module variable of that name
+                    if item.split("(")[0] in cur.module_vars:
+                        cur.module_vars.discard(item.split("(")[0])
+                        cur.types.pop(item.split("(")[0], None)
+                continue
             if s.startswith("COMMON/"):
                 m = re.fullmatch(r"COMMON/([A-Z0-9_]+)/(.+)", s)
                 items = split_top(m.group(2))
@@ -420,6 +495,41 @@ def translate_statement(s, unit, units):
         unit.names.add(m.group(1))
         target = "v_%s[%s]" % (m.group(1), translate_expr(m.group(2), unit, units)) if m.group(2) else "v_" + m.group(1)
         return ["%s = %s;" % (target, translate_expr(rhs, unit, units))]
+    if s.startswith("OPEN(") and eq_inside_parens_only(s):
+        m = re.fullmatch(r"OPEN\(UNIT=(\d+),FILE=([A-Z][A-Z0-9_]*),STATUS='OLD'\)", s)
+        if not m:
+            raise ValueError("OPEN form %r" % s)
+        unit.names.add(m.group(2))
+        return ["F_open(%s, v_%s);" % (m.group(1), m.group(2))]
+    if s.startswith("CLOSE("):
+        return [";"]
+    m = re.fullmatch(r"READ\((\d+),\*(?:,END=(\d+))?\)(.+)", s)
+    if m:  # list-directed input
+        fail = "goto L%s;" % m.group(2) if m.group(2) else "F_abort(\"end of file in READ\");"
+        out = ["if (!F_read_begin(%s)) { %s }" % (m.group(1), fail)]
+        for item in split_top(m.group(3)):
+            mm = re.fullmatch(r"\((.+),([A-Z][A-Z0-9_]*)=(.+),(.+)\)", item)
+            if mm:  # implied DO
+                var = "v_" + mm.group(2)
+                unit.names.add(mm.group(2))
+                out.append("for (%s = %s; %s <= %s; ++%s) { if (!F_read(%s, %s)) { %s } }" % (
+                    var, translate_expr(mm.group(3), unit, units), var, translate_expr(mm.group(4), unit, units), var, m.group(1),
+                    translate_expr(mm.group(1), unit, units), fail))
+            else:
+                out.append("if (!F_read(%s, %s)) { %s }" % (m.group(1), translate_expr(item, unit, units), fail))
+        return out
+    m = re.fullmatch(r"DO([A-Z][A-Z0-9_]*)=(.+)", s)
+    if m and len(split_top(m.group(2))) >= 2:  # block DO ... END DO
+        lim = split_top(m.group(2))
+        var = "v_" + m.group(1)
+        unit.names.add(m.group(1))
+        step = translate_expr(lim[2], unit, units) if len(lim) > 2 else "1"
+        return ["for (%s = %s; %s <= %s; %s += %s) {" % (var, translate_expr(lim[0], unit, units), var, translate_expr(lim[1], unit, units), var, step)]
+    if s == "ENDDO":
+        return ["}"]
+    m = re.fullmatch(r"CALL([A-Z][A-Z0-9_]*)", s)
+    if m:
+        s = s + "()"
     m = re.fullmatch(r"CALL([A-Z][A-Z0-9_]*)\((.*)\)", s)
     if m:
         callee = units.get(m.group(1))
@@ -427,7 +537,7 @@ def translate_statement(s, unit, units):
             raise ValueError("unknown subroutine %s" % m.group(1))
         p = ExprParser(tokenize(m.group(2)), unit, units)
         args = []
-        while True:
+        while m.group(2):
             args.append(p.arg_with_shape())
             if p.peek() == ",":
                 p.take()
@@ -476,6 +586,7 @@ static inline float M_float(int i) { return (float)i; }
 static inline double M_dfloat(int i) { return (double)i; }
 static inline double M_mod(double a, double p) { return fmod(a, p); }
 static inline float M_mod(float a, float p) { return fmodf(a, p); }
+static inline int M_mod(int a, int p) { return a % p; }
 // x**n, literal n: the multiplication tree of gcc's powi table (gfc_conv_cst_int_power); table[n] for n <= 8
 template <int N, class T> static inline T F_powc(T x) {
   constexpr int tbl[9] = {0, 1, 1, 2, 2, 3, 3, 4, 4};
@@ -494,6 +605,36 @@ static inline double F_pow(double x, double y) { return M_powr(x, y); }
 static inline double F_pow(double x, float y) { return M_powr(x, (double)y); }
 template <class T> static inline T& F_tmp(T&& v) { return v; }
 #define TL static thread_local
+// list-directed sequential input (READ (u,*) ...): every READ starts a new record, items are separated by blanks or commas
+// and continue onto following records; `d` exponents accepted
+#include <stdio.h>
+#include <stdlib.h>
+#include <string>
+struct F_Unit { FILE* f = nullptr; std::string line; size_t pos = 0; bool failed = false; };
+static F_Unit F_units[16];
+static void F_abort(const char* what) { fprintf(stderr, "translated Fortran: %s\n", what); abort(); }
+static void F_open(int u, const char* name) { if (F_units[u].f) fclose(F_units[u].f); F_units[u] = F_Unit(); F_units[u].f = fopen(name, "r"); F_units[u].failed = !F_units[u].f; }
+static bool F_next_line(F_Unit& U) {
+  if (!U.f) return false;
+  U.line.clear(); U.pos = 0;
+  int c; bool any = false;
+  while ((c = fgetc(U.f)) != EOF) { any = true; if (c == '\n') break; if (c != '\r') U.line.push_back((char)c); }
+  return any;
+}
+static bool F_read_begin(int u) { return F_next_line(F_units[u]); }
+template <class T> static bool F_read(int u, T& v) {
+  F_Unit& U = F_units[u];
+  for (;;) {
+    while (U.pos < U.line.size() && (U.line[U.pos] == ' ' || U.line[U.pos] == ',' || U.line[U.pos] == '\t')) ++U.pos;
+    if (U.pos < U.line.size()) break;
+    if (!F_next_line(U)) return false;
+  }
+  std::string tok;
+  while (U.pos < U.line.size() && U.line[U.pos] != ' ' && U.line[U.pos] != ',' && U.line[U.pos] != '\t') tok.push_back(U.line[U.pos++]);
+  for (char& ch : tok) if (ch == 'd' || ch == 'D') ch = 'e';
+  v = (T)strtod(tok.c_str(), nullptr);
+  return true;
+}
 """
 
 
@@ -511,7 +652,7 @@ def data_values(vals):
 
 def emit_unit(u, units, common_types):
     rt = "void" if u.kind == "SUBROUTINE" else (u.rtype or u.type_of(u.name))
-    params = ", ".join(("%s* v_%s" if a in u.dims else "%s& v_%s") % (u.type_of(a), a) for a in u.args)
+    params = ", ".join(("%s v_%s" if u.type_of(a) == "const char*" else "%s* v_%s" if a in u.dims else "%s& v_%s") % (u.type_of(a), a) for a in u.args)
     body_lines, do_stack = [], []
     for lab, s in u.body:
         if lab:
@@ -558,7 +699,7 @@ def emit_unit(u, units, common_types):
             raise ValueError("DATA in %s: %d values left over" % (u.name, len(vals) - k))
     decl = []
     for n in sorted(names):
-        if n in u.args:
+        if n in u.args or n in u.module_vars:
             continue
         t = u.type_of(n)
         if n in in_common and n in u.dims:
@@ -626,12 +767,32 @@ extern "C" void geopack_ref_igrf_gsw(float x, float y, float z, float* b) {
 """
 
 
+NGO_WRAPPERS = """
+// C entry points for the tests (ctypes): readinput, and dens the way funcPlasmaParams drives it (ngo_dens_model_adapter.f95:
+// 120-133: z(1), z(2), latitu set, `call dens`, ani(1:4) read)
+extern "C" int ngo_ref_readinput(const char* filename) { f_READINPUT(filename); return F_units[4].failed ? -1 : 0; }
+extern "C" void ngo_ref_dens(double z1, double z2, double latitu, double* ani) {
+  v_Z[1] = z1; v_Z[2] = z2; v_LATITU = latitu;
+  f_DENS();
+  for (int i = 0; i < 4; ++i) ani[i] = v_ANI[i + 1];
+}
+extern "C" void ngo_ref_state(double* out) {
+  const double s[12] = {v_ANE0, v_RBASE, v_R0, (double)v_NUM, (double)v_KDUCTS, v_THERM, v_RZERO, v_SCBOT, v_LK, v_EXPK, v_DDK, v_PI};
+  for (int i = 0; i < 12; ++i) out[i] = s[i];
+}
+"""
+
+
 def main(src, dst, only=None, wrappers="ts05"):
-    units = parse_units(read_statements(src))
+    units = parse_units(read_statements_free(src) if wrappers == "ngo" else read_statements(src))
     if only:
         units = {k: v for k, v in units.items() if k in only}
     common_types, protos, texts = {}, [], []
     for u in units.values():
+        if u.kind == "MODULE":  # module variables: one object each, shared by the contained units
+            for n in sorted(set(u.types) | set(u.dims)):
+                protos.append("TL %s v_%s%s;" % (u.type_of(n), n, "[%d] = {0}" % (int(u.dims[n]) + 1) if n in u.dims else " = 0"))
+            continue
         p, t = emit_unit(u, units, common_types)
         protos.append(p)
         texts.append(t)
@@ -640,7 +801,7 @@ def main(src, dst, only=None, wrappers="ts05"):
         commons.append("alignas(8) TL unsigned char C_%s[%d] = {0};" % (block, (size + 7) // 8 * 8))
     with open(dst, "w") as f:
         f.write(PRELUDE + "\n" + "\n".join(commons) + ("\ndouble* ts05_ref_A();\n\n" if wrappers == "ts05" else "\n\n") + "\n".join(protos) + "\n\n" + "\n".join(texts))
-        f.write(TS05_WRAPPERS if wrappers == "ts05" else GEOPACK_WRAPPERS)
+        f.write({"ts05": TS05_WRAPPERS, "geopack": GEOPACK_WRAPPERS, "ngo": NGO_WRAPPERS}[wrappers])
 
 
 if __name__ == "__main__":

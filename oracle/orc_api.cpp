@@ -69,6 +69,20 @@ void orc_model_igrf_gsw(void* mv, float x, float y, float z, float* b) {
 }
 #endif
 
+// `dens` of the Ngo model with the arguments funcPlasmaParams hands it (z(1), z(2), latitu) and the state readinput left:
+// compared with the reference's own ngo_dens_model.f95 as translated into oracle/_ref/libngo_ref*.so
+void orc_ngo_dens(void* mv, double z1, double z2, double latitu, double* ani) {
+  NgoState& st = ((NgoModel*)(Model*)mv)->st;
+  st.z[1] = z1; st.z[2] = z2; st.latitu = latitu;
+  st.dens();
+  for (int i = 0; i < 4; ++i) ani[i] = st.ani[i + 1];
+}
+void orc_ngo_state(void* mv, double* out) {
+  const NgoState& st = ((NgoModel*)(Model*)mv)->st;
+  const double s[12] = {st.ane0, st.rbase, st.r0, (double)st.num, (double)st.kducts, st.therm, st.rzero, st.scbot, st.lk, st.expk, st.ddk, st.pi};
+  for (int i = 0; i < 12; ++i) out[i] = s[i];
+}
+
 void orc_model_free(void* m) { delete (Model*)m; }
 
 double orc_model_del(void* m) { return ((Model*)m)->del; }
