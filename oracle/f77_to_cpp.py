@@ -96,7 +96,11 @@ def tokenize(s):
             j += m2.end()
         if j == i:
             raise ValueError("cannot tokenize %r at %r" % (s, s[i:]))
-        toks.append(("NUM", s[i:j]))
+        text = s[i:j]
+        if s[j:j + 2] == "_8" and not s[j + 2:j + 3].isalnum():  # kind suffix: a REAL*8 literal
+            text = text.replace("E", "D") if "E" in text else text + "D0"
+            j += 2
+        toks.append(("NUM", text))
         i = j
     return toks
 
@@ -417,6 +421,12 @@ def parse_units(stmts):
                 declare(cur, "float", s[4:]); continue
             if s.startswith("LOGICAL"):
                 declare(cur, "bool", s[7:]); continue
+            if s.startswith("INTEGER*4"):
+                declare(cur, "int", s[9:]); continue
+            if s.startswith("PARAMETER("):  # named constants: evaluated once at the top of the unit, in the declared type
+                for item in split_top(s[10:-1]):
+                    cur.body.insert(0, ("", item))
+                continue
             if s.startswith("INTEGER"):
                 declare(cur, "int", s[7:]); continue
             if s.startswith("DIMENSION"):
@@ -560,6 +570,7 @@ static inline double M_cos(double x) { return srt_cos(x); }
 static inline double M_exp(double x) { return srt_exp(x); }
 static inline double M_log(double x) { return srt_log(x); }
 static inline double M_atan2(double y, double x) { return srt_atan2(y, x); }
+static inline double M_atan(double x) { return srt_atan(x); }
 static inline double M_tan(double x) { double s, c; srt_sincos(x, s, c); return s / c; }
 static inline double M_powr(double x, double y) { return srt_pow(x, y); }
 #else
@@ -568,6 +579,7 @@ static inline double M_cos(double x) { return cos(x); }
 static inline double M_exp(double x) { return exp(x); }
 static inline double M_log(double x) { return log(x); }
 static inline double M_atan2(double y, double x) { return atan2(y, x); }
+static inline double M_atan(double x) { return atan(x); }
 static inline double M_tan(double x) { return tan(x); }
 static inline double M_powr(double x, double y) { return pow(x, y); }
 #endif
@@ -579,7 +591,6 @@ static inline float M_sin(float x) { return sinf(x); }
 static inline float M_cos(float x) { return cosf(x); }
 static inline float M_atan2(float y, float x) { return atan2f(y, x); }
 static inline float M_atan(float x) { return atanf(x); }
-static inline double M_atan(double x) { return atan(x); }
 static inline float M_asin(float x) { return asinf(x); }
 static inline float M_abs(float x) { return fabsf(x); }
 static inline float M_float(int i) { return (float)i; }
@@ -783,8 +794,27 @@ extern "C" void ngo_ref_state(double* out) {
 """
 
 
+XFORM_WRAPPERS = """
+// C entry points for the tests (ctypes): the two transformations the adapters call (ngo_dens_model_adapter.f95:145,202)
+extern "C" void xform_ref_sm_to_gsm(int yearday, int msec, const double* x, double* out) {
+  int itime[3] = {0, yearday, msec}; double xi[4] = {0, x[0], x[1], x[2]}, xo[4] = {0, 0, 0, 0};
+  f_SM_TO_GSM_D(itime, xi, xo);
+  out[0] = xo[1]; out[1] = xo[2]; out[2] = xo[3];
+}
+extern "C" void xform_ref_gsm_to_sm(int yearday, int msec, const double* x, double* out) {
+  int itime[3] = {0, yearday, msec}; double xi[4] = {0, x[0], x[1], x[2]}, xo[4] = {0, 0, 0, 0};
+  f_GSM_TO_SM_D(itime, xi, xo);
+  out[0] = xo[1]; out[1] = xo[2]; out[2] = xo[3];
+}
+"""
+
+
 def main(src, dst, only=None, wrappers="ts05"):
-    units = parse_units(read_statements_free(src) if wrappers == "ngo" else read_statements(src))
+    free = wrappers in ("ngo", "xform")
+    stmts = []
+    for one in src.split(","):
+        stmts += read_statements_free(one) if free else read_statements(one)
+    units = parse_units(stmts)
     if only:
         units = {k: v for k, v in units.items() if k in only}
     common_types, protos, texts = {}, [], []
@@ -801,7 +831,7 @@ def main(src, dst, only=None, wrappers="ts05"):
         commons.append("alignas(8) TL unsigned char C_%s[%d] = {0};" % (block, (size + 7) // 8 * 8))
     with open(dst, "w") as f:
         f.write(PRELUDE + "\n" + "\n".join(commons) + ("\ndouble* ts05_ref_A();\n\n" if wrappers == "ts05" else "\n\n") + "\n".join(protos) + "\n\n" + "\n".join(texts))
-        f.write({"ts05": TS05_WRAPPERS, "geopack": GEOPACK_WRAPPERS, "ngo": NGO_WRAPPERS}[wrappers])
+        f.write({"ts05": TS05_WRAPPERS, "geopack": GEOPACK_WRAPPERS, "ngo": NGO_WRAPPERS, "xform": XFORM_WRAPPERS}[wrappers])
 
 
 if __name__ == "__main__":

@@ -83,6 +83,11 @@ void orc_ngo_state(void* mv, double* out) {
   for (int i = 0; i < 12; ++i) out[i] = s[i];
 }
 
+// SM <-> GSM of the adapters (xform_double chain restated in orc_models.h): compared with the reference's own
+// xform_double/*.f95 as translated into oracle/_ref/libxform_ref*.so
+void orc_sm_to_gsm(void* mv, const double* x, double* out) { ((FieldBlock*)((Model*)mv)->field_block_ptr())->tilt.sm_to_gsm(x, out); }
+void orc_gsm_to_sm(void* mv, const double* x, double* out) { ((FieldBlock*)((Model*)mv)->field_block_ptr())->tilt.gsm_to_sm(x, out); }
+
 void orc_model_free(void* m) { delete (Model*)m; }
 
 double orc_model_del(void* m) { return ((Model*)m)->del; }
