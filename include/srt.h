@@ -145,7 +145,8 @@ int srt_release_scratch(void);
  *   d_summary   [nrays][24]: words 0..19 last row, 20 nsteps, 21 stopcond, 22 rejected+cone attempts, 23 flags
  *               (integers stored as doubles)
  *   d_counters  [8] uint64: log rows used, accepted steps, attempts, rays dropped because the log was full,
- *               ray-queue head, fast-forwarded NaN steps (included in accepted and attempts), block rounds sum / max
+ *               ray-queue head, fast-forwarded NaN steps (included in accepted and attempts), attempts taken from a shadow team
+ *               (team kernel, included in attempts), most block rounds of a block
  *               (zeroed by the call)
  * stream: a cudaStream_t (NULL = default stream).  Asynchronous: returns after the launch. */
 int srt_trace_batch_device(const srt_model* m, int64_t nrays, double* d_rays, const srt_run_params* p, double* d_log, int64_t log_capacity,

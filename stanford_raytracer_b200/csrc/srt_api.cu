@@ -433,6 +433,10 @@ int symbol_launched(DevCtx* c, int tu, cudaStream_t stream) {
 int launch_trace(DevCtx* c, srt_model* m, const SrtRunParams& P, const SrtBatch& B0, cudaStream_t stream) {
   SrtBatch B = B0;
   B.order_mul = ray_order_mul(B.nrays);
+  {
+    const char* env = getenv("SRT_TEAM_SHADOW");  // A/B hook: 0 = no shadow teams
+    B.shadow = (env && env[0] == '0') ? 0 : 1;
+  }
   int mode, block, grid;
   int rc = launch_config(c, m, B.nrays, &mode, &block, &grid, nullptr);
   if (rc) return rc;
@@ -783,6 +787,7 @@ int srt_trace_batch_device(const srt_model* m, int64_t nrays, double* d_rays, co
   B.counters = (unsigned long long*)d_counters;
   B.nlogged = nullptr;
   B.order_mul = 1;  // set by launch_trace
+  B.shadow = 1;     // set by launch_trace
   return launch_trace(c, const_cast<srt_model*>(m), P, B, (cudaStream_t)stream);
 }
 

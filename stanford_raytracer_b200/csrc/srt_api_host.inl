@@ -188,6 +188,7 @@ int trace_on_device(DevCtx* c, srt_model* m, const std::vector<int64_t>& ids, co
     B.counters = (unsigned long long*)c->counters.p;
     B.nlogged = (unsigned*)c->nlogged.p;
     B.order_mul = 1;
+    B.shadow = 1;
     if ((rc = launch_trace(c, m, P, B, st))) return rc;
     unsigned long long* counters = (unsigned long long*)((char*)c->small_h.p);
     unsigned* nlogged_h = (unsigned*)((char*)c->small_h.p + 64);

@@ -106,6 +106,29 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
   unsigned sync_iter = 0;
   int cap_teams = (int)(blockDim.x >> 3);  // team slots of this block that may hold a live ray
   (void)sync_iter; (void)cap_teams;
+  // ---- shadow teams (block-synchronous kernel, adaptive runs).  Once the ray queue is empty a block has more team slots
+  // than rays, and a long ray is a serial chain of attempts of which about one in four fails at the resonance-cone test
+  // (raytracer.f95:891-899: dt -> dt/2, retry from the same state; config 2: 6 439 of the 26 477 attempts of a
+  // 20 000-step ray).  The compaction step therefore seats each live ray in an EVEN team slot (the primary) and leaves
+  // the odd slot next to it to a shadow team, which runs the SAME attempt from the same state with the step the retry
+  // after a cone refinement would use.  If the primary's attempt then ends in a cone refinement to exactly that dt
+  // (compared bit for bit), the retry has already been computed: the shadow's attempt IS the retry (same state, same dt,
+  // same instructions), its outcome is taken and the failed attempt cost no extra rounds.  In every other case the
+  // shadow's work is dropped.  After each estimate round both teams take the state of the live one and the shadow sets up
+  // its next guess.  Pure scheduling of identical arithmetic: no result changes (tests/test_gpu_parity.py,
+  // test_gpu_c3_long.py and the bench's parity check run whole batches in this mode).
+  bool pairs_on = false;       // block-uniform: team slots are (primary, shadow) pairs
+  bool shadow_ready = false;   // pair-uniform: the shadow runs the current attempt alongside the primary
+  int live_is_S = 0, did_est = 0;
+  int shadow_kind = 2;         // shadow: the kind of failure whose retry it is running
+  int err_small = 1;           // the most recent error estimate of this ray was below maxerr / 100 (the growth test's condition)
+  int last_fail = 0;           // kind of this ray's most recent failed attempt: 1 error test (dt -> 0.8 dt), 2 cone test (dt -> dt / 2)
+  double dt_p = 0.0;           // shadow: the primary's dt (the stop test at the attempt start is the primary's)
+  unsigned long long my_spec = 0;
+  const bool odd_team = (lane & 8) != 0;
+  const unsigned pmask = 0xffffu << (lane & 16);
+  const int pbase = lane & 16;
+  (void)last_fail; (void)err_small; (void)shadow_kind; (void)pairs_on; (void)shadow_ready; (void)live_is_S; (void)did_est; (void)dt_p; (void)odd_team; (void)pmask; (void)pbase; (void)my_spec;
   for (;;) {
     // ================= refill: idle teams take the next ray; one atomic per warp
 #if defined(SRT_TEAM_BLOCK_SYNC)
@@ -163,22 +186,23 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
         }
       }
     }
+    bool is_shadow = pairs_on && odd_team;
 #if defined(SRT_TEAM_BLOCK_SYNC)
     // block-synchronous rounds: the warps of a block walk the round's code in phase and share instruction lines
     // live teams of this block; a team waiting for its refill round (phase alignment) still has the queue to look at
-    const int live = __syncthreads_count(((phase != SRT_PH_IDLE || !exhausted) && r == 0) ? 1 : 0);
+    const int live = __syncthreads_count(((phase != SRT_PH_IDLE || !exhausted) && r == 0 && !is_shadow) ? 1 : 0);
     if (live == 0) break;
     // ---- compaction.  Once the ray queue is empty, finished rays leave holes: a block whose few live teams are
     // spread over all its warps still issues every warp.  When at most half of the team slots in use are live, the
     // live teams are re-packed into the lowest warps through shared memory (pure data movement: results unchanged);
     // the emptied warps then only attend the barrier.  Config 2 spends most of its time in this regime.
-    if ((++sync_iter & 31u) == 0u && live * 2 <= cap_teams && cap_teams > 4) {
+    if ((++sync_iter & 31u) == 0u && live * (pairs_on ? 4 : 2) <= cap_teams && cap_teams > 4) {
       if (__syncthreads_or(exhausted ? 1 : 0)) {
         unsigned long long* pk = srt_pack_smem;
         const int nslots = (int)(blockDim.x >> 1);  // lane slots available: half a block
         if (threadIdx.x == 0) srt_pack_count = 0;
         __syncthreads();
-        if (phase != SRT_PH_IDLE) {
+        if (phase != SRT_PH_IDLE && !is_shadow) {
           int idx = 0;
           if (r == 0) idx = atomicAdd(&srt_pack_count, 1);
           idx = __shfl_sync(T.tmask, idx, T.tbase);
@@ -195,8 +219,12 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
         }
         __syncthreads();
         const int nlive = srt_pack_count;
-        if ((int)(threadIdx.x >> 3) < nlive) {
-          const int o = (int)threadIdx.x;  // team (threadIdx.x >> 3), role r
+        // the live rays fit twice (nlive <= cap_teams / 2): adaptive runs seat them as (primary, shadow) pairs
+        const bool want_pairs = adaptive && B.shadow != 0;
+        const int seat = (int)(threadIdx.x >> 3);
+        const int src_team = want_pairs ? (seat >> 1) : seat;
+        if (src_team < nlive && !(want_pairs && odd_team)) {
+          const int o = src_team * 8 + r;
           double dv[20];
 #pragma unroll
           for (int i = 0; i < 20; ++i) dv[i] = __longlong_as_double((long long)pk[i * nslots + o]);
@@ -217,7 +245,12 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
           phase = SRT_PH_IDLE;
           exhausted = true;
         }
-        cap_teams = (nlive + 3) & ~3;  // whole warps
+        pairs_on = want_pairs;
+        last_fail = 0;
+        shadow_ready = false;  // the shadows join at the end of their primary's next estimate round
+        did_est = 0;
+        cap_teams = ((want_pairs ? 2 * nlive : nlive) + 3) & ~3;  // whole warps
+        is_shadow = pairs_on && odd_team;
         __syncthreads();
       }
     }
@@ -238,13 +271,13 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
           if (srt_sqrt(srt_dot3(xs, xs)) < P.minalt) sc = 1;
           else if (srt_sqrt(srt_dot3(xs + 3, xs + 3)) == 0.0) sc = 2;
           else if (srt_sqrt(srt_dot3(vg, vg)) > 1.0 + 1e-2) sc = 3;
-          else if (dt < (double)1e-14f) sc = 5;
+          else if ((is_shadow ? dt_p : dt) < (double)1e-14f) sc = 5;  // a shadow ends when its primary does
           else if (nstep >= P.maxsteps) sc = 6;
           stopcond = sc;
           if (sc != 0) done = 1;
         }
         if (done) {
-          if (r == 0) {
+          if (r == 0 && !is_shadow) {
             double* s = B.summary + slot * SRT_SUMMARY_WORDS;
             s[20] = (double)nstep;
             s[21] = (double)stopcond;
@@ -362,16 +395,62 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
 #include "srt_team_est.inl"
       }
     }
+#if defined(SRT_TEAM_BLOCK_SYNC)
+    // ================= shadow pairs: after the primary's estimate round both teams take the state of the live one
+    if (pairs_on) {
+      const int fl = __shfl_sync(pmask, did_est | (live_is_S << 1), pbase);
+      did_est = 0;
+      if (fl & 1) {
+        const int src = pbase + ((fl & 2) ? 8 : 0) + r;
+        w = __shfl_sync(pmask, w, src); wl = __shfl_sync(pmask, wl, src); t = __shfl_sync(pmask, t, src); dt = __shfl_sync(pmask, dt, src);
+        dfdw_rec = __shfl_sync(pmask, dfdw_rec, src);
+        vg[0] = __shfl_sync(pmask, vg[0], src); vg[1] = __shfl_sync(pmask, vg[1], src); vg[2] = __shfl_sync(pmask, vg[2], src);
+        xc = __shfl_sync(pmask, xc, src); dfdk_c = __shfl_sync(pmask, dfdk_c, src); rhs1c = __shfl_sync(pmask, rhs1c, src);
+        slot = __shfl_sync(pmask, slot, src);
+        unsigned f1 = (dropped ? 1u : 0u) | (attempt_start ? 2u : 0u) | (finish_now ? 4u : 0u) | (cone_exit ? 8u : 0u) |
+                      ((unsigned)lastrefinedown << 4) | ((unsigned)phase << 8) | ((unsigned)stage << 12) | ((unsigned)stopcond << 16) |
+                      ((unsigned)last_fail << 20) | ((unsigned)err_small << 24);
+        f1 = __shfl_sync(pmask, f1, src);
+        dropped = f1 & 1u; attempt_start = f1 & 2u; finish_now = f1 & 4u; cone_exit = (f1 >> 3) & 1u;
+        lastrefinedown = (int)((f1 >> 4) & 0xfu); phase = (int)((f1 >> 8) & 0xfu); stage = (int)((f1 >> 12) & 0xfu);
+        stopcond = (int)((f1 >> 16) & 0xfu); last_fail = (int)((f1 >> 20) & 0xfu); err_small = (int)((f1 >> 24) & 1u);
+        nstep = __shfl_sync(pmask, nstep, src); nrej = __shfl_sync(pmask, nrej, src); ncone = __shfl_sync(pmask, ncone, src);
+        nlog = __shfl_sync(pmask, nlog, src);
+        exhausted = true;
+        dt_p = dt;
+        if (odd_team) {
+          // The retry the shadow prepares is the one after the kind of failure this ray met last.  Error test
+          // (raytracer.f95:790-798): dt -> 0.8 dt from the same state, `w` of :821 not yet set by that attempt.  Cone test
+          // (:891-899), reached after the growth test of :800-812, taken to go the way this ray's last error estimate would have
+          // sent it: dt -> (dt or 1.25 dt) / 2, `w` set.
+          shadow_kind = last_fail == 1 ? 1 : 2;
+          if (last_fail == 1) {
+            dt = 0.8 * dt;
+            nrej++;
+          } else {
+            const bool grow = lastrefinedown == 0 && err_small && dt * 1.25 < P.dtmax;
+            dt = grow ? (dt * 1.25) / 2.0 : dt / 2.0;
+            ncone++;
+            wl = w;
+          }
+          lastrefinedown = 1;
+        }
+        shadow_ready = true;
+      }
+    }
+#endif
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     my_accepted += __shfl_down_sync(full, my_accepted, o);
     my_attempts += __shfl_down_sync(full, my_attempts, o);
     my_ff += __shfl_down_sync(full, my_ff, o);
+    my_spec += __shfl_down_sync(full, my_spec, o);
   }
   if (lane == 0) {
     if (my_ff) atomicAdd(&B.counters[5], my_ff);
-    if (threadIdx.x == 0) { atomicAdd(&B.counters[6], (unsigned long long)sync_iter); atomicMax(&B.counters[7], (unsigned long long)sync_iter); }
+    if (my_spec) atomicAdd(&B.counters[6], my_spec);
+    if (threadIdx.x == 0) atomicMax(&B.counters[7], (unsigned long long)sync_iter);
     atomicAdd(&B.counters[1], my_accepted);
     atomicAdd(&B.counters[2], my_attempts);
   }

@@ -43,6 +43,7 @@
           } else {
             if (err != err) err = srt_nan();  // Q1
           }
+          err_small = (err < P.maxerr / 100.0) ? 1 : 0;
           if (err > P.maxerr) {
             dt = 0.8 * dt;
             lastrefinedown = 1;
@@ -53,6 +54,8 @@
             lastrefinedown = 0;
           }
         }
+        int outcome = retry ? 1 : 0;  // 0: goes on to the accept side, 1: rejected by the error test, 2: cone-refined, 3: cone exit (fixed step)
+        double knew[3] = {0.0, 0.0, 0.0};
         if (!retry) {
           wl = w;  // raytracer.f95:821, before the cone test (see srt_ray_attempt)
           // re-project |k| at est2 (lane 7 holds the plasma there and its Stix set at w)
@@ -64,7 +67,6 @@
           for (int i = 0; i < 3; ++i) kk = kk + (e2[3 + i] * e2[3 + i] - (-0.0) * 0.0);
           SrtCplx nrm;
           srt_csqrt(kk, 0.0, nrm.re, nrm.im);
-          double knew[3];
           double imsum = 0.0;
 #pragma unroll
           for (int i = 0; i < 3; ++i) {
@@ -79,14 +81,37 @@
               lastrefinedown = 1;
               ncone++;
               retry = true;
+              outcome = 2;
             } else {
               cone_exit = 1;
               stopcond = 0;
               finish_now = true;
               phase = SRT_PH_STAGE;
               attempt_start = true;
+              outcome = 3;
             }
-          } else {
+          }
+        }
+        // ---- shadow pairs (srt_team.cuh): is the retry the primary now needs the attempt its shadow has just finished?
+        bool i_live = true;
+        live_is_S = 0;
+#if defined(SRT_TEAM_BLOCK_SYNC)
+        if (outcome == 1 || outcome == 2) last_fail = outcome;
+        if (pairs_on && shadow_ready) {
+          const int out_p = __shfl_sync(pmask, outcome, pbase);
+          const long long dt_next_p = __shfl_sync(pmask, __double_as_longlong(dt), pbase);
+          const int prepared = __shfl_sync(pmask, shadow_kind, pbase + 8);
+          int hit = (odd_team && out_p == prepared && dt_next_p == __double_as_longlong(dt_used) && !(dt_used < (double)1e-14f)) ? 1 : 0;
+          hit = __shfl_sync(pmask, hit, pbase + 8);
+          live_is_S = hit;
+          i_live = odd_team ? (hit != 0) : (hit == 0);
+          if (hit && odd_team && r == 0) ++my_spec;
+          // the live attempt's failure, else the primary's, is the ray's most recent one
+          if (odd_team && hit && outcome != 1 && outcome != 2) last_fail = out_p;
+        }
+#endif
+        {
+          if (outcome == 0 && i_live) {
             // ---- accept (raytracer.f95:909-922)
             xc = (comp == 0) ? e2[0] : (comp == 1) ? e2[1] : (comp == 2) ? e2[2] : (comp == 3) ? knew[0] : (comp == 4) ? knew[1] : knew[2];
             lastrefinedown = 0;
@@ -166,7 +191,8 @@
           }
         }
         if (retry) {
-          if (r == 0) ++my_attempts;
+          if (r == 0 && (i_live || !odd_team || !pairs_on)) ++my_attempts;  // a primary's failed attempt counts; a shadow's only when it is the live one
           phase = SRT_PH_STAGE;
           attempt_start = true;
         }
+        did_est = 1;

@@ -31,4 +31,4 @@ for path in libs:
             best = min(best, e0.elapsed_time(e1))
         c = counters.cpu().numpy()
         ki = m.kernel_info(n)
-        print("%-28s %-6s n=%d ms=%9.1f accepted=%d steps/s=%.3g regs=%d local=%d blocks/SM=%d" % (os.path.basename(path), mode, n, best, c[1], c[1] / (best * 1e-3), ki["regs"], ki["local_bytes"], ki["blocks_per_sm"]), flush=True)
+        print("%-28s %-6s n=%d ms=%9.1f accepted=%d steps/s=%.3g attempts=%d shadow_attempts=%d rounds_max=%d regs=%d local=%d blocks/SM=%d" % (os.path.basename(path), mode, n, best, c[1], c[1] / (best * 1e-3), c[2], c[6], c[7], ki["regs"], ki["local_bytes"], ki["blocks_per_sm"]), flush=True)
