@@ -88,6 +88,27 @@ void orc_ngo_state(void* mv, double* out) {
 void orc_sm_to_gsm(void* mv, const double* x, double* out) { ((FieldBlock*)((Model*)mv)->field_block_ptr())->tilt.sm_to_gsm(x, out); }
 void orc_gsm_to_sm(void* mv, const double* x, double* out) { ((FieldBlock*)((Model*)mv)->field_block_ptr())->tilt.gsm_to_sm(x, out); }
 
+// Hooks for the reference's integrator as translated into oracle/_ref/librt_ref.so (f90_to_cpp.py): funcPlasmaParams = this
+// oracle's adapter for the model chosen with orc_hook_model, csvd = the oracle's stand-in for ZGESVD (row 3 of VT = the conjugate
+// of the right singular vector of the smallest singular value; the other rows are not used by the caller).
+static thread_local Model* g_hook_model = nullptr;
+void orc_hook_model(void* mv) { g_hook_model = (Model*)mv; }
+void orc_hook_plasma(const double* x, double* qs, double* Ns, double* ms, double* nus, double* B0, int* nspec) {
+  Plasma p;
+  g_hook_model->plasma(x, p);
+  *nspec = p.nspec;
+  for (int i = 0; i < p.nspec; ++i) { qs[i] = p.qs[i]; Ns[i] = p.Ns[i]; ms[i] = p.ms[i]; nus[i] = p.nus[i]; }
+  for (int i = 0; i < 3; ++i) B0[i] = p.B0[i];
+}
+void orc_hook_csvd(const double* m_re_im, double* vt_re_im) {
+  cplx M[3][3], v[3];
+  double sv[3];
+  for (int j = 0; j < 3; ++j) for (int i = 0; i < 3; ++i) M[i][j] = {m_re_im[2 * (i + 3 * j)], m_re_im[2 * (i + 3 * j) + 1]};
+  csvd3_smallest_right_vector(M, v, sv);
+  for (int k = 0; k < 18; ++k) vt_re_im[k] = 0.0;
+  for (int j = 0; j < 3; ++j) { vt_re_im[2 * (2 + 3 * j)] = v[j].re; vt_re_im[2 * (2 + 3 * j) + 1] = -v[j].im; }
+}
+
 void orc_model_free(void* m) { delete (Model*)m; }
 
 double orc_model_del(void* m) { return ((Model*)m)->del; }

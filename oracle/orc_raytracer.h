@@ -382,7 +382,7 @@ inline void raytracer_run(RunResult& out, const double pos0[3], double dir0[3], 
   k0mag = (root == 1) ? k1mag : k2mag;
   double x[7], est1[7], est2[7];
   for (int i = 0; i < 3; ++i) x[i] = pos0[i];
-  for (int i = 0; i < 3; ++i) x[3 + i] = k0mag.re * dir0[i];  // real(k0mag*dir0)
+  for (int i = 0; i < 3; ++i) x[3 + i] = k0mag.re * dir0[i] - k0mag.im * 0.0;  // real(k0mag*dir0): the full complex product with (dir0, +0.0)
   x[6] = w0;
   double dt = dt0, t = 0.0;
   int lastrefinedown = 0;

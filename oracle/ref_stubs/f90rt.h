@@ -1,0 +1,160 @@
+// oracle/ref_stubs/f90rt.h -- TEST INFRASTRUCTURE.  Run-time support for the C++ that oracle/f90_to_cpp.py produces from the
+// reference's Fortran 90 sources (fortran/raytracer.f95, util.f95, bmodel_dipole.f95, constants.f95): rank-1 and rank-2
+// arrays with Fortran's element-wise expression semantics, 1-based indexing, sections, and the array intrinsics the
+// sources use.  What this header decides (a Fortran compiler would): element-wise operations evaluate each element with
+// the scalar operation in source order; SUM, DOT_PRODUCT, MAXVAL, MINVAL run over the elements in index order starting
+// from the first (gfortran inlines them so without -ffast-math); the right-hand side of an array assignment is evaluated
+// completely before the left-hand side is stored; COMPLEX arithmetic follows -fcx-fortran-rules (compile with that flag).
+#pragma once
+#include <math.h>
+#include <complex>
+#include <type_traits>
+#include <vector>
+
+typedef std::complex<double> cd;
+
+template <class T> struct Vec;
+template <class T> struct is_vec : std::false_type {};
+template <class T> struct is_vec<Vec<T>> : std::true_type {};
+
+template <class T> struct Vec {
+  std::vector<T> d;
+  bool allocated = false;
+  Vec() {}
+  explicit Vec(int n) : d((size_t)(n > 0 ? n : 0), T()), allocated(true) {}
+  Vec(std::initializer_list<T> l) : d(l), allocated(true) {}
+  int size() const { return (int)d.size(); }
+  T& operator()(int i) { return d[(size_t)(i - 1)]; }
+  const T& operator()(int i) const { return d[(size_t)(i - 1)]; }
+  // whole-array assignment: conforming shapes; an unallocated / differently sized target takes the shape (allocatable LHS)
+  template <class U> Vec& operator=(const Vec<U>& o) {
+    std::vector<T> t(o.d.size());
+    for (size_t i = 0; i < o.d.size(); ++i) t[i] = (T)o.d[i];
+    d.swap(t); allocated = true; return *this;
+  }
+  Vec& operator=(const Vec& o) { if (this != &o) { d = o.d; allocated = true; } return *this; }
+  template <class U, class = typename std::enable_if<!is_vec<U>::value>::type> Vec& operator=(const U& s) { for (auto& e : d) e = (T)s; return *this; }
+  struct Sec {
+    Vec& v; int lo, hi;
+    template <class U> Sec& operator=(const Vec<U>& o) { for (int i = lo; i <= hi; ++i) v(i) = (T)o(i - lo + 1); return *this; }
+    Sec& operator=(const Sec& o) { Vec t = o; return *this = t; }
+    template <class U, class = typename std::enable_if<!is_vec<U>::value>::type> Sec& operator=(const U& s) { for (int i = lo; i <= hi; ++i) v(i) = (T)s; return *this; }
+    operator Vec() const { Vec r(hi - lo + 1); for (int i = lo; i <= hi; ++i) r(i - lo + 1) = v(i); return r; }
+  };
+  Sec sec(int lo, int hi) { return Sec{*this, lo, hi}; }                                                             // as the target of an assignment
+  Vec rsec(int lo, int hi) const { Vec r(hi - lo + 1); for (int i = lo; i <= hi; ++i) r(i - lo + 1) = (*this)(i); return r; }  // as a value
+};
+
+template <class T> struct Mat {  // column-major, 1-based
+  std::vector<T> d;
+  int n1 = 0, n2 = 0;
+  bool allocated = false;
+  Mat() {}
+  Mat(int a, int b) : d((size_t)a * b, T()), n1(a), n2(b), allocated(true) {}
+  T& operator()(int i, int j) { return d[(size_t)(i - 1) + (size_t)(j - 1) * n1]; }
+  const T& operator()(int i, int j) const { return d[(size_t)(i - 1) + (size_t)(j - 1) * n1]; }
+  struct Col {
+    Mat& m; int j;
+    template <class U> Col& operator=(const Vec<U>& o) { for (int i = 1; i <= m.n1; ++i) m(i, j) = (T)o(i); return *this; }
+    template <class U, class = typename std::enable_if<!is_vec<U>::value>::type> Col& operator=(const U& s) { for (int i = 1; i <= m.n1; ++i) m(i, j) = (T)s; return *this; }
+    operator Vec<T>() const { Vec<T> r(m.n1); for (int i = 1; i <= m.n1; ++i) r(i) = m(i, j); return r; }
+  };
+  Col col(int j) { return Col{*this, j}; }
+  Vec<T> rcol(int j) const { Vec<T> r(n1); for (int i = 1; i <= n1; ++i) r(i) = (*this)(i, j); return r; }
+  Vec<T> row(int i) const { Vec<T> r(n2); for (int j = 1; j <= n2; ++j) r(j) = (*this)(i, j); return r; }
+  struct Block {
+    Mat& m; int a, b, c, e;
+    Block& operator=(const Mat& o) { for (int j = c; j <= e; ++j) for (int i = a; i <= b; ++i) m(i, j) = o(i - a + 1, j - c + 1); return *this; }
+  };
+  Block block(int a, int b, int c, int e) { return Block{*this, a, b, c, e}; }
+};
+
+// ---- element-wise arithmetic
+template <class A, class B> using common_t = typename std::common_type<A, B>::type;
+#define F90_BINOP(op)                                                                                                      \
+  template <class A, class B> Vec<common_t<A, B>> operator op(const Vec<A>& a, const Vec<B>& b) {                           \
+    Vec<common_t<A, B>> r(a.size()); for (int i = 1; i <= a.size(); ++i) r(i) = (common_t<A, B>)a(i) op (common_t<A, B>)b(i); return r; } \
+  template <class A, class B, class = typename std::enable_if<!is_vec<B>::value>::type> Vec<common_t<A, B>> operator op(const Vec<A>& a, const B& b) { \
+    Vec<common_t<A, B>> r(a.size()); for (int i = 1; i <= a.size(); ++i) r(i) = (common_t<A, B>)a(i) op (common_t<A, B>)b; return r; }    \
+  template <class A, class B, class = typename std::enable_if<!is_vec<A>::value>::type> Vec<common_t<A, B>> operator op(const A& a, const Vec<B>& b) { \
+    Vec<common_t<A, B>> r(b.size()); for (int i = 1; i <= b.size(); ++i) r(i) = (common_t<A, B>)a op (common_t<A, B>)b(i); return r; }
+F90_BINOP(+) F90_BINOP(-) F90_BINOP(*) F90_BINOP(/)
+template <class A> Vec<A> operator-(const Vec<A>& a) { Vec<A> r(a.size()); for (int i = 1; i <= a.size(); ++i) r(i) = -a(i); return r; }
+
+// REAL op COMPLEX: Fortran converts the real operand to COMPLEX (x, +0.0) and performs the COMPLEX operation in full --
+// gcc's complex lowering does not shortcut an operand whose imaginary part is the constant 0.0 while signed zeros are
+// honoured (tree-complex.c, some_nonzerop) -- so the signs of zero imaginary parts, and with them the branch of a later
+// SQRT, are those of the full operation (libstdc++'s mixed operators scale or negate instead).
+inline cd operator+(double a, const cd& z) { return cd(a, 0.0) + z; }
+inline cd operator+(const cd& z, double a) { return z + cd(a, 0.0); }
+inline cd operator-(double a, const cd& z) { return cd(a, 0.0) - z; }
+inline cd operator-(const cd& z, double a) { return z - cd(a, 0.0); }
+inline cd operator*(double a, const cd& z) { return cd(a, 0.0) * z; }
+inline cd operator*(const cd& z, double a) { return z * cd(a, 0.0); }
+inline cd operator/(double a, const cd& z) { return cd(a, 0.0) / z; }
+inline cd operator/(const cd& z, double a) { return z / cd(a, 0.0); }
+inline cd operator*(const cd& a, int b) { return a * cd((double)b, 0.0); }
+inline cd operator*(int a, const cd& b) { return cd((double)a, 0.0) * b; }
+
+// ---- intrinsics
+namespace F90 {
+inline double sqrt(double x) { return ::sqrt(x); }
+inline cd sqrt(const cd& x) { return std::sqrt(x); }
+inline double abs(double x) { return ::fabs(x); }
+inline double cos(double x) { return ::cos(x); }
+inline double sin(double x) { return ::sin(x); }
+inline double acos(double x) { return ::acos(x); }
+inline double atan2(double y, double x) { return ::atan2(y, x); }
+inline double max(double a, double b) { return (b > a || a != a) ? b : a; }  // MAX(a, b) as gfortran <= 8 expands it (a decision, not a fact)
+inline double real(const cd& z) { return z.real(); }
+inline double real(double x) { return x; }
+inline double imag(const cd& z) { return z.imag(); }
+inline cd cmplx_dp(double a, double b) { return cd(a, b); }
+inline cd cmplx_sp(double a, double b) { return cd((double)(float)a, (double)(float)b); }  // CMPLX without KIND is default (single) complex
+template <class T> Vec<T> sqrt(const Vec<T>& v) { Vec<T> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = F90::sqrt(v(i)); return r; }
+inline Vec<double> abs(const Vec<double>& v) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = ::fabs(v(i)); return r; }
+inline Vec<double> real(const Vec<cd>& v) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = v(i).real(); return r; }
+inline Vec<double> real(const Vec<double>& v) { return v; }
+inline Vec<double> imag(const Vec<cd>& v) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = v(i).imag(); return r; }
+template <class T> T sum(const Vec<T>& v) { T s = T(); for (int i = 1; i <= v.size(); ++i) s = s + v(i); return s; }
+inline double dot_product(const Vec<double>& a, const Vec<double>& b) { double s = 0.0; for (int i = 1; i <= a.size(); ++i) s = s + a(i) * b(i); return s; }
+inline cd dot_product(const Vec<cd>& a, const Vec<cd>& b) { cd s(0.0, 0.0); for (int i = 1; i <= a.size(); ++i) s = s + std::conj(a(i)) * b(i); return s; }
+inline double maxval(const Vec<double>& v) { double m = v(1); for (int i = 2; i <= v.size(); ++i) if (v(i) > m) m = v(i); return m; }
+inline double minval(const Vec<double>& v) { double m = v(1); for (int i = 2; i <= v.size(); ++i) if (v(i) < m) m = v(i); return m; }
+inline Vec<double> cos(const Vec<double>& v) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = ::cos(v(i)); return r; }
+inline Vec<double> sin(const Vec<double>& v) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = ::sin(v(i)); return r; }
+inline Mat<double> reshape(const Vec<double>& v, int a, int b) { Mat<double> m(a, b); for (int i = 0; i < a * b; ++i) m.d[(size_t)i] = v.d[(size_t)i]; return m; }
+inline Mat<double> transpose(const Mat<double>& m) { Mat<double> t(m.n2, m.n1); for (int i = 1; i <= m.n1; ++i) for (int j = 1; j <= m.n2; ++j) t(j, i) = m(i, j); return t; }
+// MATMUL(matrix, vector) as gfortran inlines it: c = 0; do j; do i; c(i) = c(i) + a(i,j) * b(j)
+inline Vec<double> matmul(const Mat<double>& a, const Vec<double>& b) {
+  Vec<double> c(a.n1);
+  for (int j = 1; j <= a.n2; ++j) for (int i = 1; i <= a.n1; ++i) c(i) = c(i) + a(i, j) * b(j);
+  return c;
+}
+template <class T> int size(const Vec<T>& v) { return v.size(); }
+template <class T> int size(const Mat<T>& m, int dim) { return dim == 1 ? m.n1 : m.n2; }
+template <class T> bool allocated(const Vec<T>& v) { return v.allocated; }
+}  // namespace F90
+
+// array constructor (/ a, b, c /) of scalars and arrays
+inline void F_cat_into(Vec<double>&) {}
+template <class... R> void F_cat_into(Vec<double>& out, double a, const R&... r);
+template <class... R> void F_cat_into(Vec<double>& out, const Vec<double>& a, const R&... r) { for (int i = 1; i <= a.size(); ++i) out.d.push_back(a(i)); F_cat_into(out, r...); }
+template <class... R> void F_cat_into(Vec<double>& out, double a, const R&... r) { out.d.push_back(a); F_cat_into(out, r...); }
+template <class... A> Vec<double> F_cat(const A&... a) { Vec<double> out; out.allocated = true; F_cat_into(out, a...); return out; }
+
+template <int N, class T> T F_powc(const T& x) {
+  constexpr int tbl[9] = {0, 1, 1, 2, 2, 3, 3, 4, 4};
+  static_assert(N >= 1 && N <= 8, "exponent");
+  if constexpr (N == 1) return x;
+  else return F_powc<N - tbl[N]>(x) * F_powc<tbl[N]>(x);
+}
+inline double F_pow(double x, double y) { return ::pow(x, y); }
+inline Vec<double> F_pow(const Vec<double>& v, double y) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = ::pow(v(i), y); return r; }
+inline double F_toreal(double x) { return x; }
+inline double F_toreal(const cd& z) { return z.real(); }  // COMPLEX assigned to REAL: the real part
+inline Vec<cd> F_tocplx(const Vec<cd>& v) { return v; }
+inline Vec<cd> F_tocplx(const Vec<double>& v) { Vec<cd> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = cd(v(i), 0.0); return r; }
+template <class T> T& F_tmp(T&& v) { return v; }
+template <class T> T& F_tmp(T& v) { return v; }
+template <class T> void F_move_alloc(T& from, T& to) { to = from; to.allocated = true; from = T(); }

@@ -705,7 +705,11 @@ SRT_HDN void srt_ray_init(SrtModelRef MR, const SrtRunParams& P, const double po
 #pragma unroll
   for (int i = 0; i < 3; ++i) st.x[i] = pos0[i];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) st.k[i] = k0.re * dir0[i];
+  // real(k0mag*dir0), raytracer.f95:691: COMPLEX * REAL is the full complex product with dir0 as (d, +0.0) (gcc does not shortcut
+  // an operand whose imaginary part is the constant 0.0 while signed zeros are honoured), so the real part carries -im*0.0:
+  // only the sign of a zero (evanescent start: k0 purely imaginary) or a NaN imaginary part can show.  Found by the
+  // comparison with the reference's translated source (tests/test_raytracer_ref_cpu.py).
+  for (int i = 0; i < 3; ++i) st.k[i] = k0.re * dir0[i] - k0.im * 0.0;
   st.w = w0;
   st.dt = P.dt0;
   st.t = 0.0;

@@ -1,0 +1,145 @@
+"""The integrator itself (dispersion relation, Stix parameters, the three gradients, evalrhs, root
+solve, stop conditions, rk4 / rk45, raytracer_run with its step-size control, cone refinement and first-step quirk) against
+the REFERENCE'S OWN SOURCE: fortran/raytracer.f95 (+ util.f95, bmodel_dipole.f95, constants.f95) translated at build time
+by oracle/f90_to_cpp.py over oracle/ref_stubs/f90rt.h into oracle/_ref/librt_ref.so (no Fortran compiler here).
+
+The translation is syntactic; what a compiler decides about array expressions is stated in f90rt.h (element order of SUM and
+DOT_PRODUCT, MAX with a NaN argument, CMPLX without KIND, COMPLEX arithmetic by the Fortran rules).  Two things are hooks:
+funcPlasmaParams (the oracle's adapter: its parts are pinned by test_ngo_ref_cpu / test_geopack_ref_cpu / test_xform_ref_cpu /
+test_ts05_cpu) and csvd (LAPACK zgesvd in the reference; the oracle's stand-in, see test_hostemu_cpu's handedness tests).
+The oracle built on glibc's libm must reproduce the translated reference BIT FOR BIT: every row of every ray."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import common
+import oracle_lib as ol
+
+GRID13 = os.path.join(common.ROOT, "tests", "golden", "grid13.txt")
+
+
+@pytest.fixture(scope="module")
+def ref():
+    path = os.path.join(ol.ORC_DIR, "_ref", "librt_ref.so")
+    if not os.path.exists(path):
+        ol.ts05_ref(True)  # runs `make ref` where the reference sources exist
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/librt_ref.so not built (reference sources absent)")
+    R = C.CDLL(path)
+    d, i, l, vp = C.c_double, C.c_int, C.c_long, C.c_void_p
+    R.rt_ref_set_hooks.argtypes = [vp, vp]
+    R.rt_ref_constant.restype = d
+    R.rt_ref_evalrhs.argtypes = [vp, d, vp]
+    R.rt_ref_solve.argtypes = [vp, d, vp, vp]
+    R.rt_ref_bmodel_cartesian.argtypes = [vp, vp]
+    R.rt_ref_cartesian_to_spherical.argtypes = [vp, vp]
+    R.rt_ref_run.restype = l
+    R.rt_ref_run.argtypes = [vp, vp, d, d, d, d, i, d, i, d, i, d, vp, l, vp]
+    return R
+
+
+def hook(R, o):
+    L = o.L
+    L.orc_hook_model.argtypes = [C.c_void_p]
+    L.orc_hook_model(o.h)
+    R.rt_ref_set_hooks(C.cast(L.orc_hook_plasma, C.c_void_p), C.cast(L.orc_hook_csvd, C.c_void_p))
+
+
+def ref_run(R, o, pos0, dir0, w0, p):
+    rows = np.zeros((p["maxsteps"] + 2, 20))
+    sc, d0 = C.c_int(), np.array(dir0, dtype=np.float64)
+    n = R.rt_ref_run(np.ascontiguousarray(pos0, dtype=np.float64).ctypes.data, d0.ctypes.data, w0, p["dt0"], p["dtmax"], p["maxerr"], p["maxsteps"], p["minalt"],
+                     p["root"], p["tmax"], p["fixedstep"], o.del_, rows.ctypes.data, len(rows), C.byref(sc))
+    return rows[:n], sc.value, d0
+
+
+def assert_same(R, o, pos0, dir0, w0, p, what):
+    t = o.trace(pos0, dir0, w0, **p)
+    rows, sc, d0 = ref_run(R, o, pos0, dir0, w0, p)
+    assert len(rows) == len(t["rows"]) and sc == t["stopcond"], (what, len(rows), len(t["rows"]), sc, t["stopcond"])
+    assert np.array_equal(rows.view(np.uint64), t["rows"].view(np.uint64)), what
+    assert np.array_equal(d0, t["dir0"]), what
+    return t
+
+
+def test_constants_and_pointwise_functions(ref):
+    o = ol.OracleModel("ngo", common.NGO_CFG, libm=True)
+    hook(ref, o)
+    c = [ref.rt_ref_constant(i) for i in range(6)]
+    assert c[3] == np.sqrt(1.0 / c[0] / c[2]) and c[4] == 6371.2e3
+    rng = np.random.default_rng(2)
+    pos0, _, w0 = common.c2_grid(5, 5)
+    a, b, k4a, k4b = np.zeros(7), np.zeros(7), np.zeros(4), np.zeros(4)
+    for r in range(len(w0)):
+        x = np.ascontiguousarray(pos0[r] * rng.uniform(1.0, 3.0))
+        kdir = rng.normal(size=3)
+        kdir /= np.linalg.norm(kdir)
+        o.L.orc_solve(o.h, kdir.ctypes.data, w0[r], x.ctypes.data, k4a.ctypes.data)
+        ref.rt_ref_solve(kdir.ctypes.data, w0[r], x.ctypes.data, k4b.ctypes.data)
+        assert np.array_equal(k4a.view(np.uint64), k4b.view(np.uint64))
+        args = np.array(list(x) + list(kdir * k4a[2]) + [w0[r]])
+        o.L.orc_evalrhs(o.h, args.ctypes.data, a.ctypes.data)
+        ref.rt_ref_evalrhs(args.ctypes.data, o.del_, b.ctypes.data)
+        assert np.array_equal(a.view(np.uint64), b.view(np.uint64))
+
+
+def test_dipole_field_of_the_adapter(ref):
+    """bmodel_cartesian (bmodel_dipole.f95) + util.f95's coordinate helpers: the oracle's field block with use_igrf = 0 at a time
+    when the tilt chain is exercised too (adapter: dipole in SM -> GSM -> real*4 nT -> SM)"""
+    o = ol.OracleModel("ngo", common.NGO_CFG, 2010001, 0, 0, libm=True)
+    rng = np.random.default_rng(3)
+    b = np.zeros(3)
+    for _ in range(300):
+        x = rng.uniform(-4e7, 4e7, 3)
+        ref.rt_ref_bmodel_cartesian(x.ctypes.data, b.ctypes.data)
+        got = o.plasma(x)[0][16:19]
+        # the adapter rounds the field to real*4 nanotesla on the way (Q3): 6e-8 relative
+        assert np.abs(got - b).max() <= 2e-7 * np.linalg.norm(b)
+
+
+@pytest.mark.parametrize("use_igrf", [0, 1])
+def test_whole_rays_ngo(ref, use_igrf):
+    o = ol.OracleModel("ngo", common.NGO_CFG, 2010001, 3600000, use_igrf, libm=True)
+    hook(ref, o)
+    pos0, dir0, w0 = common.c2_grid(5, 5)
+    stops = set()
+    for r in range(len(w0)):
+        t = assert_same(ref, o, pos0[r], [0, 0, 0], w0[r], dict(common.C2, maxsteps=500), "adaptive ray %d" % r)
+        stops.add(t["stopcond"])
+        if r % 4 == 0:
+            assert_same(ref, o, pos0[r], [0, 0, 0], w0[r], dict(common.C1, maxsteps=150), "fixed-step ray %d" % r)
+    assert len(stops) >= 2
+
+
+def test_cone_refinement_before_the_first_acceptance_and_explicit_directions(ref):
+    o = ol.OracleModel("ngo", common.NGO_CFG, libm=True)
+    hook(ref, o)
+    pos, dirs, ws, dts = common.cone_first_rays(o)
+    ncone = 0
+    for p0, d0, w, dt0 in zip(pos, dirs, ws, dts):
+        t = assert_same(ref, o, p0, d0, w, dict(common.C2, dt0=dt0, maxsteps=120), "cone-first ray")
+        ncone += t["ncone"]
+        assert_same(ref, o, p0, d0, w, dict(common.C2, dt0=dt0, maxsteps=60, root=1), "root 1")
+    assert ncone > 0
+
+
+def test_whole_rays_gridded_model(ref):
+    o = ol.OracleModel("grid", GRID13, 2010001, 0, 1, libm=True)
+    hook(ref, o)
+    pos0, dir0, w0 = common.launch_grid([1000.0, 6000.0], [25.0, 45.0])
+    for r in range(len(w0)):
+        assert_same(ref, o, pos0[r], [0, 0, 0], w0[r], dict(common.C2, maxsteps=200), "grid ray %d" % r)
+
+
+def test_rays_with_ducts_and_the_external_field(ref):
+    o = ol.OracleModel("ngo", os.path.join(common.ROOT, "tests", "data", "newray_ducts_sin_gauss.in"), libm=True)
+    hook(ref, o)
+    pos0, dir0, w0 = common.launch_grid([2000.0], [30.0, 50.0])
+    for r in range(len(w0)):
+        assert_same(ref, o, pos0[r], [0, 0, 0], w0[r], dict(common.C2, maxsteps=200), "ducted ray %d" % r)
+    if ol.ts05_ref(False) is not None:
+        o2 = ol.OracleModel("ngo", common.NGO_CFG, libm=True).tsyganenko([3.0, -45.0, 2.5, -4.0, 0.4, 0.7, 0.3, 0.9, 0.6, 1.1], srt_math=False)
+        hook(ref, o2)
+        assert_same(ref, o2, pos0[0], [0, 0, 0], w0[0], dict(common.C2, maxsteps=80), "TS05 ray")
