@@ -18,11 +18,13 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 from f77_to_cpp import read_statements_free, split_top, top_level_eq  # noqa: E402
 
+HOOK_SUBS = {"SM_TO_GSM_D": "RT_sm_to_gsm", "GSM_TO_SM_D": "RT_gsm_to_sm", "TSY_RECALC": "RT_tsy_recalc", "IGRF_GSM": "RT_igrf_gsm",
+             "T04_S": "RT_t04_s", "DENS": "RT_dens"}
 DUMMY_PROCS = {"FUNCPLASMAPARAMS", "FUNCPLASMAPARAMSDATA", "FUNCSTOPCONDITIONS"}
-KEEP_UNITS = {"DISPERSION_RELATION", "STIX_PARAMETERS", "DISPERSION_RELATION_DFDK", "DISPERSION_RELATION_DFDW", "DISPERSION_RELATION_DFDX",
+KEEP_UNITS = {"FUNCPLASMAPARAMS", "DISPERSION_RELATION", "STIX_PARAMETERS", "DISPERSION_RELATION_DFDK", "DISPERSION_RELATION_DFDW", "DISPERSION_RELATION_DFDX",
               "RAYTRACER_EVALRHS", "RAYTRACER_STOPCONDITIONS", "FORM_DISPERSION_MATRIX", "IS_RIGHT_HANDED", "SOLVE_DISPERSION_RELATION", "RK4",
               "RK45", "RAYTRACER_RUN", "CARTESIAN_TO_SPHERICAL", "SPHERICAL_TO_CARTESIAN_VEC", "CARTESIAN_TO_SPHERICAL_VEC", "BMODEL_CARTESIAN", "BMODEL"}
-INTRINSICS = {"SQRT", "ABS", "COS", "SIN", "ACOS", "ATAN2", "MAX", "SUM", "DOT_PRODUCT", "MAXVAL", "MINVAL", "ALLOCATED", "MATMUL", "TRANSPOSE", "EXP"}
+INTRINSICS = {"MOD", "SQRT", "ABS", "COS", "SIN", "ACOS", "ATAN2", "MAX", "SUM", "DOT_PRODUCT", "MAXVAL", "MINVAL", "ALLOCATED", "MATMUL", "TRANSPOSE", "EXP"}
 CTYPE = {"REAL(KIND=DP)": "double", "REAL(KIND=SP)": "float", "COMPLEX(KIND=DP)": "cd", "INTEGER": "int", "LOGICAL": "bool", "CHARACTER": "char"}
 
 TOKEN = re.compile(r"(\.(?:LT|GT|LE|GE|EQ|NE|AND|OR|NOT|TRUE|FALSE)\.)|(\*\*|\(/|/\)|==|/=|>=|<=|[<>])|([A-Z][A-Z0-9_]*)|([(),+\-*/=:])")
@@ -264,10 +266,11 @@ class Expr:
             return self.array_ref(name, self.u.syms[name])
         if name == "REAL":
             e = self.expr()
+            dp = False
             if self.peek() == ",":
-                self.take(); self.take("KIND"); self.take("="); self.take()
+                self.take(); self.take("KIND"); self.take("="); self.take(); dp = True
             self.take(")")
-            return "F90::real(%s)" % e
+            return "F90::%s(%s)" % ("real" if dp else "real_default", e)
         if name == "CMPLX":
             a = self.expr(); self.take(","); b = self.expr()
             dp = False
@@ -316,7 +319,7 @@ def tr(text, unit, scope, units):
 HEAD = re.compile(r"^(SUBROUTINE|FUNCTION)([A-Z][A-Z0-9_]*)\((.*)\)$")
 
 
-def parse_decl(s, syms):
+def parse_decl(s, syms, prefix=""):
     spec, rest = s.split("::", 1)
     parts = split_top(spec)
     base = parts[0]
@@ -330,14 +333,22 @@ def parse_decl(s, syms):
             item, init = item[:k], item[k + 1:]
         m = re.fullmatch(r"([A-Z][A-Z0-9_]*)(?:\((.+)\))?", item)
         dims = split_top(m.group(2)) if m.group(2) else []
-        syms[m.group(1)] = Sym(CTYPE[base], len(dims), dims, "ALLOCATABLE" in attrs, init if "PARAMETER" in attrs else None)
+        syms[prefix + m.group(1)] = Sym(CTYPE[base], len(dims), dims, "ALLOCATABLE" in attrs, init if "PARAMETER" in attrs else None)
 
 
 def parse(stmts):
     """-> (module-level symbols, units)"""
-    glob, units, cur, skip = {}, {}, None, False
+    glob, units, cur, skip, prefix = {}, {}, None, False, ""
     for lab, s in stmts:
-        s = s.rstrip(";")
+        s = s.rstrip(";").replace("DATAP%P%", "NGO_")
+        if s.startswith("TYPE::"):  # components of the adapter's state type become module variables NGO_<component>
+            prefix = "NGO_" if s == "TYPE::NGOSTATEDATA" else "SKIP_"
+            continue
+        if s.startswith("ENDTYPE"):
+            prefix = ""
+            continue
+        if s.startswith("COMMON/") or (s.startswith("TYPE(") and cur is None):
+            continue
         if s.startswith("INTERFACE"):
             skip = True
             continue
@@ -358,7 +369,7 @@ def parse(stmts):
             cur = None
             continue
         if "::" in s and (s.split("::")[0].split(",")[0] in CTYPE):
-            parse_decl(s, glob if cur is None else cur.syms)
+            parse_decl(s, glob if cur is None else cur.syms, prefix if cur is None else "")
             continue
         if cur is not None:
             cur.body.append(s)
@@ -417,7 +428,13 @@ def statement(s, unit, scope, units):
     m = re.fullmatch(r"CALLMOVE_ALLOC\(([A-Z0-9_]+),([A-Z0-9_]+)\)", s)
     if m:
         return ["F_move_alloc(v_%s, v_%s);" % (m.group(1), m.group(2))]
+    if s == "CALLDENS":
+        return ["RT_dens();"]
+    if s.startswith("TYPE(") or s.startswith("DATAP=") or s.startswith("COMMON/"):
+        return []
     m = re.fullmatch(r"CALL([A-Z][A-Z0-9_]*)\((.*)\)", s)
+    if m and m.group(1) in HOOK_SUBS:
+        return ["%s(%s);" % (HOOK_SUBS[m.group(1)], ", ".join(tr(a, unit, scope, units) for a in split_top(m.group(2))))]
     if m:
         name = m.group(1)
         p = Expr(tokenize("(" + m.group(2) + ")"), unit, scope, units)
@@ -456,6 +473,9 @@ def emit(glob, units):
     consts = []
     for name, sym in glob.items():  # named constants of the modules, in source order
         if sym.param is None:
+            if name not in ("SP", "DP"):
+                dims = ", ".join(sym.dims or [])
+                consts.append("static thread_local %s v_%s%s;" % (sym.cpp(), name, "(%s)" % dims if sym.rank else " = 0"))
             continue
         dummy = Unit("MODULE", "", [])
         consts.append("static const %s v_%s = %s;" % (sym.cpp(), name, tr(sym.param, dummy, glob, units)))
@@ -485,6 +505,33 @@ def emit(glob, units):
 
 
 WRAPPERS = r"""
+// ---- the Ngo adapter (fortran/ngo_dens_model_adapter.f95:63-207) calls into the FORTRAN 77 libraries of the reference; those are
+// translated into their own shared objects (libngo_ref, libxform_ref, libgeopack_ref, libts05_ref): the harness hands in their entry points
+typedef void (*xform_fn)(int, int, const double*, double*);
+typedef void (*recalc_fn)(int, int, int, int, int, float*, float*);
+typedef void (*igrf_fn)(float, float, float, float*);
+typedef void (*t04_fn)(const float*, float, float, float, float, float*);
+typedef void (*dens_fn)(double, double, double, double*);
+static thread_local xform_fn g_sm2gsm = nullptr, g_gsm2sm = nullptr;
+static thread_local recalc_fn g_recalc = nullptr;
+static thread_local igrf_fn g_igrf = nullptr;
+static thread_local t04_fn g_t04 = nullptr;
+static thread_local dens_fn g_dens = nullptr;
+#if defined(RT_HAVE_NGO_ADAPTER)
+static void RT_sm_to_gsm(const Vec<int>& itime, const Vec<double>& x, Vec<double>& out) { g_sm2gsm(itime(1), itime(2), x.d.data(), out.d.data()); }
+static void RT_gsm_to_sm(const Vec<int>& itime, const Vec<double>& x, Vec<double>& out) { g_gsm2sm(itime(1), itime(2), x.d.data(), out.d.data()); }
+static void RT_tsy_recalc(int year, int day, int hour, int min, int sec) {
+  float g1[34], g2[315];
+  g_recalc(year, day, hour, min, sec, g1, g2);
+  v_PSI = g1[0];  // `real(kind=SP) :: PSI; COMMON /GEOPACK1/ PSI`: word 1 of the block
+}
+static void RT_igrf_gsm(float x, float y, float z, float& bx, float& by, float& bz) { float b[3]; g_igrf(x, y, z, b); bx = b[0]; by = b[1]; bz = b[2]; }
+static void RT_t04_s(int iopt, const Vec<float>& parmod, float ps, float x, float y, float z, float& bx, float& by, float& bz) {
+  float b[3]; (void)iopt; g_t04(parmod.d.data(), ps, x, y, z, b); bx = b[0]; by = b[1]; bz = b[2];
+}
+static void RT_dens() { double a[4]; g_dens(v_Z(1), v_Z(2), v_LATITU, a); for (int i = 1; i <= 4; ++i) v_ANI(i) = a[i - 1]; }
+#endif
+
 // ---- hooks of the test harness and C entry points (ctypes)
 typedef void (*plasma_cb_t)(const double* x, double* qs, double* Ns, double* ms, double* nus, double* B0, int* nspec);
 typedef void (*csvd_cb_t)(const double* m_re_im /*[3][3][2] column-major*/, double* vt_re_im /*[3][3][2]*/);
@@ -569,6 +616,35 @@ long rt_ref_run(const double* pos0, double* dir0, double w0, double dt0, double 
   }
   return nr;
 }
+#if defined(RT_HAVE_NGO_ADAPTER)
+// funcPlasmaParams of the Ngo adapter, translated: state = the adapter's ngoStateData, r0 = module ngo_dens_model's R0 after readinput
+void rt_ref_ngo_adapter(void* sm2gsm, void* gsm2sm, void* recalc, void* igrf, void* t04, void* dens, double r0, int yearday, int msec, int use_igrf,
+                        int use_tsyganenko, const double* parmod) {
+  g_sm2gsm = (xform_fn)sm2gsm; g_gsm2sm = (xform_fn)gsm2sm; g_recalc = (recalc_fn)recalc; g_igrf = (igrf_fn)igrf; g_t04 = (t04_fn)t04; g_dens = (dens_fn)dens;
+  v_R0 = r0; v_NGO_ITIME(1) = yearday; v_NGO_ITIME(2) = msec; v_NGO_USE_IGRF = use_igrf; v_NGO_USE_TSYGANENKO = use_tsyganenko;
+  v_NGO_PDYN = parmod[0]; v_NGO_DST = parmod[1]; v_NGO_BYIMF = parmod[2]; v_NGO_BZIMF = parmod[3];
+  v_NGO_W1 = parmod[4]; v_NGO_W2 = parmod[5]; v_NGO_W3 = parmod[6]; v_NGO_W4 = parmod[7]; v_NGO_W5 = parmod[8]; v_NGO_W6 = parmod[9];
+}
+static void ngo_adapter_cb(const double* x, double* qs, double* Ns, double* ms, double* nus, double* B0, int* nspec) {
+  Vec<double> vx(3), q, n, m, nu, b(3);
+  for (int i = 1; i <= 3; ++i) vx(i) = x[i - 1];
+  f_FUNCPLASMAPARAMS(vx, q, n, m, nu, b);
+  *nspec = q.size();
+  for (int i = 1; i <= q.size(); ++i) { qs[i - 1] = q(i); Ns[i - 1] = n(i); ms[i - 1] = m(i); nus[i - 1] = nu(i); }
+  for (int i = 1; i <= 3; ++i) B0[i - 1] = b(i);
+}
+// funcPlasmaParams of raytracer_run and friends = the translated adapter (csvd stays the hook given)
+void rt_ref_use_ngo_adapter(csvd_cb_t c) { g_plasma = ngo_adapter_cb; g_csvd = c; }
+void rt_ref_ngo_plasma(long n, const double* x, double* out /*[n][19]*/) {
+  for (long i = 0; i < n; ++i) {
+    double qs[8], Ns[8], ms[8], nus[8], b[3]; int ns = 0;
+    ngo_adapter_cb(x + 3 * i, qs, Ns, ms, nus, b, &ns);
+    double* o = out + 19 * i;
+    for (int s = 0; s < 4; ++s) { o[s] = qs[s]; o[4 + s] = Ns[s]; o[8 + s] = ms[s]; o[12 + s] = nus[s]; }
+    for (int c = 0; c < 3; ++c) o[16 + c] = b[c];
+  }
+}
+#endif
 }
 """
 
@@ -578,9 +654,15 @@ def main(dst, srcs):
     for one in srcs:
         stmts += read_statements_free(one)
     glob, units = parse(stmts)
+    glob = {k: v for k, v in glob.items() if not k.startswith("SKIP_")}
+    if "FUNCPLASMAPARAMS" in units:  # `use ngo_dens_model, only : readinput, dens, ani, z, L, R0, latitu`
+        for name, sym in (("Z", Sym("double", 1, ["5"])), ("ANI", Sym("double", 1, ["4"])), ("L", Sym("double")), ("R0", Sym("double")), ("LATITU", Sym("double"))):
+            glob.setdefault(name, sym)
     consts, protos, texts = emit(glob, units)
     with open(dst, "w") as f:
         f.write("// GENERATED by oracle/f90_to_cpp.py from the reference's Fortran 90 at build time -- never committed.\n#include \"f90rt.h\"\n")
+        if "FUNCPLASMAPARAMS" in units:
+            f.write("#define RT_HAVE_NGO_ADAPTER 1\n")
         f.write("\n".join(consts) + "\n" + WRAPPERS + "\n" + "\n".join(protos) + "\n\n" + "\n".join(texts) + ENTRY)
 
 

@@ -7,15 +7,15 @@
 //
 // PARITY: the reference ships no golden vectors for this path and no Fortran compiler
 // exists in this environment.
-//   PINNED by the reference's own source, bit for bit: the parts the reference writes in
-//   FORTRAN 77 style -- ngo_dens_model.f95 (readinput, dens), geopack2008.for (RECALC_08,
-//   SUN_08, IGRF_GSW_08, GEOGSW_08), xform_double/ (SM <-> GSM), TS05_aka_TS04.for -- are
-//   translated statement by statement at build time (f77_to_cpp.py -> _ref/*.so) and the
-//   restatements here are compared with them (tests/test_*_ref_cpu.py, test_ts05_cpu.py).
-//   PARITY UNPINNED for the Fortran 90 part (orc_raytracer.h, the adapters' glue, dipole,
-//   coordinate helpers, orc_grid.h): pinned only by reference-independent identities
-//   (tests/test_oracle_*.py) and by the reference's MATLAB prototypes at 1e-6 / 1e-9
-//   (tests/test_matlab_second_statement.py), not by reference outputs.
+//   PINNED by the reference's own source, bit for bit -- the whole Ngo path (configs 1, 2, 4):
+//   the reference's sources are translated at build time (f77_to_cpp.py for the FORTRAN 77-style
+//   files, f90_to_cpp.py over ref_stubs/f90rt.h for raytracer.f95, the Ngo adapter, util.f95,
+//   bmodel_dipole.f95, constants.f95 -> _ref/*.so) and the restatements here are compared with
+//   them, down to whole rays through the translated raytracer_run (tests/test_*_ref_cpu.py,
+//   test_ts05_cpu.py).  f90rt.h states the array semantics a compiler would decide.
+//   PARITY UNPINNED: orc_grid.h (interp adapter, libtricubic: outside the translators'
+//   subset) and the stand-in for LAPACK's zgesvd (is_right_handed): pinned only by
+//   reference-independent identities (tests/test_oracle_*.py), not by reference outputs.
 //
 // Elementary functions: by default the oracle uses the same srt_math.h layer
 // as the device (so GPU == oracle is a bitwise statement).  Compile with

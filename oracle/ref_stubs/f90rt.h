@@ -108,6 +108,12 @@ inline double atan2(double y, double x) { return ::atan2(y, x); }
 inline double max(double a, double b) { return (b > a || a != a) ? b : a; }  // MAX(a, b) as gfortran <= 8 expands it (a decision, not a fact)
 inline double real(const cd& z) { return z.real(); }
 inline double real(double x) { return x; }
+inline double real(float x) { return (double)x; }
+// REAL(x) without KIND: default REAL of a real argument, the real part (same kind) of a COMPLEX one
+inline float real_default(double x) { return (float)x; }
+inline float real_default(float x) { return x; }
+inline double real_default(const cd& z) { return z.real(); }
+inline int mod(int a, int p) { return a % p; }
 inline double imag(const cd& z) { return z.imag(); }
 inline cd cmplx_dp(double a, double b) { return cd(a, b); }
 inline cd cmplx_sp(double a, double b) { return cd((double)(float)a, (double)(float)b); }  // CMPLX without KIND is default (single) complex
@@ -115,6 +121,8 @@ template <class T> Vec<T> sqrt(const Vec<T>& v) { Vec<T> r(v.size()); for (int i
 inline Vec<double> abs(const Vec<double>& v) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = ::fabs(v(i)); return r; }
 inline Vec<double> real(const Vec<cd>& v) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = v(i).real(); return r; }
 inline Vec<double> real(const Vec<double>& v) { return v; }
+inline Vec<double> real_default(const Vec<cd>& v) { return real(v); }
+inline Vec<float> real_default(const Vec<double>& v) { Vec<float> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = (float)v(i); return r; }
 inline Vec<double> imag(const Vec<cd>& v) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = v(i).imag(); return r; }
 template <class T> T sum(const Vec<T>& v) { T s = T(); for (int i = 1; i <= v.size(); ++i) s = s + v(i); return s; }
 inline double dot_product(const Vec<double>& a, const Vec<double>& b) { double s = 0.0; for (int i = 1; i <= a.size(); ++i) s = s + a(i) * b(i); return s; }

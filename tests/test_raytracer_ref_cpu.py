@@ -143,3 +143,62 @@ def test_rays_with_ducts_and_the_external_field(ref):
         o2 = ol.OracleModel("ngo", common.NGO_CFG, libm=True).tsyganenko([3.0, -45.0, 2.5, -4.0, 0.4, 0.7, 0.3, 0.9, 0.6, 1.1], srt_math=False)
         hook(ref, o2)
         assert_same(ref, o2, pos0[0], [0, 0, 0], w0[0], dict(common.C2, maxsteps=80), "TS05 ray")
+
+
+# ---------------------------------------------------------------- the whole Ngo path from the reference's translated sources
+PARMOD = np.array([3.0, -45.0, 2.5, -4.0, 0.4, 0.7, 0.3, 0.9, 0.6, 1.1])
+
+
+def full_chain(R, cfg, yearday, msec, use_igrf, use_tsy):
+    """funcPlasmaParams = the reference's Ngo adapter (ngo_dens_model_adapter.f95, translated in librt_ref) over the reference's
+    ngo_dens_model.f95, xform_double, geopack2008.for and TS05 (each translated into its own library): nothing of the oracle but
+    the stand-in for LAPACK's zgesvd is involved."""
+    ref_dir = os.path.join(ol.ORC_DIR, "_ref")
+    N, X, G, T = (C.CDLL(os.path.join(ref_dir, n)) for n in ("libngo_ref.so", "libxform_ref.so", "libgeopack_ref.so", "libts05_ref.so"))
+    vp, d, i = C.c_void_p, C.c_double, C.c_int
+    N.ngo_ref_readinput.argtypes = [C.c_char_p]
+    N.ngo_ref_state.argtypes = [vp]
+    R.rt_ref_ngo_adapter.argtypes = [vp] * 6 + [d, i, i, i, i, vp]
+    R.rt_ref_ngo_plasma.argtypes = [C.c_long, vp, vp]
+    R.rt_ref_use_ngo_adapter.argtypes = [vp]
+    assert N.ngo_ref_readinput(cfg.encode()) == 0
+    st = np.zeros(12)
+    N.ngo_ref_state(st.ctypes.data)
+    fp = lambda f: C.cast(f, vp)  # noqa: E731
+    R.rt_ref_ngo_adapter(fp(X.xform_ref_sm_to_gsm), fp(X.xform_ref_gsm_to_sm), fp(G.geopack_ref_recalc), fp(G.geopack_ref_igrf_gsw), fp(T.ts05_ref_t04_s),
+                         fp(N.ngo_ref_dens), st[2], yearday, msec, use_igrf, use_tsy, PARMOD.ctypes.data)
+    return (N, X, G, T)  # keep the libraries alive
+
+
+@pytest.mark.parametrize("use_igrf,use_tsy", [(0, 0), (1, 0), (0, 1), (1, 1)])
+@pytest.mark.parametrize("cfg", [common.NGO_CFG, os.path.join(common.ROOT, "tests", "data", "newray_ducts_sin_gauss.in")], ids=["default", "ducts"])
+def test_ngo_adapter_from_the_translated_sources(ref, cfg, use_igrf, use_tsy):
+    keep = full_chain(ref, cfg, 2010001, 3600000, use_igrf, use_tsy)
+    o = ol.OracleModel("ngo", cfg, 2010001, 3600000, use_igrf, libm=True)
+    if use_tsy:
+        o.tsyganenko(PARMOD, srt_math=False)
+    rng = np.random.default_rng(4)
+    r = ol.R_E * rng.uniform(1.1, 7.0, 400)
+    th, ph = rng.uniform(0.2, np.pi - 0.2, 400), rng.uniform(-np.pi, np.pi, 400)
+    x = np.ascontiguousarray(np.stack([r * np.sin(th) * np.cos(ph), r * np.sin(th) * np.sin(ph), r * np.cos(th)], axis=1))
+    out = np.zeros((len(x), 19))
+    ref.rt_ref_ngo_plasma(len(x), x.ctypes.data, out.ctypes.data)
+    assert np.array_equal(o.plasma(x).view(np.uint64), out.view(np.uint64))
+    del keep
+
+
+@pytest.mark.parametrize("use_igrf,use_tsy", [(0, 0), (1, 0), (0, 1)])
+def test_whole_rays_from_the_translated_sources_only(ref, use_igrf, use_tsy):
+    """configs 1 and 2 (and the IGRF / TS05 variants), ray for ray: translated driver loop + integrator + adapter + density model +
+    coordinate chain + Geopack (+ TS05) against the oracle, every row bit for bit"""
+    keep = full_chain(ref, common.NGO_CFG, 2010001, 0, use_igrf, use_tsy)
+    o = ol.OracleModel("ngo", common.NGO_CFG, 2010001, 0, use_igrf, libm=True)
+    if use_tsy:
+        o.tsyganenko(PARMOD, srt_math=False)
+    ref.rt_ref_use_ngo_adapter(C.cast(o.L.orc_hook_csvd, C.c_void_p))
+    pos0, dir0, w0 = common.c2_grid(3, 4)
+    nsteps = 80 if use_tsy else 400
+    for r in range(len(w0)):
+        assert_same(ref, o, pos0[r], [0, 0, 0], w0[r], dict(common.C2, maxsteps=nsteps), "adaptive ray %d" % r)
+    assert_same(ref, o, pos0[5], [0, 0, 0], w0[5], dict(common.C1, maxsteps=100), "config-1 ray")
+    del keep
