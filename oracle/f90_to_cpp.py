@@ -23,9 +23,9 @@ HOOK_SUBS = {"SM_TO_GSM_D": "RT_sm_to_gsm", "GSM_TO_SM_D": "RT_gsm_to_sm", "TSY_
 DUMMY_PROCS = {"FUNCPLASMAPARAMS", "FUNCPLASMAPARAMSDATA", "FUNCSTOPCONDITIONS"}
 KEEP_UNITS = {"FUNCPLASMAPARAMS", "DISPERSION_RELATION", "STIX_PARAMETERS", "DISPERSION_RELATION_DFDK", "DISPERSION_RELATION_DFDW", "DISPERSION_RELATION_DFDX",
               "RAYTRACER_EVALRHS", "RAYTRACER_STOPCONDITIONS", "FORM_DISPERSION_MATRIX", "IS_RIGHT_HANDED", "SOLVE_DISPERSION_RELATION", "RK4",
-              "RK45", "RAYTRACER_RUN", "CARTESIAN_TO_SPHERICAL", "SPHERICAL_TO_CARTESIAN_VEC", "CARTESIAN_TO_SPHERICAL_VEC", "BMODEL_CARTESIAN", "BMODEL"}
+              "RK45", "RAYTRACER_RUN", "IJK2N", "POINT2XYZ", "TRICUBIC_GET_COEFF", "TRICUBIC_EVAL", "TRICUBIC_GET_COEFF_STACKED", "TRICUBIC_INTERPOLATE_AT", "CARTESIAN_TO_SPHERICAL", "SPHERICAL_TO_CARTESIAN_VEC", "CARTESIAN_TO_SPHERICAL_VEC", "BMODEL_CARTESIAN", "BMODEL"}
 INTRINSICS = {"MOD", "SQRT", "ABS", "COS", "SIN", "ACOS", "ATAN2", "MAX", "SUM", "DOT_PRODUCT", "MAXVAL", "MINVAL", "ALLOCATED", "MATMUL", "TRANSPOSE", "EXP"}
-CTYPE = {"REAL(KIND=DP)": "double", "REAL(KIND=SP)": "float", "COMPLEX(KIND=DP)": "cd", "INTEGER": "int", "LOGICAL": "bool", "CHARACTER": "char"}
+CTYPE = {"REAL*8": "double", "REAL(KIND=DP)": "double", "REAL(KIND=SP)": "float", "COMPLEX(KIND=DP)": "cd", "INTEGER": "int", "LOGICAL": "bool", "CHARACTER": "char"}
 
 TOKEN = re.compile(r"(\.(?:LT|GT|LE|GE|EQ|NE|AND|OR|NOT|TRUE|FALSE)\.)|(\*\*|\(/|/\)|==|/=|>=|<=|[<>])|([A-Z][A-Z0-9_]*)|([(),+\-*/=:])")
 NUMBER = re.compile(r"(\d+\.?\d*(?:[DE][+-]?\d+)?|\.\d+(?:[DE][+-]?\d+)?)(_DP|_SP|_8)?")
@@ -61,6 +61,14 @@ def tokenize(s):
     return toks
 
 
+def number_from(text):
+    sign = ""
+    if text[0] in "+-":
+        sign, text = text[0], text[1:]
+    m = NUMBER.fullmatch(text)
+    return sign + number_cpp(m.group(1), m.group(2))
+
+
 def number_cpp(txt, kind):
     isreal = "." in txt or "E" in txt or "D" in txt
     if not isreal:
@@ -76,7 +84,7 @@ class Sym:
         self.ctype, self.rank, self.dims, self.alloc, self.param = ctype, rank, dims, alloc, param
 
     def cpp(self):
-        return self.ctype if self.rank == 0 else ("Vec<%s>" if self.rank == 1 else "Mat<%s>") % self.ctype
+        return self.ctype if self.rank == 0 else {1: "Vec<%s>", 2: "Mat<%s>", 3: "Arr3<%s>", 4: "Arr4<%s>"}[self.rank] % self.ctype
 
 
 class Unit:
@@ -188,6 +196,12 @@ class Expr:
             lo = s[1] or "1"
             hi = s[2] or "%s.size()" % v
             return "%s.%s(%s, %s)" % (v, "sec" if lhs else "rsec", lo, hi)
+        if sym.rank == 3:
+            return "%s(%s)" % (v, ", ".join(x[1] for x in subs))
+        if sym.rank == 4:
+            if subs[0][0] == "i" and all(x[0] == "r" and x[1] is None and x[2] is None for x in subs[1:]):
+                return "%s.slice1(%s)" % (v, subs[0][1])
+            raise ValueError("rank-4 reference %s%r" % (name, subs))
         a, b = subs
         if a[0] == "i" and b[0] == "i":
             return "%s(%s, %s)" % (v, a[1], b[1])
@@ -336,13 +350,16 @@ def parse_decl(s, syms, prefix=""):
         syms[prefix + m.group(1)] = Sym(CTYPE[base], len(dims), dims, "ALLOCATABLE" in attrs, init if "PARAMETER" in attrs else None)
 
 
+DATA_ROWS = {}
+
+
 def parse(stmts):
     """-> (module-level symbols, units)"""
     glob, units, cur, skip, prefix = {}, {}, None, False, ""
     for lab, s in stmts:
         s = s.rstrip(";").replace("DATAP%P%", "NGO_")
         if s.startswith("TYPE::"):  # components of the adapter's state type become module variables NGO_<component>
-            prefix = "NGO_" if s == "TYPE::NGOSTATEDATA" else "SKIP_"
+            prefix = "NGO_" if s in ("TYPE::NGOSTATEDATA", "TYPE::INTERPSTATEDATA") else "SKIP_"
             continue
         if s.startswith("ENDTYPE"):
             prefix = ""
@@ -367,6 +384,10 @@ def parse(stmts):
             if cur.name in KEEP_UNITS:
                 units[cur.name] = cur
             cur = None
+            continue
+        m2 = re.fullmatch(r"DATA([A-Z][A-Z0-9_]*)\((\d+),:\)/(.+)/", s)
+        if m2 and cur is None:
+            DATA_ROWS.setdefault(m2.group(1), {})[int(m2.group(2))] = split_top(m2.group(3))
             continue
         if "::" in s and (s.split("::")[0].split(",")[0] in CTYPE):
             parse_decl(s, glob if cur is None else cur.syms, prefix if cur is None else "")
@@ -414,6 +435,24 @@ def statement(s, unit, scope, units):
         return ["}"]
     if s == "DO":
         return ["for (;;) {"]
+    m = re.fullmatch(r"DO([A-Z][A-Z0-9_]*)=(.+)", s)
+    if m and len(split_top(m.group(2))) >= 2 and m.group(1) in scope:
+        lim = split_top(m.group(2))
+        var = "v_" + m.group(1)
+        return ["for (%s = %s; %s <= %s; ++%s) {" % (var, tr(lim[0], unit, scope, units), var, tr(lim[1], unit, scope, units), var)]
+    m = re.fullmatch(r"SELECTCASE\((.+)\)", s)
+    if m:
+        return ["switch (%s) {" % tr(m.group(1), unit, scope, units)]
+    m = re.fullmatch(r"CASE\((\d+)\)", s)
+    if m:
+        return ["break; case %s:" % m.group(1)]
+    if s == "CASEDEFAULT":
+        return ["break; default:"]
+    if s == "ENDSELECT":
+        return ["}"]
+    m = re.fullmatch(r"([A-Z][A-Z0-9_]*)=MAXLOC\(\(/\(IND,IND=1,([A-Z]+)\)/\),MASK=0\.0_8<=\(([A-Z]+)-([A-Z]+)\)\)", s)
+    if m:  # the cell search of tricubic_interpolate_at (libtricubic.f95:834-839)
+        return ["v_%s(1) = F90::maxloc_iota_mask(v_%s, v_%s, v_%s);" % m.groups()]
     if s == "EXIT":
         return ["break;"]
     if s == "CYCLE":
@@ -472,10 +511,18 @@ def emit(glob, units):
     out, protos = [], []
     consts = []
     for name, sym in glob.items():  # named constants of the modules, in source order
+        if name in DATA_ROWS:  # a module matrix initialised row by row in DATA statements
+            rows = DATA_ROWS[name]
+            fill = " ".join("{ const double r[] = {%s}; for (int j = 0; j < %d; ++j) m(%d, j + 1) = r[j]; }" % (", ".join(number_from(v) for v in vals), len(vals), r)
+                            for r, vals in sorted(rows.items()))
+            consts.append("static Mat<double> F_data_%s() { Mat<double> m(%s); %s return m; }\nstatic const Mat<double> v_%s = F_data_%s();" % (
+                name, ", ".join(sym.dims), fill, name, name))
+            continue
         if sym.param is None:
             if name not in ("SP", "DP"):
                 dims = ", ".join(sym.dims or [])
-                consts.append("static thread_local %s v_%s%s;" % (sym.cpp(), name, "(%s)" % dims if sym.rank else " = 0"))
+                fixed = sym.rank in (1, 2) and ":" not in (sym.dims or [])
+                consts.append("static thread_local %s v_%s%s;" % (sym.cpp(), name, "(%s)" % dims if fixed else ("" if sym.rank else " = 0")))
             continue
         dummy = Unit("MODULE", "", [])
         consts.append("static const %s v_%s = %s;" % (sym.cpp(), name, tr(sym.param, dummy, glob, units)))
@@ -517,7 +564,7 @@ static thread_local recalc_fn g_recalc = nullptr;
 static thread_local igrf_fn g_igrf = nullptr;
 static thread_local t04_fn g_t04 = nullptr;
 static thread_local dens_fn g_dens = nullptr;
-#if defined(RT_HAVE_NGO_ADAPTER)
+#if defined(RT_HAVE_NGO_ADAPTER) || defined(RT_HAVE_GRID_ADAPTER)
 static void RT_sm_to_gsm(const Vec<int>& itime, const Vec<double>& x, Vec<double>& out) { g_sm2gsm(itime(1), itime(2), x.d.data(), out.d.data()); }
 static void RT_gsm_to_sm(const Vec<int>& itime, const Vec<double>& x, Vec<double>& out) { g_gsm2sm(itime(1), itime(2), x.d.data(), out.d.data()); }
 static void RT_tsy_recalc(int year, int day, int hour, int min, int sec) {
@@ -529,6 +576,8 @@ static void RT_igrf_gsm(float x, float y, float z, float& bx, float& by, float& 
 static void RT_t04_s(int iopt, const Vec<float>& parmod, float ps, float x, float y, float z, float& bx, float& by, float& bz) {
   float b[3]; (void)iopt; g_t04(parmod.d.data(), ps, x, y, z, b); bx = b[0]; by = b[1]; bz = b[2];
 }
+#endif
+#if defined(RT_HAVE_NGO_ADAPTER)
 static void RT_dens() { double a[4]; g_dens(v_Z(1), v_Z(2), v_LATITU, a); for (int i = 1; i <= 4; ++i) v_ANI(i) = a[i - 1]; }
 #endif
 
@@ -625,6 +674,30 @@ void rt_ref_ngo_adapter(void* sm2gsm, void* gsm2sm, void* recalc, void* igrf, vo
   v_NGO_PDYN = parmod[0]; v_NGO_DST = parmod[1]; v_NGO_BYIMF = parmod[2]; v_NGO_BZIMF = parmod[3];
   v_NGO_W1 = parmod[4]; v_NGO_W2 = parmod[5]; v_NGO_W3 = parmod[6]; v_NGO_W4 = parmod[7]; v_NGO_W5 = parmod[8]; v_NGO_W6 = parmod[9];
 }
+#endif
+#if defined(RT_HAVE_GRID_ADAPTER)
+// funcPlasmaParams of the interp adapter (interp_dens_model_adapter.f95:148-269), translated with libtricubic.f95: the state
+// arrays (interpStateData: f and its seven derivative arrays (nspec, nx, ny, nz), node coordinates, qs, ms) are the harness's
+void rt_ref_grid_adapter(void* sm2gsm, void* gsm2sm, void* recalc, void* igrf, void* t04, int yearday, int msec, int use_igrf, int use_tsyganenko,
+                         const double* parmod, const int* dims /* nspec nx ny nz */, const double* del3, const double* qs, const double* ms,
+                         const double* x, const double* y, const double* z, double* const* arrays /* f dfdx dfdy dfdz d2fdxdy d2fdxdz d2fdydz d3fdxdydz */) {
+  g_sm2gsm = (xform_fn)sm2gsm; g_gsm2sm = (xform_fn)gsm2sm; g_recalc = (recalc_fn)recalc; g_igrf = (igrf_fn)igrf; g_t04 = (t04_fn)t04;
+  v_NGO_ITIME(1) = yearday; v_NGO_ITIME(2) = msec; v_NGO_USE_IGRF = use_igrf; v_NGO_USE_TSYGANENKO = use_tsyganenko;
+  v_NGO_PDYN = parmod[0]; v_NGO_DST = parmod[1]; v_NGO_BYIMF = parmod[2]; v_NGO_BZIMF = parmod[3];
+  v_NGO_W1 = parmod[4]; v_NGO_W2 = parmod[5]; v_NGO_W3 = parmod[6]; v_NGO_W4 = parmod[7]; v_NGO_W5 = parmod[8]; v_NGO_W6 = parmod[9];
+  v_NGO_NSPEC = dims[0]; v_NGO_NX = dims[1]; v_NGO_NY = dims[2]; v_NGO_NZ = dims[3];
+  v_NGO_DELX = del3[0]; v_NGO_DELY = del3[1]; v_NGO_DELZ = del3[2];
+  v_NGO_QS = Vec<double>(dims[0]); v_NGO_MS = Vec<double>(dims[0]);
+  for (int i = 1; i <= dims[0]; ++i) { v_NGO_QS(i) = qs[i - 1]; v_NGO_MS(i) = ms[i - 1]; }
+  v_NGO_X = Vec<double>(dims[1]); v_NGO_Y = Vec<double>(dims[2]); v_NGO_Z = Vec<double>(dims[3]);
+  for (int i = 1; i <= dims[1]; ++i) v_NGO_X(i) = x[i - 1];
+  for (int i = 1; i <= dims[2]; ++i) v_NGO_Y(i) = y[i - 1];
+  for (int i = 1; i <= dims[3]; ++i) v_NGO_Z(i) = z[i - 1];
+  Arr4<double>* a[8] = {&v_NGO_F, &v_NGO_DFDX, &v_NGO_DFDY, &v_NGO_DFDZ, &v_NGO_D2FDXDY, &v_NGO_D2FDXDZ, &v_NGO_D2FDYDZ, &v_NGO_D3FDXDYDZ};
+  for (int k = 0; k < 8; ++k) { a[k]->p = arrays[k]; a[k]->n1 = dims[0]; a[k]->n2 = dims[1]; a[k]->n3 = dims[2]; a[k]->n4 = dims[3]; }
+}
+#endif
+#if defined(RT_HAVE_NGO_ADAPTER) || defined(RT_HAVE_GRID_ADAPTER)
 static void ngo_adapter_cb(const double* x, double* qs, double* Ns, double* ms, double* nus, double* B0, int* nspec) {
   Vec<double> vx(3), q, n, m, nu, b(3);
   for (int i = 1; i <= 3; ++i) vx(i) = x[i - 1];
@@ -655,14 +728,15 @@ def main(dst, srcs):
         stmts += read_statements_free(one)
     glob, units = parse(stmts)
     glob = {k: v for k, v in glob.items() if not k.startswith("SKIP_")}
-    if "FUNCPLASMAPARAMS" in units:  # `use ngo_dens_model, only : readinput, dens, ani, z, L, R0, latitu`
+    grid = "TRICUBIC_INTERPOLATE_AT" in units
+    if "FUNCPLASMAPARAMS" in units and not grid:  # `use ngo_dens_model, only : readinput, dens, ani, z, L, R0, latitu`
         for name, sym in (("Z", Sym("double", 1, ["5"])), ("ANI", Sym("double", 1, ["4"])), ("L", Sym("double")), ("R0", Sym("double")), ("LATITU", Sym("double"))):
             glob.setdefault(name, sym)
     consts, protos, texts = emit(glob, units)
     with open(dst, "w") as f:
         f.write("// GENERATED by oracle/f90_to_cpp.py from the reference's Fortran 90 at build time -- never committed.\n#include \"f90rt.h\"\n")
         if "FUNCPLASMAPARAMS" in units:
-            f.write("#define RT_HAVE_NGO_ADAPTER 1\n")
+            f.write("#define RT_HAVE_%s_ADAPTER 1\n" % ("GRID" if grid else "NGO"))
         f.write("\n".join(consts) + "\n" + WRAPPERS + "\n" + "\n".join(protos) + "\n\n" + "\n".join(texts) + ENTRY)
 
 

@@ -109,6 +109,18 @@ void orc_hook_csvd(const double* m_re_im, double* vt_re_im) {
   for (int j = 0; j < 3; ++j) { vt_re_im[2 * (2 + 3 * j)] = v[j].re; vt_re_im[2 * (2 + 3 * j) + 1] = -v[j].im; }
 }
 
+#ifdef ORC_HAVE_GRID
+// the gridded model's state (interpStateData of interp_dens_model_adapter.f95) for the reference's translated adapter + libtricubic:
+// dims = nspec nx ny nz, del3, and pointers to qs, ms, x, y, z, f, dfdx, dfdy, dfdz, d2fdxdy, d2fdxdz, d2fdydz, d3fdxdydz (Fortran order)
+void orc_grid_state(void* mv, int* dims, double* del3, double** ptrs) {
+  GridModel* g = (GridModel*)(Model*)mv;
+  dims[0] = g->nspec; dims[1] = g->nx; dims[2] = g->ny; dims[3] = g->nz;
+  del3[0] = g->delx; del3[1] = g->dely; del3[2] = g->delz;
+  std::vector<double>* v[13] = {&g->qs, &g->ms, &g->x, &g->y, &g->z, &g->f, &g->dfdx, &g->dfdy, &g->dfdz, &g->d2fdxdy, &g->d2fdxdz, &g->d2fdydz, &g->d3fdxdydz};
+  for (int i = 0; i < 13; ++i) ptrs[i] = v[i]->data();
+}
+#endif
+
 void orc_model_free(void* m) { delete (Model*)m; }
 
 double orc_model_del(void* m) { return ((Model*)m)->del; }

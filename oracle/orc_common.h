@@ -7,14 +7,15 @@
 //
 // PARITY: the reference ships no golden vectors for this path and no Fortran compiler
 // exists in this environment.
-//   PINNED by the reference's own source, bit for bit -- the whole Ngo path (configs 1, 2, 4):
-//   the reference's sources are translated at build time (f77_to_cpp.py for the FORTRAN 77-style
-//   files, f90_to_cpp.py over ref_stubs/f90rt.h for raytracer.f95, the Ngo adapter, util.f95,
-//   bmodel_dipole.f95, constants.f95 -> _ref/*.so) and the restatements here are compared with
-//   them, down to whole rays through the translated raytracer_run (tests/test_*_ref_cpu.py,
-//   test_ts05_cpu.py).  f90rt.h states the array semantics a compiler would decide.
-//   PARITY UNPINNED: orc_grid.h (interp adapter, libtricubic: outside the translators'
-//   subset) and the stand-in for LAPACK's zgesvd (is_right_handed): pinned only by
+//   PINNED by the reference's own source, bit for bit -- the hot path of configs 1-4 (Ngo and
+//   gridded density, dipole / IGRF / TS05): the reference's sources are translated at build time
+//   (f77_to_cpp.py for the FORTRAN 77-style files, f90_to_cpp.py over ref_stubs/f90rt.h for
+//   raytracer.f95, both adapters, libtricubic.f95, util.f95, bmodel_dipole.f95, constants.f95
+//   -> _ref/*.so) and the restatements here are compared with them, down to whole rays through
+//   the translated raytracer_run (tests/test_*_ref_cpu.py, test_ts05_cpu.py).  f90rt.h states
+//   the array semantics a compiler would decide.
+//   PARITY UNPINNED: the interp adapter's setup (grid file reader, finite-difference
+//   derivatives) and the stand-in for LAPACK's zgesvd (is_right_handed): pinned only by
 //   reference-independent identities (tests/test_oracle_*.py), not by reference outputs.
 //
 // Elementary functions: by default the oracle uses the same srt_math.h layer

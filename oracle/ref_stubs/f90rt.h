@@ -69,6 +69,17 @@ template <class T> struct Mat {  // column-major, 1-based
   Block block(int a, int b, int c, int e) { return Block{*this, a, b, c, e}; }
 };
 
+// rank-3 view (an assumed-shape dummy, or the section a(ind,:,:,:) of a rank-4 array) and rank-4 view over storage in
+// Fortran order that the harness owns
+template <class T> struct Arr3 {
+  T* p = nullptr; long s1 = 0, s2 = 0, s3 = 0; int n1 = 0, n2 = 0, n3 = 0;
+  T& operator()(int i, int j, int k) const { return p[(i - 1) * s1 + (j - 1) * s2 + (k - 1) * s3]; }
+};
+template <class T> struct Arr4 {
+  T* p = nullptr; int n1 = 0, n2 = 0, n3 = 0, n4 = 0;
+  Arr3<T> slice1(int i) const { Arr3<T> r; r.p = p + (i - 1); r.s1 = n1; r.s2 = (long)n1 * n2; r.s3 = (long)n1 * n2 * n3; r.n1 = n2; r.n2 = n3; r.n3 = n4; return r; }
+};
+
 // ---- element-wise arithmetic
 template <class A, class B> using common_t = typename std::common_type<A, B>::type;
 #define F90_BINOP(op)                                                                                                      \
@@ -139,8 +150,14 @@ inline Vec<double> matmul(const Mat<double>& a, const Vec<double>& b) {
   for (int j = 1; j <= a.n2; ++j) for (int i = 1; i <= a.n1; ++i) c(i) = c(i) + a(i, j) * b(j);
   return c;
 }
+inline double exp(double x) { return ::exp(x); }
+inline Vec<double> exp(const Vec<double>& v) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = ::exp(v(i)); return r; }
+template <class T> int size(const Arr3<T>& a, int dim) { return dim == 1 ? a.n1 : (dim == 2 ? a.n2 : a.n3); }
+// MAXLOC((/ (ind, ind = 1, n) /), MASK = 0.0 <= (xi - x)): the largest index whose node is not above xi; 0 if there is none
+inline int maxloc_iota_mask(int n, double xi, const Vec<double>& x) { int best = 0; for (int i = 1; i <= n; ++i) if (0.0 <= (xi - x(i))) best = i; return best; }
 template <class T> int size(const Vec<T>& v) { return v.size(); }
 template <class T> int size(const Mat<T>& m, int dim) { return dim == 1 ? m.n1 : m.n2; }
+template <class T> int size(const Vec<T>& v, int dim) { (void)dim; return v.size(); }
 template <class T> bool allocated(const Vec<T>& v) { return v.allocated; }
 }  // namespace F90
 
@@ -158,6 +175,13 @@ template <int N, class T> T F_powc(const T& x) {
   else return F_powc<N - tbl[N]>(x) * F_powc<tbl[N]>(x);
 }
 inline double F_pow(double x, double y) { return ::pow(x, y); }
+// x**n, integer n at run time: libgfortran's pow_r8_i4 / libgcc's __powidf2 (square and multiply from the low bit)
+inline double F_pow(double x, int m) {
+  unsigned n = m < 0 ? -(unsigned)m : (unsigned)m;
+  double y = (n % 2) ? x : 1;
+  while (n >>= 1) { x = x * x; if (n % 2) y *= x; }
+  return m < 0 ? 1 / y : y;
+}
 inline Vec<double> F_pow(const Vec<double>& v, double y) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = ::pow(v(i), y); return r; }
 inline double F_toreal(double x) { return x; }
 inline double F_toreal(const cd& z) { return z.real(); }  // COMPLEX assigned to REAL: the real part

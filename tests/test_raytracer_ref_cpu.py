@@ -202,3 +202,62 @@ def test_whole_rays_from_the_translated_sources_only(ref, use_igrf, use_tsy):
         assert_same(ref, o, pos0[r], [0, 0, 0], w0[r], dict(common.C2, maxsteps=nsteps), "adaptive ray %d" % r)
     assert_same(ref, o, pos0[5], [0, 0, 0], w0[5], dict(common.C1, maxsteps=100), "config-1 ray")
     del keep
+
+
+# ---------------------------------------------------------------- the gridded path (config 3) from the reference's translated sources
+def grid_chain(o, yearday, msec, use_igrf, use_tsy):
+    """funcPlasmaParams = the reference's interp adapter + libtricubic.f95 (tricubic_interpolate_at, tricubic_eval, the 64 x 64
+    coefficient product), translated in librt_grid_ref, over the translated coordinate chain, Geopack and TS05.  The state arrays
+    (f and its seven derivative arrays, filled by the adapter's `setup`: file reader + finite differences, not translated) are
+    the oracle's."""
+    ref_dir = os.path.join(ol.ORC_DIR, "_ref")
+    path = os.path.join(ref_dir, "librt_grid_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/librt_grid_ref.so not built (reference sources absent)")
+    R, X, G, T = (C.CDLL(os.path.join(ref_dir, n)) for n in ("librt_grid_ref.so", "libxform_ref.so", "libgeopack_ref.so", "libts05_ref.so"))
+    vp, d, i, l = C.c_void_p, C.c_double, C.c_int, C.c_long
+    dims, del3, ptrs = (i * 4)(), (d * 3)(), (vp * 13)()
+    o.L.orc_grid_state.argtypes = [vp, vp, vp, vp]
+    o.L.orc_grid_state(o.h, dims, del3, ptrs)
+    arrays = (vp * 8)(*ptrs[5:13])
+    fp = lambda f: C.cast(f, vp)  # noqa: E731
+    R.rt_ref_grid_adapter.argtypes = [vp] * 5 + [i, i, i, i] + [vp] * 9
+    R.rt_ref_grid_adapter(fp(X.xform_ref_sm_to_gsm), fp(X.xform_ref_gsm_to_sm), fp(G.geopack_ref_recalc), fp(G.geopack_ref_igrf_gsw), fp(T.ts05_ref_t04_s),
+                          yearday, msec, use_igrf, use_tsy, PARMOD.ctypes.data, dims, del3, ptrs[0], ptrs[1], ptrs[2], ptrs[3], ptrs[4], arrays)
+    R.rt_ref_ngo_plasma.argtypes = [l, vp, vp]
+    R.rt_ref_use_ngo_adapter.argtypes = [vp]
+    R.rt_ref_run.restype = l
+    R.rt_ref_run.argtypes = [vp, vp, d, d, d, d, i, d, i, d, i, d, vp, l, vp]
+    return R, (X, G, T, arrays)
+
+
+@pytest.mark.parametrize("use_igrf,use_tsy", [(1, 0), (0, 0), (1, 1)])
+def test_interp_adapter_and_libtricubic_from_the_translated_sources(use_igrf, use_tsy):
+    o = ol.OracleModel("grid", GRID13, 2010001, 3600000, use_igrf, libm=True, faithful_cost=True)
+    if use_tsy:
+        o.tsyganenko(PARMOD, srt_math=False)
+    R, keep = grid_chain(o, 2010001, 3600000, use_igrf, use_tsy)
+    rng = np.random.default_rng(6)
+    x = np.ascontiguousarray(rng.uniform(-4.3 * ol.R_E, 4.3 * ol.R_E, (3000, 3)))  # inside the 13^3 lattice, on its edge cells and outside
+    x[:50] = np.round(x[:50] / 4247466.666666667) * 4247466.666666667             # on lattice nodes
+    x = np.ascontiguousarray(x[np.linalg.norm(x, axis=1) > 0])                     # (the dipole field at the origin is a NaN on both sides)
+    out = np.zeros((len(x), 19))
+    R.rt_ref_ngo_plasma(len(x), x.ctypes.data, out.ctypes.data)
+    a = o.plasma(x)
+    assert np.array_equal(a.view(np.uint64), out.view(np.uint64))
+    fast = ol.OracleModel("grid", GRID13, 2010001, 3600000, use_igrf, libm=True)  # the oracle's fast form too
+    if use_tsy:
+        fast.tsyganenko(PARMOD, srt_math=False)
+    assert np.array_equal(fast.plasma(x).view(np.uint64), out.view(np.uint64))
+    del keep
+
+
+def test_whole_rays_through_the_translated_gridded_path():
+    """config 3's path ray for ray: translated driver loop + integrator + interp adapter + libtricubic + coordinate chain + Geopack"""
+    o = ol.OracleModel("grid", GRID13, 2010001, 0, 1, libm=True)
+    R, keep = grid_chain(o, 2010001, 0, 1, 0)
+    R.rt_ref_use_ngo_adapter(C.cast(o.L.orc_hook_csvd, C.c_void_p))
+    pos0, dir0, w0 = common.launch_grid([800.0, 3000.0, 9000.0], [25.0, 40.0, 55.0])
+    for r in range(len(w0)):
+        assert_same(R, o, pos0[r], [0, 0, 0], w0[r], dict(common.C2, maxsteps=250), "grid ray %d" % r)
+    del keep
