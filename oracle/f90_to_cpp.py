@@ -20,10 +20,11 @@ from f77_to_cpp import read_statements_free, split_top, top_level_eq  # noqa: E4
 
 HOOK_SUBS = {"SM_TO_GSM_D": "RT_sm_to_gsm", "GSM_TO_SM_D": "RT_gsm_to_sm", "TSY_RECALC": "RT_tsy_recalc", "IGRF_GSM": "RT_igrf_gsm",
              "T04_S": "RT_t04_s", "DENS": "RT_dens"}
-DUMMY_PROCS = {"FUNCPLASMAPARAMS", "FUNCPLASMAPARAMSDATA", "FUNCSTOPCONDITIONS"}
+DUMMY_PROCS = {"FUNCPLASMAPARAMS", "FUNCPLASMAPARAMSDATA", "FUNCSTOPCONDITIONS", "DAT"}  # DAT: the state argument of setup (its components are module variables here)
 KEEP_UNITS = {"FUNCPLASMAPARAMS", "DISPERSION_RELATION", "STIX_PARAMETERS", "DISPERSION_RELATION_DFDK", "DISPERSION_RELATION_DFDW", "DISPERSION_RELATION_DFDX",
               "RAYTRACER_EVALRHS", "RAYTRACER_STOPCONDITIONS", "FORM_DISPERSION_MATRIX", "IS_RIGHT_HANDED", "SOLVE_DISPERSION_RELATION", "RK4",
-              "RK45", "RAYTRACER_RUN", "IJK2N", "POINT2XYZ", "TRICUBIC_GET_COEFF", "TRICUBIC_EVAL", "TRICUBIC_GET_COEFF_STACKED", "TRICUBIC_INTERPOLATE_AT", "CARTESIAN_TO_SPHERICAL", "SPHERICAL_TO_CARTESIAN_VEC", "CARTESIAN_TO_SPHERICAL_VEC", "BMODEL_CARTESIAN", "BMODEL"}
+              "RK45", "RAYTRACER_RUN", "IJK2N", "POINT2XYZ", "TRICUBIC_GET_COEFF", "TRICUBIC_EVAL", "TRICUBIC_GET_COEFF_STACKED", "TRICUBIC_INTERPOLATE_AT", "TRICUBIC_COMPUTE_FINITE_DIFFERENCE_DERIVATIVES", "CARTESIAN_TO_SPHERICAL", "SPHERICAL_TO_CARTESIAN_VEC", "CARTESIAN_TO_SPHERICAL_VEC", "BMODEL_CARTESIAN", "BMODEL"}
+GRID_BUILD = False
 INTRINSICS = {"MOD", "SQRT", "ABS", "COS", "SIN", "ACOS", "ATAN2", "MAX", "SUM", "DOT_PRODUCT", "MAXVAL", "MINVAL", "ALLOCATED", "MATMUL", "TRANSPOSE", "EXP"}
 CTYPE = {"REAL*8": "double", "REAL(KIND=DP)": "double", "REAL(KIND=SP)": "float", "COMPLEX(KIND=DP)": "cd", "INTEGER": "int", "LOGICAL": "bool", "CHARACTER": "char"}
 
@@ -84,6 +85,8 @@ class Sym:
         self.ctype, self.rank, self.dims, self.alloc, self.param = ctype, rank, dims, alloc, param
 
     def cpp(self):
+        if self.ctype == "char":
+            return "const char*"
         return self.ctype if self.rank == 0 else {1: "Vec<%s>", 2: "Mat<%s>", 3: "Arr3<%s>", 4: "Arr4<%s>"}[self.rank] % self.ctype
 
 
@@ -197,10 +200,17 @@ class Expr:
             hi = s[2] or "%s.size()" % v
             return "%s.%s(%s, %s)" % (v, "sec" if lhs else "rsec", lo, hi)
         if sym.rank == 3:
-            return "%s(%s)" % (v, ", ".join(x[1] for x in subs))
+            if all(x[0] == "i" for x in subs):
+                return "%s(%s)" % (v, ", ".join(x[1] for x in subs))
+            ext = []  # a section; a scalar subscript keeps its dimension with extent 1 (every operand of one statement has it in the same place)
+            for d, x in enumerate(subs):
+                ext += [x[1], x[1]] if x[0] == "i" else [x[1] or "1", x[2] or "%s.n%d" % (v, d + 1)]
+            return "%s.sec3(%s)" % (v, ", ".join(ext))
         if sym.rank == 4:
             if subs[0][0] == "i" and all(x[0] == "r" and x[1] is None and x[2] is None for x in subs[1:]):
                 return "%s.slice1(%s)" % (v, subs[0][1])
+            if all(x[0] == "i" for x in subs):
+                return "%s(%s)" % (v, ", ".join(x[1] for x in subs))
             raise ValueError("rank-4 reference %s%r" % (name, subs))
         a, b = subs
         if a[0] == "i" and b[0] == "i":
@@ -254,6 +264,10 @@ class Expr:
             e = self.expr()
             self.take(")")
             return "(%s)" % e
+        if tok == "(/" and self.peek() == "(" and self.peek(2) == "," and self.peek(1) == self.peek(3) and self.peek(4) == "=":
+            self.take(); self.take(); self.take(); self.take(); self.take()  # (/ (IND, IND = lo, hi) /): the integers lo..hi
+            lo = self.expr(); self.take(","); hi = self.expr(); self.take(")"); self.take("/)")
+            return "F90::iota(%s, %s)" % (lo, hi)
         if tok == "(/":
             items = []
             while True:
@@ -337,6 +351,8 @@ def parse_decl(s, syms, prefix=""):
     spec, rest = s.split("::", 1)
     parts = split_top(spec)
     base = parts[0]
+    if base.startswith("CHARACTER("):
+        base = "CHARACTER"
     if base not in CTYPE:
         raise ValueError("declaration %r" % s)
     attrs = set(p.split("(")[0] for p in parts[1:])
@@ -357,7 +373,7 @@ def parse(stmts):
     """-> (module-level symbols, units)"""
     glob, units, cur, skip, prefix = {}, {}, None, False, ""
     for lab, s in stmts:
-        s = s.rstrip(";").replace("DATAP%P%", "NGO_")
+        s = s.rstrip(";").replace("DATAP%P%", "NGO_").replace("DAT%", "NGO_")
         if s.startswith("TYPE::"):  # components of the adapter's state type become module variables NGO_<component>
             prefix = "NGO_" if s in ("TYPE::NGOSTATEDATA", "TYPE::INTERPSTATEDATA") else "SKIP_"
             continue
@@ -381,7 +397,7 @@ def parse(stmts):
             cur = Unit(m.group(1), m.group(2), [a for a in m.group(3).split(",") if a])
             continue
         if s.startswith("ENDFUNCTION") or s.startswith("ENDSUBROUTINE"):
-            if cur.name in KEEP_UNITS:
+            if cur.name in KEEP_UNITS or (GRID_BUILD and cur.name == "SETUP"):
                 units[cur.name] = cur
             cur = None
             continue
@@ -389,7 +405,7 @@ def parse(stmts):
         if m2 and cur is None:
             DATA_ROWS.setdefault(m2.group(1), {})[int(m2.group(2))] = split_top(m2.group(3))
             continue
-        if "::" in s and (s.split("::")[0].split(",")[0] in CTYPE):
+        if "::" in s and (s.split("::")[0].split(",")[0] in CTYPE or s.startswith("CHARACTER(")):
             parse_decl(s, glob if cur is None else cur.syms, prefix if cur is None else "")
             continue
         if cur is not None:
@@ -453,6 +469,28 @@ def statement(s, unit, scope, units):
     m = re.fullmatch(r"([A-Z][A-Z0-9_]*)=MAXLOC\(\(/\(IND,IND=1,([A-Z]+)\)/\),MASK=0\.0_8<=\(([A-Z]+)-([A-Z]+)\)\)", s)
     if m:  # the cell search of tricubic_interpolate_at (libtricubic.f95:834-839)
         return ["v_%s(1) = F90::maxloc_iota_mask(v_%s, v_%s, v_%s);" % m.groups()]
+    m = re.fullmatch(r'OPEN\(UNIT=([A-Z0-9_]+),FILE=([A-Z0-9_]+),STATUS="OLD"\)', s.upper())
+    if m:
+        return ["F_open(v_%s, v_%s);" % m.groups()]
+    m = re.fullmatch(r"CLOSE\(([A-Z0-9_]+)\)", s)
+    if m:
+        return ["F_close(v_%s);" % m.group(1)]
+    m = re.fullmatch(r"READ\(([A-Z0-9_]+),\*\),?(.+)", s)
+    if m:  # list-directed READ: one statement = one F_Read, which starts at a record and ends by skipping the rest of the last one
+        def items(text):
+            out = []
+            for it in split_top(text):
+                if it.startswith("(") and it.endswith(")") and top_level_eq(it[1:-1]) >= 0:
+                    parts = split_top(it[1:-1])
+                    k = next(i for i, q in enumerate(parts) if top_level_eq(q) >= 0)
+                    var, lo = parts[k].split("=", 1)
+                    v = "v_" + var
+                    out.append("for (%s = %s; %s <= %s; ++%s) { %s }" % (v, tr(lo, unit, scope, units), v, tr(parts[k + 1], unit, scope, units), v,
+                                                                         " ".join(items(",".join(parts[:k])))))
+                else:
+                    out.append("rd.item(%s);" % lhs_cpp(it, unit, scope, units)[0])
+            return out
+        return ["{ F_Read rd(v_%s); %s }" % (m.group(1), " ".join(items(m.group(2))))]
     if s == "EXIT":
         return ["break;"]
     if s == "CYCLE":
@@ -503,6 +541,8 @@ def statement(s, unit, scope, units):
             return ["%s = F_toreal(%s);" % (target, rhs)]
         if whole and sym.rank == 1 and sym.ctype == "cd":
             return ["%s = F_tocplx(%s);" % (target, rhs)]
+        if sym.rank == 3 and (whole or ".sec3(" in target):
+            return ["F_assign3(%s, %s);" % (target, rhs)]
         return ["%s = %s;" % (target, rhs)]
     raise ValueError("cannot translate %r in %s" % (s, unit.name))
 
@@ -536,7 +576,9 @@ def emit(glob, units):
             if n in u.args or n in DUMMY_PROCS:
                 continue
             dims = [d for d in (sym.dims or [])]
-            if sym.rank and not sym.alloc and ":" not in dims:
+            if sym.param is not None:  # a local named constant
+                decl.append("const %s v_%s = %s;" % (sym.cpp(), n, tr(sym.param, u, scope, units)))
+            elif sym.rank and not sym.alloc and ":" not in dims:
                 decl.append("%s v_%s(%s);" % (sym.cpp(), n, ", ".join(tr(d, u, scope, units) for d in dims)))
             elif sym.rank:
                 decl.append("%s v_%s;" % (sym.cpp(), n))
@@ -696,6 +738,36 @@ void rt_ref_grid_adapter(void* sm2gsm, void* gsm2sm, void* recalc, void* igrf, v
   Arr4<double>* a[8] = {&v_NGO_F, &v_NGO_DFDX, &v_NGO_DFDY, &v_NGO_DFDZ, &v_NGO_D2FDXDY, &v_NGO_D2FDXDZ, &v_NGO_D2FDYDZ, &v_NGO_D3FDXDYDZ};
   for (int k = 0; k < 8; ++k) { a[k]->p = arrays[k]; a[k]->n1 = dims[0]; a[k]->n2 = dims[1]; a[k]->n3 = dims[2]; a[k]->n4 = dims[3]; }
 }
+// setup of the interp adapter (interp_dens_model_adapter.f95:52-134), translated: reads the grid file (list-directed READs),
+// builds the node coordinates and either reads the seven derivative arrays or computes them by finite differences; the other
+// members of the state (time, field switches, TS05 parameters) are the caller's, as in the driver (raytracer_driver.f95)
+void rt_ref_grid_setup(const char* path, void* sm2gsm, void* gsm2sm, void* recalc, void* igrf, void* t04, int yearday, int msec, int use_igrf,
+                       int use_tsyganenko, const double* parmod) {
+  g_sm2gsm = (xform_fn)sm2gsm; g_gsm2sm = (xform_fn)gsm2sm; g_recalc = (recalc_fn)recalc; g_igrf = (igrf_fn)igrf; g_t04 = (t04_fn)t04;
+  v_NGO_ITIME(1) = yearday; v_NGO_ITIME(2) = msec; v_NGO_USE_IGRF = use_igrf; v_NGO_USE_TSYGANENKO = use_tsyganenko;
+  v_NGO_PDYN = parmod[0]; v_NGO_DST = parmod[1]; v_NGO_BYIMF = parmod[2]; v_NGO_BZIMF = parmod[3];
+  v_NGO_W1 = parmod[4]; v_NGO_W2 = parmod[5]; v_NGO_W3 = parmod[6]; v_NGO_W4 = parmod[7]; v_NGO_W5 = parmod[8]; v_NGO_W6 = parmod[9];
+  f_SETUP(path);
+}
+// what setup left in the state: dims = nspec nx ny nz; ptrs = qs ms x y z f dfdx dfdy dfdz d2fdxdy d2fdxdz d2fdydz d3fdxdydz
+void rt_ref_grid_state(int* dims, double* del3, double** ptrs) {
+  dims[0] = v_NGO_NSPEC; dims[1] = v_NGO_NX; dims[2] = v_NGO_NY; dims[3] = v_NGO_NZ;
+  del3[0] = v_NGO_DELX; del3[1] = v_NGO_DELY; del3[2] = v_NGO_DELZ;
+  ptrs[0] = &v_NGO_QS(1); ptrs[1] = &v_NGO_MS(1); ptrs[2] = &v_NGO_X(1); ptrs[3] = &v_NGO_Y(1); ptrs[4] = &v_NGO_Z(1);
+  Arr4<double>* a[8] = {&v_NGO_F, &v_NGO_DFDX, &v_NGO_DFDY, &v_NGO_DFDZ, &v_NGO_D2FDXDY, &v_NGO_D2FDXDZ, &v_NGO_D2FDYDZ, &v_NGO_D3FDXDYDZ};
+  for (int k = 0; k < 8; ++k) ptrs[5 + k] = a[k]->p;
+}
+// tricubic_compute_finite_difference_derivatives (libtricubic.f95:722-793), translated, called species by species on the
+// sections (ind,:,:,:) as setup does (interp_dens_model_adapter.f95:120-131); arrays[0] = f is read, arrays[1..7] are written
+void rt_ref_grid_fd(const int* dims, const double* del3, double* const* arrays) {
+  Arr4<double> a[8];
+  for (int k = 0; k < 8; ++k) { a[k].p = arrays[k]; a[k].n1 = dims[0]; a[k].n2 = dims[1]; a[k].n3 = dims[2]; a[k].n4 = dims[3]; }
+  double dx = del3[0], dy = del3[1], dz = del3[2];
+  for (int ind = 1; ind <= dims[0]; ++ind)
+    f_TRICUBIC_COMPUTE_FINITE_DIFFERENCE_DERIVATIVES(F_tmp<Arr3<double>>(a[0].slice1(ind)), dx, dy, dz,
+        F_tmp<Arr3<double>>(a[1].slice1(ind)), F_tmp<Arr3<double>>(a[2].slice1(ind)), F_tmp<Arr3<double>>(a[3].slice1(ind)), F_tmp<Arr3<double>>(a[4].slice1(ind)),
+        F_tmp<Arr3<double>>(a[5].slice1(ind)), F_tmp<Arr3<double>>(a[6].slice1(ind)), F_tmp<Arr3<double>>(a[7].slice1(ind)));
+}
 #endif
 #if defined(RT_HAVE_NGO_ADAPTER) || defined(RT_HAVE_GRID_ADAPTER)
 static void ngo_adapter_cb(const double* x, double* qs, double* Ns, double* ms, double* nus, double* B0, int* nspec) {
@@ -723,6 +795,8 @@ void rt_ref_ngo_plasma(long n, const double* x, double* out /*[n][19]*/) {
 
 
 def main(dst, srcs):
+    global GRID_BUILD
+    GRID_BUILD = any("libtricubic" in one for one in srcs)
     stmts = []
     for one in srcs:
         stmts += read_statements_free(one)

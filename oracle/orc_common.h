@@ -14,9 +14,10 @@
 //   -> _ref/*.so) and the restatements here are compared with them, down to whole rays through
 //   the translated raytracer_run (tests/test_*_ref_cpu.py, test_ts05_cpu.py).  f90rt.h states
 //   the array semantics a compiler would decide.
-//   PARITY UNPINNED: the interp adapter's setup (grid file reader, finite-difference
-//   derivatives) and the stand-in for LAPACK's zgesvd (is_right_handed): pinned only by
-//   reference-independent identities (tests/test_oracle_*.py), not by reference outputs.
+//   The interp adapter's setup (grid file reader, node coordinates, finite-difference
+//   derivatives) is translated too and leaves the state orc_models.h builds, bit for bit.
+//   PARITY UNPINNED: the stand-in for LAPACK's zgesvd (is_right_handed) and the driver's file
+//   formats: pinned only by reference-independent identities (tests/test_oracle_*.py).
 //
 // Elementary functions: by default the oracle uses the same srt_math.h layer
 // as the device (so GPU == oracle is a bitwise statement).  Compile with

@@ -8,6 +8,11 @@
 #pragma once
 #include <math.h>
 #include <complex>
+#include <stdio.h>
+#include <stdlib.h>
+#include <map>
+#include <memory>
+#include <string>
 #include <type_traits>
 #include <vector>
 
@@ -74,9 +79,33 @@ template <class T> struct Mat {  // column-major, 1-based
 template <class T> struct Arr3 {
   T* p = nullptr; long s1 = 0, s2 = 0, s3 = 0; int n1 = 0, n2 = 0, n3 = 0;
   T& operator()(int i, int j, int k) const { return p[(i - 1) * s1 + (j - 1) * s2 + (k - 1) * s3]; }
+  // the section (a1:b1, a2:b2, a3:b3); a scalar subscript i is passed as i:i and keeps its dimension with extent 1
+  Arr3 sec3(int a1, int b1, int a2, int b2, int a3, int b3) const {
+    Arr3 r = *this; r.p = &(*this)(a1, a2, a3); r.n1 = b1 - a1 + 1; r.n2 = b2 - a2 + 1; r.n3 = b3 - a3 + 1; return r; }
 };
+// value of a rank-3 array expression (elements are independent of one another: the order of evaluation is free; the right-hand
+// side is complete before the assignment stores, as the language requires)
+struct Val3 {
+  std::vector<double> d; int n1 = 0, n2 = 0, n3 = 0;
+  Val3(int a, int b, int c) : d((size_t)a * b * c), n1(a), n2(b), n3(c) {}
+  double& operator()(int i, int j, int k) { return d[(size_t)(i - 1) + (size_t)n1 * ((j - 1) + (size_t)n2 * (k - 1))]; }
+  double operator()(int i, int j, int k) const { return d[(size_t)(i - 1) + (size_t)n1 * ((j - 1) + (size_t)n2 * (k - 1))]; }
+};
+inline Val3 operator-(const Arr3<double>& a, const Arr3<double>& b) {
+  Val3 r(a.n1, a.n2, a.n3);
+  for (int k = 1; k <= a.n3; ++k) for (int j = 1; j <= a.n2; ++j) for (int i = 1; i <= a.n1; ++i) r(i, j, k) = a(i, j, k) - b(i, j, k);
+  return r; }
+inline Val3 operator/(Val3 a, double s) { for (double& v : a.d) v = v / s; return a; }
+inline void F_assign3(const Arr3<double>& dst, const Val3& v) {
+  for (int k = 1; k <= dst.n3; ++k) for (int j = 1; j <= dst.n2; ++j) for (int i = 1; i <= dst.n1; ++i) dst(i, j, k) = v(i, j, k); }
+inline void F_assign3(const Arr3<double>& dst, double s) {
+  for (int k = 1; k <= dst.n3; ++k) for (int j = 1; j <= dst.n2; ++j) for (int i = 1; i <= dst.n1; ++i) dst(i, j, k) = s; }
 template <class T> struct Arr4 {
   T* p = nullptr; int n1 = 0, n2 = 0, n3 = 0, n4 = 0;
+  std::shared_ptr<std::vector<T>> own;  // set by ALLOCATE; empty when the harness lends its storage
+  Arr4() {}
+  Arr4(int a, int b, int c, int d) : n1(a), n2(b), n3(c), n4(d), own(new std::vector<T>((size_t)a * b * c * d)) { p = own->data(); }
+  T& operator()(int i, int j, int k, int l) const { return p[(size_t)(i - 1) + (size_t)n1 * ((j - 1) + (size_t)n2 * ((k - 1) + (size_t)n3 * (l - 1)))]; }
   Arr3<T> slice1(int i) const { Arr3<T> r; r.p = p + (i - 1); r.s1 = n1; r.s2 = (long)n1 * n2; r.s3 = (long)n1 * n2 * n3; r.n1 = n2; r.n2 = n3; r.n3 = n4; return r; }
 };
 
@@ -152,6 +181,7 @@ inline Vec<double> matmul(const Mat<double>& a, const Vec<double>& b) {
 }
 inline double exp(double x) { return ::exp(x); }
 inline Vec<double> exp(const Vec<double>& v) { Vec<double> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = ::exp(v(i)); return r; }
+inline Vec<int> iota(int lo, int hi) { Vec<int> r(hi - lo + 1 > 0 ? hi - lo + 1 : 0); for (int i = lo; i <= hi; ++i) r(i - lo + 1) = i; return r; }
 template <class T> int size(const Arr3<T>& a, int dim) { return dim == 1 ? a.n1 : (dim == 2 ? a.n2 : a.n3); }
 // MAXLOC((/ (ind, ind = 1, n) /), MASK = 0.0 <= (xi - x)): the largest index whose node is not above xi; 0 if there is none
 inline int maxloc_iota_mask(int n, double xi, const Vec<double>& x) { int best = 0; for (int i = 1; i <= n; ++i) if (0.0 <= (xi - x(i))) best = i; return best; }
@@ -187,6 +217,35 @@ inline double F_toreal(double x) { return x; }
 inline double F_toreal(const cd& z) { return z.real(); }  // COMPLEX assigned to REAL: the real part
 inline Vec<cd> F_tocplx(const Vec<cd>& v) { return v; }
 inline Vec<cd> F_tocplx(const Vec<double>& v) { Vec<cd> r(v.size()); for (int i = 1; i <= v.size(); ++i) r(i) = cd(v(i), 0.0); return r; }
+// ---- list-directed input (OPEN / READ(unit,*) / CLOSE of the interp adapter's setup): values are separated by blanks, commas
+// or record ends; a READ takes as many records as its list needs and leaves the file at the start of the next record
+inline std::map<int, FILE*>& F_units() { static std::map<int, FILE*> u; return u; }
+inline void F_open(int unit, const char* name) {
+  FILE* f = fopen(name, "r");
+  if (!f) { fprintf(stderr, "f90rt: cannot open %s\n", name); abort(); }
+  F_units()[unit] = f;
+}
+inline void F_close(int unit) { fclose(F_units()[unit]); F_units().erase(unit); }
+struct F_Read {
+  FILE* f;
+  explicit F_Read(int unit) : f(F_units()[unit]) {}
+  ~F_Read() { int c; while ((c = fgetc(f)) != EOF && c != '\n') {} }
+  std::string token() {
+    int c;
+    while ((c = fgetc(f)) != EOF && (c == ' ' || c == '\t' || c == ',' || c == '\n' || c == '\r')) {}
+    if (c == EOF) { fprintf(stderr, "f90rt: end of file in a READ\n"); abort(); }
+    std::string t;
+    while (c != EOF && c != ' ' && c != '\t' && c != ',' && c != '\n' && c != '\r') { t.push_back(c == 'D' || c == 'd' ? 'E' : (char)c); c = fgetc(f); }
+    if (c != EOF) ungetc(c, f);
+    return t;
+  }
+  void item(int& v) { v = (int)strtol(token().c_str(), nullptr, 10); }
+  void item(double& v) { v = strtod(token().c_str(), nullptr); }  // decimal -> nearest double, as libgfortran's read_real does
+  void item(const Arr4<double>& a) {  // a whole array: its elements in array-element order
+    size_t n = (size_t)a.n1 * a.n2 * a.n3 * a.n4;
+    for (size_t i = 0; i < n; ++i) item(a.p[i]);
+  }
+};
 template <class T> T& F_tmp(T&& v) { return v; }
 template <class T> T& F_tmp(T& v) { return v; }
 template <class T> void F_move_alloc(T& from, T& to) { to = from; to.allocated = true; from = T(); }

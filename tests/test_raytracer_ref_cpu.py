@@ -261,3 +261,88 @@ def test_whole_rays_through_the_translated_gridded_path():
     for r in range(len(w0)):
         assert_same(R, o, pos0[r], [0, 0, 0], w0[r], dict(common.C2, maxsteps=250), "grid ray %d" % r)
     del keep
+
+
+def state_of(get, *head):
+    """(dims, del3, 13 arrays) of a grid state: the oracle's (orc_grid_state) or the translated setup's (rt_ref_grid_state)"""
+    vp, i, d = C.c_void_p, C.c_int, C.c_double
+    dims, del3, ptrs = (i * 4)(), (d * 3)(), (vp * 13)()
+    get.argtypes = [vp] * (len(head) + 3)
+    get(*head, dims, del3, ptrs)
+    ns, nx, ny, nz = dims
+    sizes = [ns, ns, nx, ny, nz] + [ns * nx * ny * nz] * 8
+    arrs = [np.ctypeslib.as_array(C.cast(ptrs[k], C.POINTER(d)), (sizes[k],)).copy() for k in range(13)]
+    return list(dims), np.array(del3), arrs
+
+
+def translated_setup(path, yearday=2010001, msec=0, use_igrf=1, use_tsy=0):
+    ref_dir = os.path.join(common.ROOT, "oracle", "_ref")
+    if not os.path.exists(os.path.join(ref_dir, "librt_grid_ref.so")):
+        pytest.skip("oracle/_ref/librt_grid_ref.so not built (reference sources absent)")
+    R, X, G, T = (C.CDLL(os.path.join(ref_dir, n)) for n in ("librt_grid_ref.so", "libxform_ref.so", "libgeopack_ref.so", "libts05_ref.so"))
+    vp, i = C.c_void_p, C.c_int
+    fp = lambda f: C.cast(f, vp)  # noqa: E731
+    R.rt_ref_grid_setup.argtypes = [C.c_char_p] + [vp] * 5 + [i] * 4 + [vp]
+    R.rt_ref_grid_setup(path.encode(), fp(X.xform_ref_sm_to_gsm), fp(X.xform_ref_gsm_to_sm), fp(G.geopack_ref_recalc), fp(G.geopack_ref_igrf_gsw),
+                        fp(T.ts05_ref_t04_s), yearday, msec, use_igrf, use_tsy, PARMOD.ctypes.data)
+    R.rt_ref_ngo_plasma.argtypes = [C.c_long, vp, vp]
+    R.rt_ref_use_ngo_adapter.argtypes = [vp]
+    R.rt_ref_run.restype = C.c_long
+    d, l = C.c_double, C.c_long
+    R.rt_ref_run.argtypes = [vp, vp, d, d, d, d, i, d, i, d, i, d, vp, l, vp]
+    return R, (X, G, T)
+
+
+NAMES13 = ["qs", "ms", "x", "y", "z", "f", "dfdx", "dfdy", "dfdz", "d2fdxdy", "d2fdxdz", "d2fdydz", "d3fdxdydz"]
+
+
+def test_setup_of_the_interp_adapter_from_the_translated_source():
+    """the grid file reader, the node coordinates and tricubic_compute_finite_difference_derivatives (a16's set-up half, row f3's
+    derivative build): the oracle's state == the state the translated `setup` leaves, every array bit for bit"""
+    o = ol.OracleModel("grid", GRID13, 2010001, 0, 1, libm=True)
+    R, keep = translated_setup(GRID13)
+    da, ea, A = state_of(o.L.orc_grid_state, o.h)
+    db, eb, B = state_of(R.rt_ref_grid_state)
+    assert da == db == [4, 13, 13, 13]
+    assert np.array_equal(ea.view(np.uint64), eb.view(np.uint64))
+    for name, a, b in zip(NAMES13, A, B):
+        assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), name
+    assert all(np.abs(a).max() > 0 for a in A[5:])
+
+
+def test_setup_with_the_derivatives_in_the_file(tmp_path):
+    """computederivatives = 1: the seven arrays are read from the file in array-element order, not computed"""
+    o = ol.OracleModel("grid", GRID13, 2010001, 0, 1, libm=True)
+    dims, del3, A = state_of(o.L.orc_grid_state, o.h)
+    rng = np.random.default_rng(12)
+    given = [a * rng.uniform(0.5, 1.5, a.shape) for a in A[6:]]  # not what finite differences would give
+    path = str(tmp_path / "grid13_with_derivatives.txt")
+    with open(path, "w") as f:
+        f.write("1 %d %d %d %d\n" % tuple(dims))
+        f.write(" ".join("%.17e" % v for v in [A[2][0], A[2][-1], A[3][0], A[3][-1], A[4][0], A[4][-1]]) + "\n")
+        f.write(" ".join("%.17e" % v for v in A[0]) + "\n" + " ".join("%.17e" % v for v in A[1]) + "\n")
+        for row in A[5].reshape(-1, dims[0]):
+            f.write(" ".join("%.17e" % v for v in row) + "\n")
+        for g in given:  # one record each (READ of a whole array), here broken over lines of 5 values
+            for k in range(0, len(g), 5):
+                f.write(" ".join("%.17e" % v for v in g[k:k + 5]) + "\n")
+    o2 = ol.OracleModel("grid", path, 2010001, 0, 1, libm=True)
+    R, keep = translated_setup(path)
+    _, _, A2 = state_of(o2.L.orc_grid_state, o2.h)
+    _, _, B2 = state_of(R.rt_ref_grid_state)
+    for name, a, b in zip(NAMES13, A2, B2):
+        assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), name
+    for g, b in zip(given, B2[6:]):
+        assert np.array_equal(g.view(np.uint64), b.view(np.uint64))
+
+
+def test_whole_rays_from_the_translated_setup_on():
+    """grid file -> translated setup -> translated funcPlasmaParams / libtricubic -> translated raytracer_run: nothing of the oracle on
+    the reference side but the SVD stand-in; rows equal the oracle's bit for bit"""
+    o = ol.OracleModel("grid", GRID13, 2010001, 0, 1, libm=True)
+    R, keep = translated_setup(GRID13)
+    R.rt_ref_use_ngo_adapter(C.cast(o.L.orc_hook_csvd, C.c_void_p))
+    pos0, dir0, w0 = common.launch_grid([800.0, 3000.0, 9000.0], [25.0, 40.0, 55.0])
+    for r in range(len(w0)):
+        assert_same(R, o, pos0[r], [0, 0, 0], w0[r], dict(common.C2, maxsteps=250), "grid ray %d" % r)
+    del keep
