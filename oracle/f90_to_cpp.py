@@ -679,6 +679,7 @@ void rt_ref_solve(const double* k, double w, const double* x, double* k1k2 /* re
   f_SOLVE_DISPERSION_RELATION(vk, w, vx, k1, k2);
   k1k2[0] = k1.real(); k1k2[1] = k1.imag(); k1k2[2] = k2.real(); k1k2[3] = k2.imag();
 }
+int rt_ref_is_right_handed(double n2, double phi, double S, double D, double P) { return f_IS_RIGHT_HANDED(n2, phi, S, D, P) ? 1 : 0; }
 void rt_ref_bmodel_cartesian(const double* x, double* b) {
   Vec<double> vx(3); for (int i = 1; i <= 3; ++i) vx(i) = x[i - 1];
   Vec<double> r = f_BMODEL_CARTESIAN(vx);

@@ -16,8 +16,11 @@
 //   the array semantics a compiler would decide.
 //   The interp adapter's setup (grid file reader, node coordinates, finite-difference
 //   derivatives) is translated too and leaves the state orc_models.h builds, bit for bit.
-//   PARITY UNPINNED: the stand-in for LAPACK's zgesvd (is_right_handed) and the driver's file
-//   formats: pinned only by reference-independent identities (tests/test_oracle_*.py).
+//   csvd = LAPACK's zgesvd (third party, absent from the reference tree): the tests hook the
+//   image's own zgesvd (scipy.linalg.lapack) under the translated is_right_handed and get this
+//   restatement's answers (3000 matrices, whole rays on both roots).
+//   PARITY UNPINNED: the driver's file formats only (restated Fortran edit descriptors, pinned
+//   by frozen fixtures).
 //
 // Elementary functions: by default the oracle uses the same srt_math.h layer
 // as the device (so GPU == oracle is a bitwise statement).  Compile with

@@ -346,3 +346,79 @@ def test_whole_rays_from_the_translated_setup_on():
     for r in range(len(w0)):
         assert_same(R, o, pos0[r], [0, 0, 0], w0[r], dict(common.C2, maxsteps=250), "grid ray %d" % r)
     del keep
+
+
+# ---- the last stand-in: LAPACK's zgesvd itself (scipy carries it) as the reference's csvd
+
+def lapack_csvd_hook():
+    """csvd (blas.f95:180-221) = zgesvd('A', 'A', ...) with the optimal workspace: scipy.linalg.lapack.zgesvd is that LAPACK routine
+    (compute_uv = 1, full_matrices = 1 -> JOBU = JOBVT = 'A'), here as the hook the translated is_right_handed calls"""
+    lapack = pytest.importorskip("scipy.linalg.lapack")
+    calls = [0]
+
+    @C.CFUNCTYPE(None, C.POINTER(C.c_double), C.POINTER(C.c_double))
+    def cb(m_re_im, vt_re_im):
+        a = np.ctypeslib.as_array(m_re_im, (18,)).copy()
+        M = (a[0::2] + 1j * a[1::2]).reshape(3, 3, order="F")
+        u, sv, vt, info = lapack.zgesvd(M, compute_uv=1, full_matrices=1)
+        assert info == 0
+        calls[0] += 1
+        flat = np.asarray(vt).reshape(-1, order="F")
+        out = np.ctypeslib.as_array(vt_re_im, (18,))
+        out[0::2], out[1::2] = flat.real, flat.imag
+    return cb, calls
+
+
+def test_handedness_with_lapack_zgesvd_under_the_translated_source(ref):
+    """a11: translated form_dispersion_matrix + is_right_handed (raytracer.f95:355-405) calling LAPACK's zgesvd == the oracle's
+    stand-in (complex one-sided Jacobi), on the matrices the path meets: n2 a root of the dispersion relation (the null space is
+    one-dimensional there) for random Stix parameters and angles, and off-root n2 as well"""
+    cb, calls = lapack_csvd_hook()
+    L = ol.lib()
+    ref.rt_ref_set_hooks(None, C.cast(cb, C.c_void_p))
+    d = C.c_double
+    ref.rt_ref_is_right_handed.argtypes = [d] * 5
+    L.orc_is_right_handed.argtypes = [d] * 5
+    rng = np.random.default_rng(21)
+    n, skipped = 0, 0
+    for k in range(3000):
+        S, D, P = rng.uniform(-50, 50), rng.uniform(-200, 200), -10 ** rng.uniform(1, 6)
+        phi = rng.uniform(0.0, np.pi / 2) if k % 2 else rng.uniform(0, 90)  # the caller passes radians; larger arguments exercise the same code
+        if k % 3:  # a root of A n^4 - B n^2 + R L P = 0 (raytracer.f95:466-478)
+            Rr, Ll = S + D, S - D
+            A = S * np.sin(phi) ** 2 + P * np.cos(phi) ** 2
+            B = Rr * Ll * np.sin(phi) ** 2 + P * S * (1 + np.cos(phi) ** 2)
+            disc = B * B - 4 * A * Rr * Ll * P
+            if disc < 0 or A == 0:
+                continue
+            n2 = (B + (1 if k % 2 else -1) * np.sqrt(disc)) / (2 * A)
+        else:
+            n2 = 10 ** rng.uniform(-1, 4)
+        a, b = ref.rt_ref_is_right_handed(n2, phi, S, D, P), L.orc_is_right_handed(n2, phi, S, D, P)
+        if a != b:  # only where the smallest singular value is not isolated is the vector (and so the answer) undefined
+            sv = np.linalg.svd(_dispersion_matrix(n2, phi, S, D, P), compute_uv=False)
+            assert sv[2] > 0.9 * sv[1] or sv[1] == 0, (n2, phi, S, D, P, sv)
+            skipped += 1
+        n += 1
+    print("handedness with LAPACK zgesvd: %d matrices, %d with a degenerate null space" % (n, skipped))
+    assert n > 2000 and skipped < 0.01 * n and calls[0] >= n
+
+
+def _dispersion_matrix(n2, phi, S, D, P):
+    s, c = np.sin(phi), np.cos(phi)
+    return np.array([[S - n2 * c * c, -1j * D, n2 * c * s], [1j * D, S - n2, 0], [n2 * c * s, 0, P - n2 * s * s]])
+
+
+def test_whole_rays_with_lapack_zgesvd_and_translated_sources_only(ref):
+    """Ngo input file -> translated readinput / adapter / density model / coordinate chain / Geopack / integrator, LAPACK's zgesvd
+    as csvd: NOTHING of the oracle on the reference side.  Rows equal the oracle's bit for bit, both roots."""
+    cb, calls = lapack_csvd_hook()
+    keep = full_chain(ref, common.NGO_CFG, 2010001, 0, 1, 0)
+    ref.rt_ref_use_ngo_adapter(C.cast(cb, C.c_void_p))
+    o = ol.OracleModel("ngo", common.NGO_CFG, 2010001, 0, 1, libm=True)
+    pos0, dir0, w0 = common.c2_grid(3, 3)
+    for root in (1, 2):
+        for k in range(len(w0)):
+            assert_same(ref, o, pos0[k], dir0[k], w0[k], dict(common.C2, maxsteps=80, root=root), "root %d ray %d" % (root, k))
+    assert calls[0] >= 2 * len(w0)
+    del keep
