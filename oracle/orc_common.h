@@ -16,7 +16,7 @@
 //   the array semantics a compiler would decide.
 //   The interp adapter's setup (grid file reader, node coordinates, finite-difference
 //   derivatives) is translated too and leaves the state orc_models.h builds, bit for bit.
-//   csvd = LAPACK's zgesvd (third party, absent from the reference tree): the tests hook the
+//   csvd = LAPACK's zgesvd (vendored by the reference as lapack-3.2.1, not translated): the tests hook the
 //   image's own zgesvd (scipy.linalg.lapack) under the translated is_right_handed and get this
 //   restatement's answers (3000 matrices, whole rays on both roots).
 //   PARITY UNPINNED: the driver's file formats only (restated Fortran edit descriptors, pinned
