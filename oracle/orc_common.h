@@ -19,8 +19,9 @@
 //   csvd = LAPACK's zgesvd (vendored by the reference as lapack-3.2.1, not translated): the tests hook the
 //   image's own zgesvd (scipy.linalg.lapack) under the translated is_right_handed and get this
 //   restatement's answers (3000 matrices, whole rays on both roots).
-//   PARITY UNPINNED: the driver's file formats only (restated Fortran edit descriptors, pinned
-//   by frozen fixtures).
+//   PARITY UNPINNED: the digit generation of the driver's Fortran edit descriptors and its
+//   list-directed ray input only (the record layout is read back by the reference's own
+//   read_rayfile, _ref/libwipp_read.so).
 //
 // Elementary functions: by default the oracle uses the same srt_math.h layer
 // as the device (so GPU == oracle is a bitwise statement).  Compile with

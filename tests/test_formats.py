@@ -155,3 +155,47 @@ def test_read_output_round_trip(tmp_path):
                                       got[k]["w"], got[k]["qs"], got[k]["ms"], got[k]["nus"][i])
                    for k in got for i in range(len(got[k]["time"])))
     assert text == p.read_text()
+
+
+def test_output_rows_through_the_references_own_reader(built, tmp_path):
+    """f2 / a22: the product's native writer of output.ray, read by the REFERENCE'S OWN consumer of that format --
+    read_rayfile of damping/src/wipp_fileutils.cpp, compiled where it lies into oracle/_ref/libwipp_read.so -- gives back every
+    field in its place (ray number, stop code, time, pos, vprel, vgrel, n, B0, w, nspec, qs, ms, Ns, nus), to the 16 digits the
+    record carries."""
+    import ctypes as C
+    import os
+
+    import pytest
+
+    import common
+    import stanford_raytracer_b200 as srt
+    lib = os.path.join(common.ROOT, "oracle", "_ref", "libwipp_read.so")
+    if not os.path.exists(lib):
+        pytest.skip("oracle/_ref/libwipp_read.so not built (reference sources absent)")
+    W = C.CDLL(lib)
+    W.wipp_read_ray.restype = C.c_long
+    W.wipp_read_ray.argtypes = [C.c_char_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_long]
+    rng = np.random.default_rng(15)
+    for nspec in (4, 2):
+        qs = [-1.602e-19, 1.602e-19, 1.602e-19, 1.602e-19][:nspec]
+        ms = [9.10938188e-31, 1.6726e-27, 6.6904e-27, 2.67616e-26][:nspec]
+        nus = [0.0, 1.5, 2.5e3, 1e-7][:nspec]
+        rays = {3: (1, 41), 17: (6, 7), 1200: (0, 1)}
+        path = str(tmp_path / ("out%d.ray" % nspec))
+        want = {}
+        with open(path, "wb") as f:
+            for raynum, (stop, nrows) in rays.items():
+                rows = np.exp(rng.uniform(-30, 30, (nrows, 20))) * rng.choice([-1.0, 1.0], (nrows, 20))
+                w = float(rng.uniform(1e3, 1e5))
+                f.write(srt.format_rows(raynum, stop, rows, w, qs, ms, nus))
+                want[raynum] = (stop, rows, w)
+        digits16 = lambda a: np.array([float("%.15E" % v) for v in np.ravel(a)]).reshape(np.shape(a))  # noqa: E731
+        for raynum, (stop, rows, w) in want.items():
+            head, qm, got = np.zeros(5), np.zeros(2 * nspec), np.zeros((len(rows) + 3, 16 + 2 * nspec))
+            n = W.wipp_read_ray(path.encode(), raynum, head.ctypes.data, qm.ctypes.data, got.ctypes.data, len(got))
+            assert n == len(rows) and head[0] == len(rays) and head[1] == len(rows) and head[2] == nspec and head[3] == stop
+            assert head[4] == digits16([w])[0]
+            assert np.array_equal(qm, digits16(qs + ms))
+            assert np.array_equal(got[:n, :16], digits16(rows[:, :16]))
+            assert np.array_equal(got[:n, 16:16 + nspec], digits16(rows[:, 16:16 + nspec]))
+            assert np.array_equal(got[:n, 16 + nspec:], np.tile(digits16(nus), (n, 1)))
