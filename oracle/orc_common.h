@@ -16,9 +16,9 @@
 //   the array semantics a compiler would decide.
 //   The interp adapter's setup (grid file reader, node coordinates, finite-difference
 //   derivatives) is translated too and leaves the state orc_models.h builds, bit for bit.
-//   csvd = LAPACK's zgesvd (vendored by the reference as lapack-3.2.1, not translated): the tests hook the
-//   image's own zgesvd (scipy.linalg.lapack) under the translated is_right_handed and get this
-//   restatement's answers (3000 matrices, whole rays on both roots).
+//   csvd = zgesvd of the LAPACK 3.2.1 the reference vendors: translated as well
+//   (lapack_to_cpp.py -> _ref/liblapack_ref.so) and hooked under the translated is_right_handed,
+//   it gives this restatement's answers (20 000 matrices, whole rays on both roots).
 //   PARITY UNPINNED: the digit generation of the driver's Fortran edit descriptors and its
 //   list-directed ray input only (the record layout is read back by the reference's own
 //   read_rayfile, _ref/libwipp_read.so).

@@ -369,6 +369,92 @@ def lapack_csvd_hook():
     return cb, calls
 
 
+def vendored_lapack():
+    """oracle/_ref/liblapack_ref.so: zgesvd and the routines under it from the LAPACK 3.2.1 the reference vendors (lapack-3.2.1/) and
+    links, translated by oracle/lapack_to_cpp.py"""
+    path = os.path.join(ol.ORC_DIR, "_ref", "liblapack_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/liblapack_ref.so not built (reference sources absent)")
+    L = C.CDLL(path)
+    L.lapack_ref_csvd3.argtypes = [C.c_void_p] * 4
+    L.lapack_ref_csvd3.restype = C.c_int
+    return L
+
+
+def test_translated_lapack_321_against_the_compiled_zgesvd():
+    """the translation of the vendored zgesvd itself: singular values equal those of the image's compiled LAPACK (a later version)
+    to the last digits, U S VT reconstructs the matrix, and every row of VT equals the compiled routine's up to the sign the two
+    versions' Householder / rotation conventions leave open"""
+    lapack = pytest.importorskip("scipy.linalg.lapack")
+    L = vendored_lapack()
+    rng = np.random.default_rng(31)
+    signs = set()
+    for k in range(1500):
+        M = rng.normal(size=(3, 3)) * 10.0 ** rng.uniform(-3, 3) + 1j * rng.normal(size=(3, 3))
+        if k % 3 == 0:
+            M[:, 2] = M[:, 0] * (1 + 1e-9 * k) + 1e-8 * M[:, 1]  # nearly singular, as a dispersion matrix at its root
+        flat = M.reshape(-1, order="F")
+        a, s, u, vt = np.zeros(18), np.zeros(3), np.zeros(18), np.zeros(18)
+        a[0::2], a[1::2] = flat.real, flat.imag
+        assert L.lapack_ref_csvd3(a.ctypes.data, s.ctypes.data, u.ctypes.data, vt.ctypes.data) == 0
+        U, VT = ((x[0::2] + 1j * x[1::2]).reshape(3, 3, order="F") for x in (u, vt))
+        u2, s2, vt2, info = lapack.zgesvd(M, compute_uv=1, full_matrices=1)
+        assert np.abs(s - s2).max() <= 4e-15 * s2[0]
+        assert np.abs(U @ np.diag(s) @ VT - M).max() <= 1e-13 * s2[0]
+        if s2[2] < 0.999 * s2[1] < 0.998 * s2[0]:  # distinct singular values: the vectors are defined up to a unit factor
+            for i in range(3):
+                p = np.vdot(vt2[i], VT[i])
+                assert abs(abs(p) - 1) < 1e-7 and abs(p.imag) < 1e-7, (k, i, p)
+                signs.add(int(np.sign(p.real)))
+    assert signs == {1, -1}  # the two LAPACK versions do differ in sign conventions: the handedness decision must not (and does not) care
+
+
+def test_handedness_with_the_vendored_lapack_under_the_translated_source(ref):
+    """a11 end to end in the reference's own code: translated form_dispersion_matrix + is_right_handed (raytracer.f95:355-405)
+    calling the translated zgesvd of the vendored LAPACK 3.2.1 == the oracle's handedness, on and off the roots"""
+    V = vendored_lapack()
+    L = ol.lib()
+    ref.rt_ref_set_hooks(None, C.cast(V.lapack_ref_csvd_hook, C.c_void_p))
+    d = C.c_double
+    ref.rt_ref_is_right_handed.argtypes = [d] * 5
+    L.orc_is_right_handed.argtypes = [d] * 5
+    rng = np.random.default_rng(22)
+    n = 0
+    for k in range(20000):
+        S, D, P = rng.uniform(-50, 50), rng.uniform(-200, 200), -10 ** rng.uniform(1, 6)
+        phi = rng.uniform(0.0, np.pi / 2)
+        if k % 3:
+            Rr, Ll = S + D, S - D
+            A = S * np.sin(phi) ** 2 + P * np.cos(phi) ** 2
+            B = Rr * Ll * np.sin(phi) ** 2 + P * S * (1 + np.cos(phi) ** 2)
+            disc = B * B - 4 * A * Rr * Ll * P
+            if disc < 0 or A == 0:
+                continue
+            n2 = (B + (1 if k % 2 else -1) * np.sqrt(disc)) / (2 * A)
+        else:
+            n2 = 10 ** rng.uniform(-1, 4)
+        a, b = ref.rt_ref_is_right_handed(n2, phi, S, D, P), L.orc_is_right_handed(n2, phi, S, D, P)
+        if a != b:
+            sv = np.linalg.svd(_dispersion_matrix(n2, phi, S, D, P), compute_uv=False)
+            assert sv[2] > 0.9 * sv[1] or sv[1] == 0, (n2, phi, S, D, P, sv)
+        n += 1
+    assert n > 15000
+
+
+def test_whole_rays_in_the_references_own_code_only(ref):
+    """Ngo input file -> translated readinput / adapter / density model / coordinate chain / Geopack / integrator / vendored LAPACK:
+    every line executed on the reference side is the reference's (translated).  Rows equal the oracle's bit for bit, both roots."""
+    V = vendored_lapack()
+    keep = full_chain(ref, common.NGO_CFG, 2010001, 0, 1, 0)
+    ref.rt_ref_use_ngo_adapter(C.cast(V.lapack_ref_csvd_hook, C.c_void_p))
+    o = ol.OracleModel("ngo", common.NGO_CFG, 2010001, 0, 1, libm=True)
+    pos0, dir0, w0 = common.c2_grid(3, 3)
+    for root in (1, 2):
+        for k in range(len(w0)):
+            assert_same(ref, o, pos0[k], dir0[k], w0[k], dict(common.C2, maxsteps=80, root=root), "root %d ray %d" % (root, k))
+    del keep
+
+
 def test_handedness_with_lapack_zgesvd_under_the_translated_source(ref):
     """a11: translated form_dispersion_matrix + is_right_handed (raytracer.f95:355-405) calling LAPACK's zgesvd == the oracle's
     stand-in (complex one-sided Jacobi), on the matrices the path meets: n2 a root of the dispersion relation (the null space is
