@@ -193,8 +193,10 @@ int64_t srt_format_rows(int64_t raynum, int stopcond, const double* rows /*[nrow
  * from first_raynum).  nthreads workers format, the caller's thread writes; nthreads <= 0: all host cores. */
 int srt_result_write_text(const srt_result* r, const srt_model* m, const double* w0 /*[nrays]*/, const char* path, int64_t first_raynum,
                           int append, int nthreads);
-/* inputraysfile (driver:1146): list-directed `pos0(3) dir0(3) w` per ray; stops at the first record that does not
- * parse.  The three arrays are allocated by the library: release each with srt_free. */
+/* inputraysfile (fortran/raytracer_driver.f95:1140-1150): the loop `read(infile,*,iostat=status) pos0, dir0, w` under gfortran's
+ * list-directed rules (blank / comma / semicolon separators, records continuing, null values keeping the previous READ's value,
+ * r*c and r*, `/` ending a READ, D / Q exponents, 1.5+3, INF / NAN); stops at the first token that is not a number or at the end
+ * of the file.  The three arrays are allocated by the library: release each with srt_free. */
 int srt_read_inputrays(const char* path, double** pos0 /*[n][3]*/, double** dir0 /*[n][3]*/, double** w0 /*[n]*/, int64_t* nrays);
 void srt_free(void* p);
 

@@ -19,9 +19,9 @@
 //   csvd = zgesvd of the LAPACK 3.2.1 the reference vendors: translated as well
 //   (lapack_to_cpp.py -> _ref/liblapack_ref.so) and hooked under the translated is_right_handed,
 //   it gives this restatement's answers (20 000 matrices, whole rays on both roots).
-//   PARITY UNPINNED: the digit generation of the driver's Fortran edit descriptors and its
-//   list-directed ray input only (the record layout is read back by the reference's own
-//   read_rayfile, _ref/libwipp_read.so).
+//   The driver's file formats are not restated here at all: the product's writer and reader
+//   are compared with gfortran's own run-time library executing the driver's READ / WRITE
+//   statements (ref_stubs/gfortran_io_shim.c, tests/test_formats_gfortran.py).
 //
 // Elementary functions: by default the oracle uses the same srt_math.h layer
 // as the device (so GPU == oracle is a bitwise statement).  Compile with

@@ -11,40 +11,90 @@ import re
 
 import numpy as np
 
-_SEP = re.compile(r"[,\s]+")
+_NUMBER = re.compile(r"^([+-]?)(\d+\.?\d*|\.\d+)(?:[EDQedq]([+-]?\d+)|([+-]\d+))?$")
+_INFNAN = re.compile(r"^([+-]?)(inf|infinity|nan|nan\([^)]*\))$", re.IGNORECASE)
+_BLANK = " \t\r\n"
+_END = _BLANK + ",;/"
 
 
 def _fortran_float(tok):
-    t = tok.strip().lower().replace("d", "e")
-    # Fortran accepts 1.0+5 as 1.0e+5
-    m = re.match(r"^([+-]?(\d+\.?\d*|\.\d+))([+-]\d+)$", t)
+    """One value of a list-directed READ into a REAL item, as gfortran's run-time library accepts it: digits with an optional
+    point, an exponent E|D|Q [sign] digits or just sign digits (1.5+3), or INF / INFINITY / NAN / NAN(...) in any case."""
+    tok = tok.strip(" ")  # (fixed-width fields of read_output come with their padding)
+    m = _NUMBER.match(tok)
     if m:
-        t = m.group(1) + "e" + m.group(3)
-    return float(t)
+        exp = m.group(3) or m.group(4)
+        return float(m.group(1) + m.group(2) + ("e" + exp if exp else ""))
+    m = _INFNAN.match(tok)
+    if not m:
+        raise ValueError(tok)
+    if m.group(2).lower().startswith("nan"):
+        return float("nan")
+    return float("-inf") if m.group(1) == "-" else float("inf")
 
 
 def read_inputrays(path):
-    """Returns pos0[n][3], dir0[n][3], w[n].  A READ takes seven items, continuing over records if it has to, and
-    drops what is left of the record it ends in; the first item that is not a number ends the file (iostat /= 0).
+    """Returns pos0[n][3], dir0[n][3], w[n]: the driver's loop `read(infile,*,iostat=status) pos0, dir0, w` under gfortran's
+    list-directed rules.  Values are separated by blanks (tab, CR, end of record), one comma or semicolon, or a slash, which ends
+    the READ; nothing between two separators is a null value and leaves the item as the previous READ left it (zeros at first);
+    r*c is r copies, r* is r nulls; a READ takes records until its seven items are served and drops the rest of the record it ends
+    in; the first token that is not a number, or the end of the file inside a READ, ends the loop.
     Pure-Python statement of the library's srt_read_inputrays (csrc/srt_io.cpp)."""
-    vals = []
-    toks = []
+    with open(path, "rb") as f:
+        text = f.read().decode("latin-1")
+    vals, cur, p, n = [], [0.0] * 7, 0, 0
+    n = len(text)
     stop = False
-    with open(path) as f:
-        for line in f:
-            for t in _SEP.split(line.strip()):
-                if not t:
-                    continue
-                toks.append(t)
-                if len(toks) == 7:
-                    try:
-                        vals.append([_fortran_float(x) for x in toks])
-                    except ValueError:
-                        stop = True
-                    toks = []
-                    break  # rest of the record is dropped
-            if stop:
+    while not stop:
+        idx, expecting, slash = 0, True, False
+        while idx < 7 and not stop and not slash:
+            while p < n and text[p] in _BLANK:
+                p += 1
+            if p >= n:
+                stop = True
                 break
+            c = text[p]
+            if c in ",;":
+                p += 1
+                if expecting:
+                    idx += 1
+                else:
+                    expecting = True
+                continue
+            if c == "/":
+                p += 1
+                slash = True
+                break
+            q = p
+            while q < n and text[q] not in _END:
+                q += 1
+            tok, p, rep = text[p:q], q, 1
+            m = re.match(r"^(\d+)\*(.*)$", tok, re.DOTALL)
+            if m:
+                rep, tok = int(m.group(1)), m.group(2)
+                if rep == 0:
+                    stop = True
+                    break
+                if tok == "":
+                    idx += min(rep, 7)
+                    expecting = False
+                    continue
+            try:
+                v = _fortran_float(tok)
+            except ValueError:
+                stop = True
+                break
+            while rep > 0 and idx < 7:
+                cur[idx] = v
+                idx += 1
+                rep -= 1
+            expecting = False
+        if stop:
+            break
+        vals.append(list(cur))
+        while p < n and text[p] != "\n":
+            p += 1
+        p += 1
     a = np.array(vals, dtype=np.float64).reshape(-1, 7)
     return a[:, 0:3].copy(), a[:, 3:6].copy(), a[:, 6].copy()
 

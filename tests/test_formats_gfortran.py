@@ -1,0 +1,135 @@
+"""The driver's file formats against gfortran's OWN run-time library.
+
+The reference is built with gfortran: its output.ray is what libgfortran's formatted WRITE produces for i10 / es24.15e3, its ray file
+is what libgfortran's list-directed READ accepts (fortran/raytracer_driver.f95:1140-1217).  libgfortran.so.5 travels in the image's
+numpy / scipy wheels; oracle/ref_stubs/gfortran_io_shim.c issues the calls gfortran emits for those statements.  The product's
+native formatter, writer and reader (csrc, through the C ABI) must agree with it byte for byte / value for value."""
+import ctypes as C
+import glob
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import common
+import oracle_lib as ol
+from stanford_raytracer_b200 import rayfile
+
+
+@pytest.fixture(scope="module")
+def gf():
+    libs = sorted(p for d in sys.path if d.endswith("site-packages") for p in glob.glob(os.path.join(d, "scipy.libs", "libgfortran*.so*")))
+    if not libs:
+        pytest.skip("no libgfortran in the image's wheels")
+    ol.build()
+    G = C.CDLL(os.path.join(ol.ORC_DIR, "_build", "libgfio.so"))
+    G.gfio_open_lib.argtypes = [C.c_char_p]
+    if G.gfio_open_lib(libs[0].encode()) != 0:
+        pytest.skip("libgfortran does not export the GFORTRAN_8 I/O entry points")
+    G.gfio_write_es.argtypes = [C.c_double, C.c_char_p]
+    G.gfio_write_rayfile.argtypes = [C.c_char_p, C.c_long, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    G.gfio_read_rays.argtypes = [C.c_char_p, C.c_void_p, C.c_long]
+    G.gfio_read_rays.restype = C.c_long
+    return G
+
+
+@pytest.fixture(scope="module")
+def srt(built):
+    import stanford_raytracer_b200 as s
+    return s
+
+
+def awkward():
+    rng = np.random.default_rng(41)
+    v = [0.0, -0.0, 1.0, -1.0, 9.9999999999999995e-8, 9.999999999999999e22, 1e23, 5e-324, 2.2250738585072014e-308, 1.7976931348623157e308,
+         0.1, 0.5, 1.5, 2.5, 1.0000000000000002, 9.999999999999995, 9.9999999999999995, 1.2345678901234565, 1.2345678901234575,
+         float("inf"), float("-inf"), float("nan"), 7.3712e6, -1.602e-19, 8.854187817e-12, 299792458.0, 123456789012345.5, 1e100, 1e-100, 1e-99, 9.5e99]
+    v += list(np.ldexp(rng.uniform(0.5, 1.0, 4000), rng.integers(-1070, 1023, 4000)) * rng.choice([-1.0, 1.0], 4000))
+    v += list(np.round(rng.uniform(1, 10, 2000), 15) * 10.0 ** rng.integers(-300, 300, 2000))  # decimals with at most 16 digits: ties and near-ties
+    v += [float("%d.%015d5e%d" % (rng.integers(1, 10), rng.integers(0, 10 ** 15), rng.integers(-200, 200))) for _ in range(2000)]  # a 17th digit 5
+    return np.array(v, dtype=np.float64)
+
+
+def test_es24_15e3_digit_generation(gf, srt):
+    v = awkward()
+    mine = srt.format_es24(v)
+    buf = C.create_string_buffer(25)
+    for x, m in zip(v, mine):
+        gf.gfio_write_es(float(x), buf)
+        want = buf.raw[:24].decode()
+        assert m == want, (repr(float(x)), m, want)
+        assert rayfile.es24(float(x)) == want, (repr(float(x)), rayfile.es24(float(x)), want)
+
+
+def test_output_file_byte_for_byte(gf, srt, tmp_path):
+    """the driver's output loop run by libgfortran == the product's writer, whole files (2, 3 and 4 species; ray numbers beyond i10)"""
+    rng = np.random.default_rng(42)
+    for nspec in (4, 3, 2):
+        qs = [-1.602e-19, 1.602e-19, 1.602e-19, 1.602e-19][:nspec]
+        ms = [9.10938188e-31, 1.6726e-27, 6.6904e-27, 2.67616e-26][:nspec]
+        nus = [0.0, 1.5, 2.5e3, 1e-7][:nspec]
+        chunks, head, v17, sp = [], [], [], []
+        for raynum, stop, nrows in ((1, 0, 30), (2, 6, 1), (99999, 3, 12), (2147483647, 1, 2), (-5, 2, 1)):
+            rows = np.exp(rng.uniform(-60, 60, (nrows, 20))) * rng.choice([-1.0, 1.0], (nrows, 20))
+            rows[0, 16:] = [0.0, np.nan, np.inf, -np.inf]
+            w = float(rng.uniform(1e3, 1e5))
+            chunks.append(srt.format_rows(raynum, stop, rows, w, qs, ms, nus))
+            for r in rows:
+                head.append([raynum, stop])
+                v17.append(list(r[:16]) + [w])
+                sp.append(qs + ms + list(r[16:16 + nspec]) + nus)
+        head, v17, sp = np.array(head, dtype=np.int32), np.array(v17), np.array(sp)
+        path = str(tmp_path / ("gf%d.ray" % nspec))
+        gf.gfio_write_rayfile(path.encode(), len(head), head.ctypes.data, v17.ctypes.data, nspec, sp.ctypes.data)
+        want = open(path, "rb").read()
+        got = b"".join(chunks)
+        assert len(want) == len(head) * (20 + 17 * 24 + 10 + 4 * nspec * 24 + 1)
+        assert got == want
+
+
+RAY_FILES = {
+    "plain": "1.0E007 0.0 0.0 0.0 0.0 1.0 6.28e4\n7.3712d6 0 0 0 0 0 12566.37\n",
+    "commas_tabs_trailing": " 7.3712d6, 0, 0, 0 0 0 12566.37 trailing ignored\n\t1.5+3,2,3,4,5,6,7\r\n1\t2\t3\t4\t5\t6\t7\n",
+    "records_continue": "5 5 5\n 1 0 0 100 200 300\n8 8 8\n\n\n 0 0 1\n 42\n",
+    "blank_lines_between": "\n\n1 2 3 4 5 6 7\n\n   \n8 9 10 11 12 13 14\n\n",
+    "bad_token_stops": "1 2 3 4 5 6 7\nbad line stops reading\n9 9 9 0 0 1 7\n",
+    "short_last_record": "1 2 3 4 5 6 7\n8 9 10\n",
+    "no_final_newline": "1 2 3 4 5 6 7\n7 6 5 4 3 2 1",
+    "more_than_seven": " 1 2 3 4 5 6 7 8 9 10 11 12 13 14\n1,2,3,4,5,6,7,8\n9 9 9 9 9 9 9\n",
+    "repeat_counts": "3*1.5 3*0 7\n1 2 3 4 5 6 7\n9*2\n1 2*3 4 5 6 7 8\n",
+    "repeat_nulls": "1 1 1 1 1 1 1\n2* 3 4 5 6 7\n2*,8 4 5 6 7 8\n2*1 2* 2*3 4\n",
+    "null_values": "1 2 3 4 5 6 7\n8,,10 11 12 13 14\n,2 3 4 5 6 7\n1 2 3 ,, , 6 7 8\n1 2 3,\n,4 5 6 7 8\n1;;3 4 5 6 7\n;2 3 4 5 6 7\n",
+    "semicolons": "1;2;3;4;5;6;7\n1 2 3 4 5 6 7;8\n",
+    "slash_ends_a_read": "1 2 3 4 5 6 7\n1 2 3 / 9 9 9 9\n5 5 5 5 5 5 5\n/\n1 2 3 4 5 6 7 /\n1 2 3 4 5 6 7/\n1 2 3 4 5 6/7\n8 8 8 8 8 8 8\n",
+    "number_forms": "+.5 -.5e-1 1d+3 1.D+3 1.E3 1.e-3 .5\n+1.e3 -.5 1d-3 1.5e+3 2.E-2 -0 +7\n1q2 1.5-3 1+5 5. +5.e1 1e+0003 1E5\n",
+    "inf_and_nan": "1 2 3 4 5 6 inf\n-Infinity nan 1 1 1 1 +NaN\n+inf INF NaN nan(abc) -nan 1 1\n",
+    "rounding": "12345678901234567890123 0.1000000000000000055511151231257827 1e400 1e-400 4.9e-324 2.4703282292062328e-324 9007199254740993\n",
+    "value_then_comment": "1 2 3 4 5 6 7 ! c\n2 2 2 2 2 2 2\n",
+    "value_then_split_exponent": "1 2 3 4 5 6 1 e5\n1 2 3 4 5 6 1,5\n",
+    "empty": "",
+}
+# each of these ends the loop at once (iostat > 0): nothing is read
+for _k, _t in enumerate(["1e", ".", "+", "1e5.3", "0x10", "1_8", "'a'", "T", "7e+", "1.5E 3", "1.5d0d", "--1", "infinit", "nan(abc", ".e3", "*5", "2**3", "1.0*3",
+                         "1-", "1e5e", "(7)", '"7"', "7.5.", "1.5e+3-2", "1.5+3e2", "1e3d2", "infinity5", "in", "na", "0*5", "\x0c4"]):
+    RAY_FILES["bad_%02d" % _k] = "1 2 3 4 5 6 %s\n1 1 1 1 1 1 1\n" % _t
+RAY_FILES["bad_comment_line"] = "! comment\n1 2 3 4 5 6 7\n"
+
+
+@pytest.mark.parametrize("name", sorted(RAY_FILES))
+def test_ray_file_reader_against_list_directed_read(gf, srt, tmp_path, name):
+    """the driver's loop `read(infile,*,iostat=status) pos0, dir0, w` run by libgfortran == the product's reader, ray for ray"""
+    path = tmp_path / (name + ".txt")
+    path.write_bytes(RAY_FILES[name].encode())
+    want = np.zeros((64, 7))
+    n = gf.gfio_read_rays(str(path).encode(), want.ctypes.data, 64)
+    want = want[:n]
+    for reader in (srt.read_inputrays, rayfile.read_inputrays):
+        pos0, dir0, w0 = reader(str(path))
+        got = np.concatenate([pos0, dir0, w0[:, None]], axis=1) if len(w0) else np.zeros((0, 7))
+        assert got.shape == want.shape, (name, reader.__module__, got, want)
+        assert np.array_equal(np.isnan(got), np.isnan(want)), (name, reader.__module__, got, want)
+        a, b = np.where(np.isnan(got), 0.0, got), np.where(np.isnan(want), 0.0, want)
+        assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), (name, reader.__module__, got, want)  # incl. the sign of zero
+    if name == "bad_comment_line" or name[4:6].isdigit():
+        assert n == 0, name
