@@ -8,6 +8,7 @@
 // out), so the product's formatter and ray-file reader are checked against the real digit generation and the real
 // list-directed parser.  The library is opened at run time from the path the test hands in; nothing of it is linked or copied.
 #include <dlfcn.h>
+#include <stddef.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
@@ -35,6 +36,11 @@ enum { HAS_IOSTAT = 1 << 5, DT_LIST_FORMAT = 1 << 7, DT_HAS_FORMAT = 1 << 12, DT
        OPEN_HAS_FILE = 1 << 8, OPEN_HAS_STATUS = 1 << 9 };
 
 static void (*st_write)(dt_t*), (*st_write_done)(dt_t*), (*st_read)(dt_t*), (*st_read_done)(dt_t*), (*st_open)(open_t*), (*st_close)(close_t*);
+// array descriptors of ABI GFORTRAN_8 (libgfortran.h), for _gfortran_matmul_r8
+typedef struct { ptrdiff_t stride, lbound, ubound; } dim_t;
+typedef struct { size_t elem_len; int version; signed char rank, type; short attribute; } dtype_t;
+typedef struct { double* base; size_t offset; dtype_t dtype; ptrdiff_t span; dim_t dim[2]; } desc_t;
+static void (*matmul_r8)(desc_t*, desc_t*, desc_t*, int, int, void*);
 static void (*xfer_real_w)(dt_t*, void*, int), (*xfer_int_w)(dt_t*, void*, int), (*xfer_real)(dt_t*, void*, int), (*xfer_char_w)(dt_t*, void*, size_t);
 
 int gfio_open_lib(const char* path) {
@@ -45,7 +51,8 @@ int gfio_open_lib(const char* path) {
   st_open = dlsym(h, "_gfortran_st_open"); st_close = dlsym(h, "_gfortran_st_close");
   xfer_real_w = dlsym(h, "_gfortran_transfer_real_write"); xfer_int_w = dlsym(h, "_gfortran_transfer_integer_write");
   xfer_real = dlsym(h, "_gfortran_transfer_real"); xfer_char_w = dlsym(h, "_gfortran_transfer_character_write");
-  return (st_write && st_write_done && st_read && st_read_done && st_open && st_close && xfer_real_w && xfer_int_w && xfer_real && xfer_char_w) ? 0 : -2;
+  matmul_r8 = dlsym(h, "_gfortran_matmul_r8");
+  return (matmul_r8 && st_write && st_write_done && st_read && st_read_done && st_open && st_close && xfer_real_w && xfer_int_w && xfer_real && xfer_char_w) ? 0 : -2;
 }
 
 static void open_unit(int unit, const char* path, const char* status) {
@@ -119,4 +126,13 @@ long gfio_read_rays(const char* path, double* out7, long cap) {
   }
   close_unit(60);
   return n;
+}
+
+// c = matmul(A, x), A(m,k) in Fortran order, x(k): the library routine gfortran calls for `a = matmul(Amat, x)` of
+// tricubic_get_coeff_stacked (libtricubic.f95:719: 64 x 64 is above the inlining limit)
+void gfio_matmul_r8(const double* A, const double* x, double* c, int m, int k) {
+  desc_t da = {(double*)A, (size_t)(-1 - m), {8, 0, 2, 3, 0}, 8, {{1, 1, m}, {m, 1, k}}};
+  desc_t db = {(double*)x, (size_t)-1, {8, 0, 1, 3, 0}, 8, {{1, 1, k}, {0, 0, 0}}};
+  desc_t dc = {c, (size_t)-1, {8, 0, 1, 3, 0}, 8, {{1, 1, m}, {0, 0, 0}}};
+  matmul_r8(&dc, &da, &db, 0, 0, 0);
 }

@@ -133,3 +133,27 @@ def test_ray_file_reader_against_list_directed_read(gf, srt, tmp_path, name):
         assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), (name, reader.__module__, got, want)  # incl. the sign of zero
     if name == "bad_comment_line" or name[4:6].isdigit():
         assert n == 0, name
+
+
+def test_q13_the_runtime_matmul_is_machine_dependent(gf):
+    """Q13 (libtricubic.f95:719, `a = matmul(Amat, x)`): gfortran calls libgfortran's matmul_r8, which is built with -ffast-math and
+    picks an AVX / AVX2+FMA / AVX-512 variant at run time: its sums are reassociated and fused per machine.  The oracle and the
+    kernels fix the order (ascending column, unfused).  Recorded here: the library's result on THIS host agrees with that order to
+    a few units of the last place of the sum of magnitudes and, where the CPU has FMA, not bit for bit -- so no fixed order can equal
+    the reference on every machine, and the difference is rounding noise of the coefficient product."""
+    gf.gfio_matmul_r8.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_int]
+    rng = np.random.default_rng(51)
+    differ, total, worst = 0, 0, 0.0
+    for _ in range(100):
+        A = np.asfortranarray(np.where(rng.random((64, 64)) < 0.2, rng.integers(-27, 28, (64, 64)), 0).astype(np.float64))  # as sparse and small-integer as Amat
+        x = rng.uniform(-20, 20, 64)
+        c = np.zeros(64)
+        gf.gfio_matmul_r8(A.ctypes.data, x.ctypes.data, c.ctypes.data, 64, 64)
+        ref = np.zeros(64)
+        for col in range(64):  # ascending column order, one rounding per product and per sum
+            ref = ref + A[:, col] * x[col]
+        differ += int((c.view(np.uint64) != ref.view(np.uint64)).sum())
+        total += 64
+        worst = max(worst, float((np.abs(c - ref) / np.maximum(np.abs(A) @ np.abs(x), 1e-300)).max()))
+    print("libgfortran matmul_r8 on this host: %d of %d results differ in bits from the fixed order; worst |difference| / sum|terms| = %.1e" % (differ, total, worst))
+    assert worst < 2e-15
