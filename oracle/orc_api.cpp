@@ -112,6 +112,9 @@ void orc_hook_csvd(const double* m_re_im, double* vt_re_im) {
 #ifdef ORC_HAVE_GRID
 // the gridded model's state (interpStateData of interp_dens_model_adapter.f95) for the reference's translated adapter + libtricubic:
 // dims = nspec nx ny nz, del3, and pointers to qs, ms, x, y, z, f, dfdx, dfdy, dfdz, d2fdxdy, d2fdxdz, d2fdydz, d3fdxdydz (Fortran order)
+// x**n of tricubic_eval as the oracle evaluates it (orc_grid.h), for the comparison with libgcc's __powidf2 (what gfortran's
+// __builtin_powi becomes) and libgfortran's pow_r8_i4
+double orc_pow_r8_i4(double x, int n) { return pow_r8_i4(x, n); }
 void orc_grid_state(void* mv, int* dims, double* del3, double** ptrs) {
   GridModel* g = (GridModel*)(Model*)mv;
   dims[0] = g->nspec; dims[1] = g->nx; dims[2] = g->ny; dims[3] = g->nz;

@@ -157,3 +157,26 @@ def test_q13_the_runtime_matmul_is_machine_dependent(gf):
         worst = max(worst, float((np.abs(c - ref) / np.maximum(np.abs(A) @ np.abs(x), 1e-300)).max()))
     print("libgfortran matmul_r8 on this host: %d of %d results differ in bits from the fixed order; worst |difference| / sum|terms| = %.1e" % (differ, total, worst))
     assert worst < 2e-15
+
+
+def test_q24_integer_powers_against_libgcc_and_libgfortran(gf):
+    """Q24 (libtricubic.f95:677-679, `x**(i-derx)`): gfortran turns REAL(8)**INTEGER(4) into __builtin_powi = libgcc's __powidf2; other
+    kinds go to libgfortran's pow_r8_i4.  The oracle's restatement equals both, bit for bit, for every exponent the path can meet."""
+    import ctypes.util
+    L = ol.lib()
+    L.orc_pow_r8_i4.restype = C.c_double
+    L.orc_pow_r8_i4.argtypes = [C.c_double, C.c_int]
+    gcc = C.CDLL(ctypes.util.find_library("gcc_s") or "libgcc_s.so.1")
+    gcc.__powidf2.restype = C.c_double
+    gcc.__powidf2.argtypes = [C.c_double, C.c_int]
+    libs = sorted(p for d in sys.path if d.endswith("site-packages") for p in glob.glob(os.path.join(d, "scipy.libs", "libgfortran*.so*")))
+    gfl = C.CDLL(libs[0])
+    gfl._gfortran_pow_r8_i4.restype = C.c_double
+    gfl._gfortran_pow_r8_i4.argtypes = [C.c_double, C.c_int]
+    rng = np.random.default_rng(52)
+    xs = list(rng.uniform(-2, 2, 300)) + list(np.exp(rng.uniform(-200, 200, 100))) + [0.0, -0.0, 1.0, 5e-324, 1e308]
+    for x in xs:
+        for n in range(0, 12):
+            a, b = L.orc_pow_r8_i4(x, n), gcc.__powidf2(x, n)
+            assert np.float64(a).tobytes() == np.float64(b).tobytes(), (x, n, a, b)
+            assert np.float64(a).tobytes() == np.float64(gfl._gfortran_pow_r8_i4(x, n)).tobytes(), (x, n)
