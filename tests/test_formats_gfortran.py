@@ -161,7 +161,7 @@ def test_q13_the_runtime_matmul_is_machine_dependent(gf):
 
 def test_q24_integer_powers_against_libgcc_and_libgfortran(gf):
     """Q24 (libtricubic.f95:677-679, `x**(i-derx)`): gfortran turns REAL(8)**INTEGER(4) into __builtin_powi = libgcc's __powidf2; other
-    kinds go to libgfortran's pow_r8_i4.  The oracle's restatement equals both, bit for bit, for every exponent the path can meet."""
+    kinds go to libgfortran's pow_r8_i8 and the like.  The oracle's restatement equals both, bit for bit, for every exponent the path can meet."""
     import ctypes.util
     L = ol.lib()
     L.orc_pow_r8_i4.restype = C.c_double
@@ -171,12 +171,12 @@ def test_q24_integer_powers_against_libgcc_and_libgfortran(gf):
     gcc.__powidf2.argtypes = [C.c_double, C.c_int]
     libs = sorted(p for d in sys.path if d.endswith("site-packages") for p in glob.glob(os.path.join(d, "scipy.libs", "libgfortran*.so*")))
     gfl = C.CDLL(libs[0])
-    gfl._gfortran_pow_r8_i4.restype = C.c_double
-    gfl._gfortran_pow_r8_i4.argtypes = [C.c_double, C.c_int]
+    gfl._gfortran_pow_r8_i8.restype = C.c_double  # (REAL(8)**INTEGER(4) has no library routine: it is the builtin; this is the INTEGER(8) one)
+    gfl._gfortran_pow_r8_i8.argtypes = [C.c_double, C.c_int64]
     rng = np.random.default_rng(52)
     xs = list(rng.uniform(-2, 2, 300)) + list(np.exp(rng.uniform(-200, 200, 100))) + [0.0, -0.0, 1.0, 5e-324, 1e308]
     for x in xs:
         for n in range(0, 12):
             a, b = L.orc_pow_r8_i4(x, n), gcc.__powidf2(x, n)
             assert np.float64(a).tobytes() == np.float64(b).tobytes(), (x, n, a, b)
-            assert np.float64(a).tobytes() == np.float64(gfl._gfortran_pow_r8_i4(x, n)).tobytes(), (x, n)
+            assert np.float64(a).tobytes() == np.float64(gfl._gfortran_pow_r8_i8(x, n)).tobytes(), (x, n)
