@@ -41,6 +41,7 @@ typedef struct { ptrdiff_t stride, lbound, ubound; } dim_t;
 typedef struct { size_t elem_len; int version; signed char rank, type; short attribute; } dtype_t;
 typedef struct { double* base; size_t offset; dtype_t dtype; ptrdiff_t span; dim_t dim[2]; } desc_t;
 static void (*matmul_r8)(desc_t*, desc_t*, desc_t*, int, int, void*);
+static void (*xfer_int)(dt_t*, void*, int);
 static void (*xfer_real_w)(dt_t*, void*, int), (*xfer_int_w)(dt_t*, void*, int), (*xfer_real)(dt_t*, void*, int), (*xfer_char_w)(dt_t*, void*, size_t);
 
 int gfio_open_lib(const char* path) {
@@ -51,8 +52,8 @@ int gfio_open_lib(const char* path) {
   st_open = dlsym(h, "_gfortran_st_open"); st_close = dlsym(h, "_gfortran_st_close");
   xfer_real_w = dlsym(h, "_gfortran_transfer_real_write"); xfer_int_w = dlsym(h, "_gfortran_transfer_integer_write");
   xfer_real = dlsym(h, "_gfortran_transfer_real"); xfer_char_w = dlsym(h, "_gfortran_transfer_character_write");
-  matmul_r8 = dlsym(h, "_gfortran_matmul_r8");
-  return (matmul_r8 && st_write && st_write_done && st_read && st_read_done && st_open && st_close && xfer_real_w && xfer_int_w && xfer_real && xfer_char_w) ? 0 : -2;
+  matmul_r8 = dlsym(h, "_gfortran_matmul_r8"); xfer_int = dlsym(h, "_gfortran_transfer_integer");
+  return (matmul_r8 && xfer_int && st_write && st_write_done && st_read && st_read_done && st_open && st_close && xfer_real_w && xfer_int_w && xfer_real && xfer_char_w) ? 0 : -2;
 }
 
 static void open_unit(int unit, const char* path, const char* status) {
@@ -135,4 +136,44 @@ void gfio_matmul_r8(const double* A, const double* x, double* c, int m, int k) {
   desc_t db = {(double*)x, (size_t)-1, {8, 0, 1, 3, 0}, 8, {{1, 1, k}, {0, 0, 0}}};
   desc_t dc = {c, (size_t)-1, {8, 0, 1, 3, 0}, 8, {{1, 1, m}, {0, 0, 0}}};
   matmul_r8(&dc, &da, &db, 0, 0, 0);
+}
+
+// the end of dumpmodel.f95 (:1284-1289): write(outfile,'(5i10)') nspec,nx,ny,nz; write(outfile,'(6es24.15e3)') the six limits;
+// write(outfile,'(es24.15e3)') f -- the whole array through a one-item format, so one value per record
+void gfio_write_dump(const char* path, const int* head4, const double* lims6, const double* f, long n) {
+  static dt_t d;
+  open_unit(62, path, "replace");
+  dt_begin(&d, 0, 62, "(5i10)", 0); st_write(&d);
+  for (int k = 0; k < 4; ++k) { int v = head4[k]; xfer_int_w(&d, &v, 4); }
+  st_write_done(&d);
+  dt_begin(&d, 0, 62, "(6es24.15e3)", 0); st_write(&d);
+  for (int k = 0; k < 6; ++k) { double v = lims6[k]; xfer_real_w(&d, &v, 8); }
+  st_write_done(&d);
+  dt_begin(&d, 0, 62, "(es24.15e3)", 0); st_write(&d);
+  for (long i = 0; i < n; ++i) { double v = f[i]; xfer_real_w(&d, &v, 8); }
+  st_write_done(&d);
+  close_unit(62);
+}
+
+// the READ statements of the interp adapter's setup (interp_dens_model_adapter.f95:59-117): header, limits, qs, ms, one READ per
+// node for f(1:nspec, j, k, l), and with computederivatives = 1 seven READs of whole arrays.  f and deriv[7] hold
+// nspec*nx*ny*nz values each.  -> 0, or the iostat of the READ that failed
+int gfio_read_grid(const char* path, int* head5, double* lims6, double* qs, double* ms, double* f, double* deriv, long cap) {
+  static dt_t d;
+  int32_t status = 0;
+  open_unit(63, path, "old");
+#define READ_BEGIN dt_begin(&d, DT_LIST_FORMAT | HAS_IOSTAT, 63, 0, 0); d.common.iostat = &status; st_read(&d)
+#define READ_END st_read_done(&d); if (status != 0) { close_unit(63); return status; }
+  READ_BEGIN; for (int k = 0; k < 5; ++k) xfer_int(&d, &head5[k], 4); READ_END
+  READ_BEGIN; for (int k = 0; k < 6; ++k) xfer_real(&d, &lims6[k], 8); READ_END
+  const int ns = head5[1];
+  const long nodes = (long)head5[2] * head5[3] * head5[4];
+  if (ns < 1 || ns > 16 || nodes * ns > cap) { close_unit(63); return -1000; }
+  READ_BEGIN; for (int k = 0; k < ns; ++k) xfer_real(&d, &qs[k], 8); READ_END
+  READ_BEGIN; for (int k = 0; k < ns; ++k) xfer_real(&d, &ms[k], 8); READ_END
+  for (long node = 0; node < nodes; ++node) { READ_BEGIN; for (int k = 0; k < ns; ++k) xfer_real(&d, &f[node * ns + k], 8); READ_END }
+  if (head5[0] == 1)
+    for (int a = 0; a < 7; ++a) { READ_BEGIN; for (long i = 0; i < nodes * ns; ++i) xfer_real(&d, &deriv[a * nodes * ns + i], 8); READ_END }
+  close_unit(63);
+  return 0;
 }

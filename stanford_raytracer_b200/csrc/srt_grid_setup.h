@@ -48,6 +48,11 @@ struct NumberStream {
     p = end;
     return true;
   }
+  // the end of one READ statement of `setup`: what is left of the record it ended in is not read (the next READ starts at a record)
+  void end_read() {
+    while (*p && *p != '\n') ++p;
+    if (*p) ++p;
+  }
 };
 
 // one derivative pass of libtricubic.f95:738-790 along `axis` (0: x, 1: y, 2: z) for array slot
@@ -87,18 +92,22 @@ inline int load_grid(const char* path, SrtModel& M, HostGrid& hg, bool host_deri
   double v[6];
   for (int i = 0; i < 5; ++i)
     if (!in.next(v[i])) return -2;
+  in.end_read();  // read(infile,*) computederivatives, nspec, nx, ny, nz (interp_dens_model_adapter.f95:61)
   const int compder = (int)v[0], nspec = (int)v[1], nx = (int)v[2], ny = (int)v[3], nz = (int)v[4];
   if (nspec < 1 || nx < 1 || ny < 1 || nz < 1) return -2;
   if (nspec > SRT_NSPEC) return -3;
   for (int i = 0; i < 6; ++i)
     if (!in.next(v[i])) return -2;
+  in.end_read();
   const double minx = v[0], maxx = v[1], miny = v[2], maxy = v[3], minz = v[4], maxz = v[5];
   memset(&M.grid, 0, sizeof M.grid);
   for (int i = 0; i < SRT_NSPEC; ++i) { M.qs[i] = 0.0; M.ms[i] = 1.0; }  // absent species: zero charge, zero density
   for (int i = 0; i < nspec; ++i)
     if (!in.next(M.qs[i])) return -2;
+  in.end_read();
   for (int i = 0; i < nspec; ++i)
     if (!in.next(M.ms[i])) return -2;
+  in.end_read();
   SrtGrid& g = M.grid;
   g.nx = nx; g.ny = ny; g.nz = nz; g.nspec = nspec;
   g.minx = minx; g.miny = miny; g.minz = minz;
@@ -113,13 +122,16 @@ inline int load_grid(const char* path, SrtModel& M, HostGrid& hg, bool host_deri
   const size_t nnodes = (size_t)nx * ny * nz;
   hg.nodes.assign(nnodes * 32, 0.0);
   const int narr = compder == 1 ? 8 : 1;
+  // f: one READ per node (:102-108); the seven derivative arrays: one READ each (:112-118)
   for (int q = 0; q < narr; ++q)
-    for (size_t node = 0; node < nnodes; ++node)
+    for (size_t node = 0; node < nnodes; ++node) {
       for (int s = 0; s < nspec; ++s) {
         double val;
         if (!in.next(val)) return -2;
         hg.nodes[(node * 8 + q) * 4 + s] = val;
       }
+      if (q == 0 || node + 1 == nnodes) in.end_read();
+    }
   if (compder_out) *compder_out = compder;
   if (compder != 1 && host_derivatives) {
     for (int s = 0; s < nspec; ++s) {

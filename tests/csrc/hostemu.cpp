@@ -142,6 +142,21 @@ void* emu_model_grid(const char* path, int yearday, int msec, int use_igrf) {
   return M;  // hg leaks with the model: test-only
 }
 #endif
+#ifdef EMU_HAVE_GRID
+// what load_grid read: dims = nspec nx ny nz; out[q][node][s] for the eight arrays q (f and the seven derivative arrays)
+long emu_grid_nodes(void* m, int* dims, double* qs_ms, double* out, long cap) {
+  const SrtModel* M = (const SrtModel*)m;
+  const SrtGrid& g = M->grid;
+  dims[0] = g.nspec; dims[1] = g.nx; dims[2] = g.ny; dims[3] = g.nz;
+  const long nodes = (long)g.nx * g.ny * g.nz;
+  if (8 * nodes * g.nspec > cap) return -1;
+  for (int s = 0; s < g.nspec; ++s) { qs_ms[s] = M->qs[s]; qs_ms[g.nspec + s] = M->ms[s]; }
+  for (int q = 0; q < 8; ++q)
+    for (long node = 0; node < nodes; ++node)
+      for (int s = 0; s < g.nspec; ++s) out[(q * nodes + node) * g.nspec + s] = g.nodes[(node * 8 + q) * 4 + s];
+  return nodes;
+}
+#endif
 // use_tsyganenko = 1 with the given parameters; the tilt argument as finish_model (csrc/srt_api.cu) sets it
 void emu_model_tsyganenko(void* m, const double* parmod, int yearday, int msec) {
   SrtModel* M = (SrtModel*)m;

@@ -180,3 +180,76 @@ def test_q24_integer_powers_against_libgcc_and_libgfortran(gf):
             a, b = L.orc_pow_r8_i4(x, n), gcc.__powidf2(x, n)
             assert np.float64(a).tobytes() == np.float64(b).tobytes(), (x, n, a, b)
             assert np.float64(a).tobytes() == np.float64(gfl._gfortran_pow_r8_i8(x, n)).tobytes(), (x, n)
+
+
+def test_dump_file_byte_for_byte(gf, built, tmp_path):
+    """the end of dumpmodel.f95 (:1284-1289) run by libgfortran == dumpmodel.write_dump, whole file"""
+    from stanford_raytracer_b200 import dumpmodel as dm
+    gf.gfio_write_dump.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_long]
+    rng = np.random.default_rng(61)
+    for nspec in (4, 3):
+        m = 4 * nspec + 3
+        f = rng.standard_normal((3, 4, 5, m)) * 10.0 ** rng.integers(-300, 300, (3, 4, 5, m))
+        f[0, 0, 0, :4] = [-1.602e-19, 0.0, -0.0, np.inf]
+        ext = np.array([-6371200.0, 6371200.0, 0.0, 0.0, -1.27424e7, 1.27424e7])
+        mine, theirs = str(tmp_path / ("mine%d.txt" % nspec)), str(tmp_path / ("gf%d.txt" % nspec))
+        dm.write_dump(mine, f, tuple(ext))
+        head = np.array([nspec, 5, 4, 3], dtype=np.int32)
+        flat = np.ascontiguousarray(f).ravel()
+        gf.gfio_write_dump(theirs.encode(), head.ctypes.data, ext.ctypes.data, flat.ctypes.data, len(flat))
+        assert open(mine, "rb").read() == open(theirs, "rb").read()
+
+
+def _grid_text(style, compder, rng):
+    """a small grid file in several writing styles the list-directed READs of `setup` accept"""
+    ns, nx, ny, nz = 3, 3, 2, 4
+    nodes = nx * ny * nz
+    vals = rng.uniform(5, 25, (8 if compder else 1, nodes, ns))
+    fmt = {"one_per_line": lambda v: "".join("%24.15E\n" % x for x in v),
+           "node_per_line": lambda v: "".join(" ".join("%.17g" % x for x in row) + "\n" for row in v.reshape(-1, ns)),
+           "commas_and_d": lambda v: "".join(",".join(("%.16e" % x).replace("e", "D") for x in row) + "\n" for row in v.reshape(-1, ns)),
+           "trailing_junk": lambda v: "".join(" ".join("%.17g" % x for x in row) + " 999 ignored\n" for row in v.reshape(-1, ns))}[style]
+    junk = "  77 88 trailing\n" if style == "trailing_junk" else "\n"
+    text = "%d %d %d %d %d%s" % (compder, ns, nx, ny, nz, junk)
+    text += "-2.5e7 2.5e7 -1e7,1e7 -3e7 3.0D+7%s" % junk
+    text += "-1.602e-19 1.602e-19 1.602e-19%s" % junk
+    text += "9.1e-31\n1.67e-27\n6.69e-27%s" % junk  # a READ continuing over records
+    text += fmt(vals[0].ravel())
+    for q in range(1, len(vals)):  # whole-array READs: the values may sit on lines of any length; the next array starts on a new record
+        flat = vals[q].ravel()
+        text += "".join(" ".join("%.17g" % x for x in flat[k:k + 5]) + "\n" for k in range(0, len(flat), 5)) if style != "one_per_line" else fmt(flat)
+    return text, (ns, nx, ny, nz)
+
+
+@pytest.mark.parametrize("compder", [0, 1])
+@pytest.mark.parametrize("style", ["one_per_line", "node_per_line", "commas_and_d", "trailing_junk"])
+def test_grid_file_reader_against_the_runtime(gf, built, tmp_path, style, compder):
+    """the READ statements of the interp adapter's setup run by libgfortran == the product's loader (csrc/srt_grid_setup.h, here its host
+    build) == the oracle's, every array"""
+    text, (ns, nx, ny, nz) = _grid_text(style, compder, np.random.default_rng(62))
+    path = str(tmp_path / "grid.txt")
+    open(path, "w").write(text)
+    nodes = nx * ny * nz
+    gf.gfio_read_grid.argtypes = [C.c_char_p] + [C.c_void_p] * 6 + [C.c_long]
+    head, lims, qs, ms = np.zeros(5, dtype=np.int32), np.zeros(6), np.zeros(16), np.zeros(16)
+    f, deriv = np.zeros(nodes * ns), np.zeros(7 * nodes * ns)
+    assert gf.gfio_read_grid(path.encode(), head.ctypes.data, lims.ctypes.data, qs.ctypes.data, ms.ctypes.data, f.ctypes.data, deriv.ctypes.data, len(f)) == 0
+    assert list(head) == [compder, ns, nx, ny, nz]
+    e = common.HostEmu("grid", path, 2010001, 0, 0)
+    E = e.E
+    E.emu_grid_nodes.restype = C.c_long
+    E.emu_grid_nodes.argtypes = [C.c_void_p] * 4 + [C.c_long]
+    dims, qm, out = np.zeros(4, dtype=np.int32), np.zeros(8), np.zeros(8 * nodes * ns)
+    assert E.emu_grid_nodes(e.h, dims.ctypes.data, qm.ctypes.data, out.ctypes.data, len(out)) == nodes
+    assert list(dims) == [ns, nx, ny, nz]
+    assert np.array_equal(qm[:ns], qs[:ns]) and np.array_equal(qm[ns:2 * ns], ms[:ns])
+    assert np.array_equal(out[:nodes * ns].view(np.uint64), f.view(np.uint64))
+    if compder:
+        assert np.array_equal(out[nodes * ns:].view(np.uint64), deriv.view(np.uint64))
+    o = ol.OracleModel("grid", path, 2010001, 0, 0, libm=True)
+    import test_raytracer_ref_cpu as T
+    _, _, A = T.state_of(o.L.orc_grid_state, o.h)
+    assert np.array_equal(A[5].view(np.uint64), f.view(np.uint64))
+    assert np.array_equal(A[2], np.arange(nx) * ((lims[1] - lims[0]) / (nx - 1.0)) + lims[0])
+    if compder:
+        assert np.array_equal(np.concatenate(A[6:]).view(np.uint64), deriv.view(np.uint64))
