@@ -20,7 +20,7 @@ import sys
 LOGOPS = {".LT.": "<", ".GT.": ">", ".LE.": "<=", ".GE.": ">=", ".EQ.": "==", ".NE.": "!=", ".AND.": "&&", ".OR.": "||", ".NOT.": "!"}
 INTRINSICS = {"DSIN": "M_sin", "DCOS": "M_cos", "DSQRT": "M_sqrt", "SQRT": "M_sqrt", "DEXP": "M_exp", "DLOG": "M_log", "DATAN2": "M_atan2",
               "DABS": "M_abs", "DTAN": "M_tan", "TAN": "M_tan", "SIN": "M_sin", "COS": "M_cos", "EXP": "M_exp", "ABS": "M_abs", "ATAN2": "M_atan2",
-              "ATAN": "M_atan", "ASIN": "M_asin", "FLOAT": "M_float", "DFLOAT": "M_dfloat", "DMOD": "M_mod", "AMOD": "M_mod", "MOD": "M_mod"}
+              "ATAN": "M_atan", "ASIN": "M_asin", "FLOAT": "M_float", "DFLOAT": "M_dfloat", "DMOD": "M_mod", "AMOD": "M_mod", "MOD": "M_mod", "SIGN": "M_sign", "DSIGN": "M_sign"}
 
 
 def read_statements(path):
@@ -598,6 +598,8 @@ static inline double M_dfloat(int i) { return (double)i; }
 static inline double M_mod(double a, double p) { return fmod(a, p); }
 static inline float M_mod(float a, float p) { return fmodf(a, p); }
 static inline int M_mod(int a, int p) { return a % p; }
+static inline double M_sign(double a, double b) { return copysign(fabs(a), b); }  // SIGN(A,B): |A| with the sign bit of B (gfortran, IEEE)
+static inline float M_sign(float a, float b) { return copysignf(fabsf(a), b); }
 // x**n, literal n: the multiplication tree of gcc's powi table (gfc_conv_cst_int_power); table[n] for n <= 8
 template <int N, class T> static inline T F_powc(T x) {
   constexpr int tbl[9] = {0, 1, 1, 2, 2, 3, 3, 4, 4};
@@ -809,8 +811,19 @@ extern "C" void xform_ref_gsm_to_sm(int yearday, int msec, const double* x, doub
 """
 
 
+XFORMD_WRAPPERS = """
+// the Fortran entry points of libxformd the reference's damping code links (damping/include/coord_transforms.h:31-48), under the
+// names gfortran gives them; arguments by reference, arrays 1-based inside the translation
+extern "C" void sm_to_mag_d_(int* itime, double* x_in, double* x_out) { f_SM_TO_MAG_D(itime - 1, x_in - 1, x_out - 1); }
+extern "C" void geo_to_mag_d_(int* itime, double* x_in, double* x_out) { f_GEO_TO_MAG_D(itime - 1, x_in - 1, x_out - 1); }
+extern "C" void mag_to_geo_d_(int* itime, double* x_in, double* x_out) { f_MAG_TO_GEO_D(itime - 1, x_in - 1, x_out - 1); }
+extern "C" void cart_to_pol_d_(double* x_in, double* lat, double* lon, double* radial) { f_CART_TO_POL_D(x_in - 1, *lat, *lon, *radial); }
+extern "C" void pol_to_cart_d_(double* lat, double* lon, double* radial, double* x_out) { f_POL_TO_CART_D(*lat, *lon, *radial, x_out - 1); }
+"""
+
+
 def main(src, dst, only=None, wrappers="ts05"):
-    free = wrappers in ("ngo", "xform")
+    free = wrappers in ("ngo", "xform", "xformd")
     stmts = []
     for one in src.split(","):
         stmts += read_statements_free(one) if free else read_statements(one)
@@ -831,7 +844,7 @@ def main(src, dst, only=None, wrappers="ts05"):
         commons.append("alignas(8) TL unsigned char C_%s[%d] = {0};" % (block, (size + 7) // 8 * 8))
     with open(dst, "w") as f:
         f.write(PRELUDE + "\n" + "\n".join(commons) + ("\ndouble* ts05_ref_A();\n\n" if wrappers == "ts05" else "\n\n") + "\n".join(protos) + "\n\n" + "\n".join(texts))
-        f.write({"ts05": TS05_WRAPPERS, "geopack": GEOPACK_WRAPPERS, "ngo": NGO_WRAPPERS, "xform": XFORM_WRAPPERS}[wrappers])
+        f.write({"ts05": TS05_WRAPPERS, "geopack": GEOPACK_WRAPPERS, "ngo": NGO_WRAPPERS, "xform": XFORM_WRAPPERS, "xformd": XFORMD_WRAPPERS}[wrappers])
 
 
 if __name__ == "__main__":

@@ -1,6 +1,6 @@
 """Damping along the ray (config 5), CPU side.
   * oracle/_ref/damping is the REFERENCE's own post-processor (damping/src/*.cpp compiled where they lie, oracle/Makefile
-    `ref`; MATLAB's libmat and the Fortran transforms replaced by oracle/ref_stubs/).  Its outputs on a committed ray file
+    `ref`; MATLAB's libmat replaced by oracle/ref_stubs/, the Fortran transforms by the reference's own xform_double translated).  Its outputs on a committed ray file
     are the golden vectors tests/golden/damping_ref_*.damp; here the binary must reproduce them byte for byte (the same
     binary is the checker of the GPU path in tests/test_gpu_damping.py).
   * the host set-up of the GPU kernels (Gauss-Legendre table, SM->MAG matrix, Greenwich longitude) against numpy and

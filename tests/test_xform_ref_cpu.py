@@ -57,3 +57,38 @@ def test_sm_gsm_equal_the_translated_reference(yearday, msec, srt_math):
             R.xform_ref_gsm_to_sm(yearday, msec, x.ctypes.data, a.ctypes.data)
             mine = np.array([x[0] * c + x[2] * s, x[1], x[2] * c - x[0] * s])
             assert np.array_equal(a.view(np.uint64), mine.view(np.uint64))
+
+
+def test_libxformd_entry_points_of_the_damping_code():
+    """sm_to_mag_d_, geo_to_mag_d_, mag_to_geo_d_, cart_to_pol_d_, pol_to_cart_d_ (damping/include/coord_transforms.h:31-48): the
+    reference's damping binary (oracle/_ref/damping) links the TRANSLATED xform_double (SM_TO_MAG, GEO_TO_MAG, MAG_TO_GEO, Cart_to_pol,
+    POL_TO_CART, T0-T5, ...); the hand restatement oracle/ref_stubs/xform_d.cpp (used by tests/csrc/damping_probe.cpp) equals it bit
+    for bit"""
+    path = os.path.join(ol.ORC_DIR, "_ref", "libxformd_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libxformd_ref.so not built (reference sources absent)")
+    ol.build()
+    R, S = C.CDLL(path), C.CDLL(os.path.join(ol.ORC_DIR, "_build", "libxform_d_standin.so"))
+    rng = np.random.default_rng(71)
+    vp = C.c_void_p
+    for yearday, msec in TIMES:
+        itime = np.array([yearday, msec], dtype=np.int32)
+        for x in rng.uniform(-5e7, 5e7, (100, 3)):
+            x = np.ascontiguousarray(x)
+            for name in ("sm_to_mag_d_", "geo_to_mag_d_", "mag_to_geo_d_"):
+                a, b = np.zeros(3), np.zeros(3)
+                for lib, out in ((R, a), (S, b)):
+                    fn = getattr(lib, name)
+                    fn.argtypes = [vp, vp, vp]
+                    fn(itime.ctypes.data, x.ctypes.data, out.ctypes.data)
+                assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), (name, yearday, msec)
+            pa, pb = np.zeros(3), np.zeros(3)
+            for lib, out in ((R, pa), (S, pb)):
+                lib.cart_to_pol_d_.argtypes = [vp] * 4
+                lib.cart_to_pol_d_(x.ctypes.data, out[0:].ctypes.data, out[1:].ctypes.data, out[2:].ctypes.data)
+            assert np.array_equal(pa.view(np.uint64), pb.view(np.uint64))
+            ca, cb = np.zeros(3), np.zeros(3)
+            for lib, out in ((R, ca), (S, cb)):
+                lib.pol_to_cart_d_.argtypes = [vp] * 4
+                lib.pol_to_cart_d_(pa[0:].ctypes.data, pa[1:].ctypes.data, pa[2:].ctypes.data, out.ctypes.data)
+            assert np.array_equal(ca.view(np.uint64), cb.view(np.uint64))
