@@ -215,6 +215,68 @@ def parity_check(summary_rows, idx, cpu):
     return len(idx), bad
 
 
+def translated_reference_run(cfg, pos0, dir0, w0, params, idx, threads):
+    """The reference's OWN Fortran of the path -- raytracer.f95, the Ngo adapter and density model, xform_double, Geopack, the vendored
+    LAPACK's zgesvd -- as translated to C++ at build time (oracle/_ref/*.so; no Fortran compiler exists), traced on the host cores:
+    one dynamic ray queue, every worker thread with its own (thread-local) module state.  Each array expression of the Fortran 90
+    is a heap temporary there, so this is slower than a compiled Fortran binary would be: reported beside the port, not instead of it.
+    Returns None where oracle/_ref was not built."""
+    import ctypes as C
+    import oracle_lib as ol
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    names = ["librt_ref.so", "libngo_ref.so", "libxform_ref.so", "libgeopack_ref.so", "libts05_ref.so", "liblapack_ref.so"]
+    if not all(os.path.exists(os.path.join(ref_dir, n)) for n in names):
+        return None
+    R, N, X, G, T, V = (C.CDLL(os.path.join(ref_dir, n)) for n in names)
+    vp, d, i, l = C.c_void_p, C.c_double, C.c_int, C.c_long
+    N.ngo_ref_readinput.argtypes = [C.c_char_p]
+    N.ngo_ref_state.argtypes = [vp]
+    R.rt_ref_ngo_adapter.argtypes = [vp] * 6 + [d, i, i, i, i, vp]
+    R.rt_ref_use_ngo_adapter.argtypes = [vp]
+    R.rt_ref_run.restype = l
+    R.rt_ref_run.argtypes = [vp, vp, d, d, d, d, i, d, i, d, i, d, vp, l, vp]
+    port = ol.OracleModel("ngo", cfg, libm=True)  # the port on glibc's libm, as the translation is: the rows must be the same bits
+    n = len(idx)
+    last = np.zeros((n, 20))
+    nrows = np.zeros(n, dtype=np.int64)
+    nthreads = max(1, min(threads, n))
+    lock, head = threading.Lock(), [0]
+    fp = lambda f: C.cast(f, vp)  # noqa: E731
+    parmod = np.zeros(10)
+
+    def work(t):
+        if N.ngo_ref_readinput(cfg.encode()) != 0:
+            raise RuntimeError("translated readinput failed")
+        st = np.zeros(12)
+        N.ngo_ref_state(st.ctypes.data)
+        R.rt_ref_ngo_adapter(fp(X.xform_ref_sm_to_gsm), fp(X.xform_ref_gsm_to_sm), fp(G.geopack_ref_recalc), fp(G.geopack_ref_igrf_gsw), fp(T.ts05_ref_t04_s),
+                             fp(N.ngo_ref_dens), st[2], 2010001, 0, 0, 0, parmod.ctypes.data)
+        R.rt_ref_use_ngo_adapter(fp(V.lapack_ref_csvd_hook))
+        rows = np.zeros((params["maxsteps"] + 2, 20))
+        while True:
+            with lock:
+                j = head[0]
+                head[0] += 1
+            if j >= n:
+                return
+            r = int(idx[j])
+            sc, d0 = C.c_int(), np.array(dir0[r], dtype=np.float64)
+            p0 = np.ascontiguousarray(pos0[r], dtype=np.float64)
+            k = R.rt_ref_run(p0.ctypes.data, d0.ctypes.data, w0[r], params["dt0"], params["dtmax"], params["maxerr"], params["maxsteps"], params["minalt"],
+                             params["root"], params["tmax"], params["fixedstep"], port.del_, rows.ctypes.data, len(rows), C.byref(sc))
+            last[j], nrows[j] = rows[k - 1], k
+
+    t0 = time.perf_counter()
+    ts = [threading.Thread(target=work, args=(q,)) for q in range(nthreads)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    dt = time.perf_counter() - t0
+    same = all(np.array_equal(port.trace_summary(pos0[int(r)], dir0[int(r)], w0[int(r)], **params)["last_row"], last[j], equal_nan=True) for j, r in enumerate(idx[:8]))
+    return {"value": float((nrows - 1).sum() / dt), "unit": UNIT, "cores": nthreads, "rays": int(n), "seconds": dt, "rows_equal_the_port": bool(same),
+            "kind": "reference (its Fortran translated to C++ at build time)",
+            "sample": "first %d steps of %d rays strided out of the 10k-ray sweep" % (params["maxsteps"], n)}
+
+
 def run_reference(args):
     """The reference arm: the CPU restatement of the reference on every host core, on the line's workload (C2),
     each step a bounded sample of it.  value = the de-duplicated statement (same algorithmic work as the GPU: the
@@ -240,6 +302,7 @@ def run_reference(args):
     idx_rc = idx[:: max(1, len(idx) // max(threads, 16))]
     rc = cpu_run("refcost", "ngo", cfg, 0, pos0, dir0, w0, params, idx_rc, threads)
     val = acc_total / t_total
+    tr = translated_reference_run(cfg, pos0, dir0, w0, dict(params, maxsteps=1000), idx[:: max(1, len(idx) // (8 * threads))], threads)
     line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "impl": "reference", "config": config_dict(args.gpus, "c2", 10000, 10000 * args.gpus),
@@ -248,7 +311,8 @@ def run_reference(args):
                                        "of the C++ restatement of the Fortran (no Fortran compiler on the box)" % len(idx),
                              "faithful_call_structure": {"value": f["accepted"] / f["seconds"], "cores": f["threads"], "seconds": f["seconds"], "rays": len(idx)},
                              "reference_cost": {"value": rc["accepted"] / rc["seconds"], "cores": rc["threads"], "seconds": rc["seconds"], "rays": len(idx_rc),
-                                                "note": "RECALC_08 and the dipole-tilt chain on every plasma call, as the Fortran adapters do"}},
+                                                "note": "RECALC_08 and the dipole-tilt chain on every plasma call, as the Fortran adapters do"},
+                             "translated_reference": tr},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -410,6 +474,12 @@ def measure(C, name, steps, warmup, e2e_steps, with_cpu, cpu_sizes):
                                    "sample": "%d whole rays strided out of the launch set, %.1f s, one dynamic ray queue; de-duplicated evaluation order (same algorithmic work as "
                                              "the GPU) of the C++ restatement of the reference" % (d["rays"], d["seconds"]),
                                    "modes": modes}
+            if kind == "ngo" and name == "c2":  # the reference's own translated source on the same cores, for scale (rank 0, N = 1 only)
+                tidx = np.unique(np.linspace(0, len(w0) - 1, 4 * threads).astype(int))
+                try:
+                    out["cpu_baseline"]["translated_reference"] = translated_reference_run(model_path, pos0, dir0, w0, dict(params, maxsteps=1000), tidx, threads)
+                except Exception as e:  # an auxiliary figure: it must not cost the line
+                    out["cpu_baseline"]["translated_reference"] = {"unavailable": repr(e)}
             # the same rays on the GPU (this rank's shard holds those with shard_of == 0), bit for bit
             mine = np.searchsorted(idx, cidx)
             ok = (mine < len(idx)) & (idx[np.minimum(mine, len(idx) - 1)] == cidx)
