@@ -177,3 +177,26 @@ int gfio_read_grid(const char* path, int* head5, double* lims6, double* qs, doub
   close_unit(63);
   return 0;
 }
+
+// a sequence of list-directed READs of REAL(8) items from one file, counts[r] items each, every READ with its own iostat (e.g. the
+// cards of readinput, ngo_dens_model.f95:61-115).  out holds the items READ after READ (in/out: a null value keeps what is there);
+// status[r] = iostat of READ r; reading stops at the first READ that fails.  -> READs completed
+int gfio_read_counts(const char* path, const int* counts, int nreads, double* out, int* status) {
+  static dt_t d;
+  int done = 0;
+  open_unit(64, path, "old");
+  for (int r = 0; r < nreads; ++r) {
+    int32_t st = 0;
+    dt_begin(&d, DT_LIST_FORMAT | HAS_IOSTAT, 64, 0, 0);
+    d.common.iostat = &st;
+    st_read(&d);
+    for (int k = 0; k < counts[r]; ++k) xfer_real(&d, &out[k], 8);
+    st_read_done(&d);
+    status[r] = st;
+    if (st != 0) break;
+    out += counts[r];
+    ++done;
+  }
+  close_unit(64);
+  return done;
+}

@@ -19,42 +19,6 @@ struct HostGrid {
   std::vector<double> nodes, xs, ys, zs;
 };
 
-// whitespace/comma separated numbers of a whole file, Fortran D exponents accepted
-struct NumberStream {
-  std::vector<char> buf;
-  char* p = nullptr;
-  bool open(const char* path) {
-    FILE* f = fopen(path, "rb");
-    if (!f) return false;
-    fseek(f, 0, SEEK_END);
-    long n = ftell(f);
-    fseek(f, 0, SEEK_SET);
-    if (n < 0) { fclose(f); return false; }
-    buf.resize((size_t)n + 1);
-    size_t got = fread(buf.data(), 1, (size_t)n, f);
-    fclose(f);
-    buf[got] = 0;
-    for (size_t i = 0; i < got; ++i)
-      if (buf[i] == 'D' || buf[i] == 'd') buf[i] = 'e';
-    p = buf.data();
-    return true;
-  }
-  bool next(double& v) {
-    while (*p == ' ' || *p == '\t' || *p == ',' || *p == '\n' || *p == '\r') ++p;
-    if (!*p) return false;
-    char* end = nullptr;
-    v = strtod(p, &end);
-    if (end == p) return false;
-    p = end;
-    return true;
-  }
-  // the end of one READ statement of `setup`: what is left of the record it ended in is not read (the next READ starts at a record)
-  void end_read() {
-    while (*p && *p != '\n') ++p;
-    if (*p) ++p;
-  }
-};
-
 // one derivative pass of libtricubic.f95:738-790 along `axis` (0: x, 1: y, 2: z) for array slot
 // `src` -> slot `dst` of every node record, species s
 inline void fd_pass(std::vector<double>& nodes, int nx, int ny, int nz, int s, int src, int dst, int axis, double h, bool enabled) {
@@ -87,27 +51,20 @@ inline void fd_pass(std::vector<double>& nodes, int nx, int ny, int nz, int s, i
 // host_derivatives = false leaves the derivative slots of a file without derivatives at zero: the library computes
 // them on the device (srt_fd_kernel, srt_api.cu); the CPU test build keeps the host passes below.
 inline int load_grid(const char* path, SrtModel& M, HostGrid& hg, bool host_derivatives = true, int* compder_out = nullptr) {
-  NumberStream in;
+  // every READ of `setup` (interp_dens_model_adapter.f95:59-118) is one ListReader::read: list-directed, starting at a record
+  ListReader in;
   if (!in.open(path)) return -1;
-  double v[6];
-  for (int i = 0; i < 5; ++i)
-    if (!in.next(v[i])) return -2;
-  in.end_read();  // read(infile,*) computederivatives, nspec, nx, ny, nz (interp_dens_model_adapter.f95:61)
+  double v[6] = {0, 0, 0, 0, 0, 0};
+  if (in.read(5, v) != 5) return -2;  // computederivatives, nspec, nx, ny, nz
   const int compder = (int)v[0], nspec = (int)v[1], nx = (int)v[2], ny = (int)v[3], nz = (int)v[4];
   if (nspec < 1 || nx < 1 || ny < 1 || nz < 1) return -2;
   if (nspec > SRT_NSPEC) return -3;
-  for (int i = 0; i < 6; ++i)
-    if (!in.next(v[i])) return -2;
-  in.end_read();
+  if (in.read(6, v) != 6) return -2;
   const double minx = v[0], maxx = v[1], miny = v[2], maxy = v[3], minz = v[4], maxz = v[5];
   memset(&M.grid, 0, sizeof M.grid);
   for (int i = 0; i < SRT_NSPEC; ++i) { M.qs[i] = 0.0; M.ms[i] = 1.0; }  // absent species: zero charge, zero density
-  for (int i = 0; i < nspec; ++i)
-    if (!in.next(M.qs[i])) return -2;
-  in.end_read();
-  for (int i = 0; i < nspec; ++i)
-    if (!in.next(M.ms[i])) return -2;
-  in.end_read();
+  if (in.read(nspec, M.qs) != nspec) return -2;
+  if (in.read(nspec, M.ms) != nspec) return -2;
   SrtGrid& g = M.grid;
   g.nx = nx; g.ny = ny; g.nz = nz; g.nspec = nspec;
   g.minx = minx; g.miny = miny; g.minz = minz;
@@ -121,17 +78,21 @@ inline int load_grid(const char* path, SrtModel& M, HostGrid& hg, bool host_deri
   for (int i = 0; i < nz; ++i) hg.zs[i] = (double)i * g.delz + minz;
   const size_t nnodes = (size_t)nx * ny * nz;
   hg.nodes.assign(nnodes * 32, 0.0);
-  const int narr = compder == 1 ? 8 : 1;
-  // f: one READ per node (:102-108); the seven derivative arrays: one READ each (:112-118)
-  for (int q = 0; q < narr; ++q)
-    for (size_t node = 0; node < nnodes; ++node) {
-      for (int s = 0; s < nspec; ++s) {
-        double val;
-        if (!in.next(val)) return -2;
-        hg.nodes[(node * 8 + q) * 4 + s] = val;
-      }
-      if (q == 0 || node + 1 == nnodes) in.end_read();
+  // f: one READ per node (:102-108)
+  for (size_t node = 0; node < nnodes; ++node) {
+    double val[SRT_NSPEC] = {0, 0, 0, 0};
+    if (in.read(nspec, val) != nspec) return -2;
+    for (int s = 0; s < nspec; ++s) hg.nodes[(node * 8 + 0) * 4 + s] = val[s];
+  }
+  // the seven derivative arrays: one READ each of a whole array (:112-118)
+  if (compder == 1) {
+    std::vector<double> arr(nnodes * (size_t)nspec, 0.0);
+    for (int q = 1; q < 8; ++q) {
+      if (in.read((long)arr.size(), arr.data()) != (long)arr.size()) return -2;
+      for (size_t node = 0; node < nnodes; ++node)
+        for (int s = 0; s < nspec; ++s) hg.nodes[(node * 8 + q) * 4 + s] = arr[node * nspec + s];
     }
+  }
   if (compder_out) *compder_out = compder;
   if (compder != 1 && host_derivatives) {
     for (int s = 0; s < nspec; ++s) {

@@ -16,65 +16,12 @@
 #include <string>
 #include <vector>
 
+#include "srt_listread.h"
 #include "srt_physics.h"
 
 namespace srt_host {
 
-// ---- Fortran list-directed numeric input, as far as the config/ray/grid files need it
-struct CardReader {
-  std::vector<std::string> rec;
-  size_t next = 0;
-  bool open(const char* path) {
-    FILE* f = fopen(path, "rb");
-    if (!f) return false;
-    std::string cur;
-    char buf[1 << 16];
-    size_t n;
-    while ((n = fread(buf, 1, sizeof buf, f)) > 0) {
-      for (size_t i = 0; i < n; ++i) {
-        if (buf[i] == '\n') { rec.push_back(cur); cur.clear(); }
-        else if (buf[i] != '\r') cur.push_back(buf[i]);
-      }
-    }
-    if (!cur.empty()) rec.push_back(cur);
-    fclose(f);
-    return true;
-  }
-  static bool is_sep(char c) { return c == ' ' || c == '\t' || c == ','; }
-  // READ(unit,*) of `want` numbers: starts at a fresh record, spills onto the next ones
-  // until satisfied, ignores what is left of the last record.  A '/' ends the list
-  // (remaining items keep their previous values).  Returns how many were assigned, or
-  // -1 at end of file before anything could be read.
-  int read(int want, double* v) {
-    int got = 0;
-    bool any_record = false;
-    while (got < want) {
-      if (next >= rec.size()) return any_record ? got : -1;
-      const std::string& s = rec[next++];
-      any_record = true;
-      size_t i = 0;
-      while (got < want) {
-        while (i < s.size() && is_sep(s[i])) ++i;
-        if (i >= s.size()) break;
-        if (s[i] == '/') return got;
-        size_t j = i;
-        while (j < s.size() && !is_sep(s[j])) ++j;
-        std::string tok(s, i, j - i);
-        // repeat counts r*value
-        int rep = 1;
-        size_t star = tok.find('*');
-        if (star != std::string::npos) { rep = atoi(tok.substr(0, star).c_str()); tok = tok.substr(star + 1); }
-        for (char& ch : tok) if (ch == 'd' || ch == 'D') ch = 'e';
-        char* end = nullptr;
-        double val = strtod(tok.c_str(), &end);
-        if (end == tok.c_str()) return got;  // not a number: I/O error in Fortran terms
-        for (int r = 0; r < rep && got < want; ++r) v[got++] = val;
-        i = j;
-      }
-    }
-    return got;
-  }
-};
+// ---- Fortran list-directed numeric input: srt_listread.h (one READ statement = one ListReader::read)
 
 // ---- dipole tilt (xform_double chain), FP64 with the shared elementary functions
 inline void rot_x(double a, const double v[3], double o[3]) {
@@ -136,7 +83,7 @@ inline void set_time(SrtModel& M, int yearday, int msec) {
 // ---- Ngo config cards -> SrtNgo.  Returns 0, or a negative error:
 //   -1 cannot open, -2 truncated/garbled cards, -3 too many ducts
 inline int load_ngo_config(const char* path, SrtModel& M) {
-  CardReader rd;
+  ListReader rd;
   if (!rd.open(path)) return -1;
   SrtNgo& g = M.ngo;
   memset(&g, 0, sizeof g);

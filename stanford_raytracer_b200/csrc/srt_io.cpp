@@ -23,6 +23,7 @@
 #include <vector>
 
 #include "../../include/srt.h"
+#include "srt_listread.h"
 
 namespace {
 
@@ -59,44 +60,6 @@ inline void put_i10(long long v, char* out) {
   if (n > 10) { memset(out, '*', 10); return; }
   memset(out, ' ', 10 - n);
   memcpy(out + 10 - n, buf, n);
-}
-
-// One value of a list-directed READ into a REAL item, as gfortran's run-time library accepts it (tests/test_formats_gfortran.py
-// holds the cases, checked against libgfortran itself): [sign] digits[.digits] | .digits, then an exponent E|D|Q [sign] digits or
-// just sign digits (1.5+3); or [sign] INF | INFINITY | NAN | NAN(...), any case.  Converted by strtod: correctly rounded,
-// overflow gives Infinity, underflow zero or a subnormal.
-bool fortran_number(const std::string& tok, double& v) {
-  size_t i = 0;
-  const size_t n = tok.size();
-  std::string t;
-  if (i < n && (tok[i] == '+' || tok[i] == '-')) t.push_back(tok[i++]);
-  if (i < n && isalpha((unsigned char)tok[i])) {
-    std::string w;
-    for (size_t k = i; k < n; ++k) w.push_back((char)tolower((unsigned char)tok[k]));
-    const bool neg = !t.empty() && t[0] == '-';
-    if (w == "inf" || w == "infinity") { v = neg ? -HUGE_VAL : HUGE_VAL; return true; }
-    if (w == "nan" || (w.size() >= 5 && w.compare(0, 4, "nan(") == 0 && w.back() == ')' && w.find(')') == w.size() - 1)) { v = NAN; return true; }
-    return false;
-  }
-  size_t digits = 0;
-  while (i < n && isdigit((unsigned char)tok[i])) { t.push_back(tok[i++]); ++digits; }
-  if (i < n && tok[i] == '.') {
-    t.push_back(tok[i++]);
-    while (i < n && isdigit((unsigned char)tok[i])) { t.push_back(tok[i++]); ++digits; }
-  }
-  if (digits == 0) return false;
-  if (i < n) {
-    const char c = tok[i];
-    if (c == 'e' || c == 'E' || c == 'd' || c == 'D' || c == 'q' || c == 'Q') ++i;
-    else if (c != '+' && c != '-') return false;
-    t.push_back('e');
-    if (i < n && (tok[i] == '+' || tok[i] == '-')) t.push_back(tok[i++]);
-    size_t ed = 0;
-    while (i < n && isdigit((unsigned char)tok[i])) { t.push_back(tok[i++]); ++ed; }
-    if (ed == 0 || i != n) return false;
-  }
-  v = strtod(t.c_str(), nullptr);
-  return true;
 }
 
 }  // namespace
@@ -206,57 +169,15 @@ int srt_result_write_text(const srt_result* res, const srt_model* m, const doubl
 
 int srt_read_inputrays(const char* path, double** pos0, double** dir0, double** w0, int64_t* nrays) {
   if (!path || !pos0 || !dir0 || !w0 || !nrays) return SRT_E_ARG;
-  FILE* f = fopen(path, "rb");
-  if (!f) return SRT_E_IO;
-  std::string text;
-  char chunk[1 << 16];
-  for (size_t got; (got = fread(chunk, 1, sizeof chunk, f)) > 0;) text.append(chunk, got);
-  fclose(f);
   // The driver's loop `read(infile, *, iostat=status) pos0, dir0, w` (raytracer_driver.f95:1146) under gfortran's list-directed
-  // rules: values are separated by blanks (tab, CR and the end of a record count as blanks), by one comma or semicolon, or by a
-  // slash, which ends the READ; nothing between two separators (or before the first one of a READ) is a null value and leaves the
-  // item as the previous READ left it (zeros at first: variables of the main program); r*c is r copies of c, r* is r nulls; a READ
-  // takes records until its seven items are served and drops the rest of the record it ends in; the first token that is not a number,
-  // or the end of the file before the seventh item, ends the loop.
+  // rules (srt_listread.h).  pos0, dir0 and w are variables of the main program: an item given a null value keeps what the
+  // previous READ left (zeros at first); the first READ that does not complete -- a token that is not a number, or the end of
+  // the file -- ends the loop.
+  srt_host::ListReader rd;
+  if (!rd.open(path)) return SRT_E_IO;
   std::vector<double> vals;
   double cur[7] = {0, 0, 0, 0, 0, 0, 0};
-  size_t p = 0;
-  const size_t n_text = text.size();
-  auto is_blank = [](char c) { return c == ' ' || c == '\t' || c == '\r' || c == '\n'; };
-  auto is_end = [&](char c) { return is_blank(c) || c == ',' || c == ';' || c == '/'; };
-  bool stop = false;
-  while (!stop) {
-    int idx = 0;
-    bool expecting = true, slash = false;
-    while (idx < 7 && !stop && !slash) {
-      while (p < n_text && is_blank(text[p])) ++p;
-      if (p >= n_text) { stop = true; break; }  // end of file inside a READ
-      const char c = text[p];
-      if (c == ',' || c == ';') { ++p; if (expecting) ++idx; else expecting = true; continue; }
-      if (c == '/') { ++p; slash = true; break; }
-      size_t q = p;
-      while (q < n_text && !is_end(text[q])) ++q;
-      std::string tok = text.substr(p, q - p);
-      p = q;
-      long rep = 1;
-      size_t d = 0;
-      while (d < tok.size() && isdigit((unsigned char)tok[d])) ++d;
-      if (d > 0 && d < tok.size() && tok[d] == '*') {
-        rep = d > 9 ? 1000000000L : atol(tok.substr(0, d).c_str());
-        if (rep == 0) { stop = true; break; }
-        tok = tok.substr(d + 1);
-        if (tok.empty()) { idx += (int)(rep < 7 ? rep : 7); expecting = false; continue; }  // r*: r null values
-      }
-      double v;
-      if (!fortran_number(tok, v)) { stop = true; break; }
-      for (; rep > 0 && idx < 7; --rep) cur[idx++] = v;
-      expecting = false;
-    }
-    if (stop) break;
-    vals.insert(vals.end(), cur, cur + 7);
-    while (p < n_text && text[p] != '\n') ++p;  // the rest of the record the READ ended in
-    if (p < n_text) ++p;
-  }
+  while (rd.read(7, cur) == 7) vals.insert(vals.end(), cur, cur + 7);
   const int64_t n = (int64_t)(vals.size() / 7);
   *pos0 = (double*)malloc(sizeof(double) * 3 * (size_t)(n ? n : 1));
   *dir0 = (double*)malloc(sizeof(double) * 3 * (size_t)(n ? n : 1));

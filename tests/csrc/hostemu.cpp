@@ -157,6 +157,21 @@ long emu_grid_nodes(void* m, int* dims, double* qs_ms, double* out, long cap) {
   return nodes;
 }
 #endif
+// a sequence of list-directed READs through the product's reader (csrc/srt_listread.h), as gfio_read_counts of
+// oracle/ref_stubs/gfortran_io_shim.c does through libgfortran: -> READs completed, status[r] = 0 / -1 end of file / -2 bad value
+int emu_read_counts(const char* path, const int* counts, int nreads, double* out, int* status) {
+  srt_host::ListReader rd;
+  if (!rd.open(path)) return -1;
+  int done = 0;
+  for (int r = 0; r < nreads; ++r) {
+    const long got = rd.read(counts[r], out);
+    status[r] = got == counts[r] ? 0 : (int)got;
+    if (status[r] != 0) break;
+    out += counts[r];
+    ++done;
+  }
+  return done;
+}
 // use_tsyganenko = 1 with the given parameters; the tilt argument as finish_model (csrc/srt_api.cu) sets it
 void emu_model_tsyganenko(void* m, const double* parmod, int yearday, int msec) {
   SrtModel* M = (SrtModel*)m;

@@ -253,3 +253,47 @@ def test_grid_file_reader_against_the_runtime(gf, built, tmp_path, style, compde
     assert np.array_equal(A[2], np.arange(nx) * ((lims[1] - lims[0]) / (nx - 1.0)) + lims[0])
     if compder:
         assert np.array_equal(np.concatenate(A[6:]).view(np.uint64), deriv.view(np.uint64))
+
+
+CARD_FILES = {
+    "newray_default": None,   # the files of the test suite themselves
+    "newray_ducts": None,
+    "cards_in_odd_styles": "0,1 0 200.\n -1.0 , 50\n3 0;1 0 2*0 1.d3 4.0 0. 3e3\n0.0 1600.\n4* /\n7370. 3000 .08 .02, ,\n"
+                           "6470 140 6370 1 30 / the rest is not read\n 4.0 .13 .07 1.e9 50\n1 2 3 4 5 6 7 8 9 10 11 12 13\n0 0 0 0 0 0 0 0\n",
+    "truncated": "0 1 0 200.\n-1 50\n3 0 1 0 0\n",
+    "bad_number": "0 1 0 200.\n-1 5O\n3 0 1 0 0 0 1 2 3 4\n",
+}
+CARD_COUNTS = [4, 2, 10, 5, 5, 5, 5, 12, 8]
+
+
+@pytest.mark.parametrize("name", sorted(CARD_FILES))
+def test_config_cards_against_the_runtime(gf, built, tmp_path, name):
+    """the READ statements of readinput (ngo_dens_model.f95:61-115: 4, 2, 10, 5, 5, 5, 5, 12, 8 items) run by libgfortran == the
+    product's list-directed reader (csrc/srt_listread.h), item for item, with the same READ failing the same way"""
+    if name == "newray_default":
+        path = common.NGO_CFG
+    elif name == "newray_ducts":
+        path = os.path.join(common.ROOT, "tests", "data", "newray_ducts_sin_gauss.in")
+    else:
+        path = str(tmp_path / (name + ".in"))
+        open(path, "w").write(CARD_FILES[name])
+    counts = np.array(CARD_COUNTS, dtype=np.int32)
+    common.build_hostemu()
+    E = C.CDLL(os.path.join(common.BUILD, "libsrt_hostemu.so"))
+    res = []
+    for fn in (gf.gfio_read_counts, E.emu_read_counts):
+        fn.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        out, status = np.full(int(counts.sum()), -777.0), np.zeros(len(counts), dtype=np.int32)
+        done = fn(path.encode(), counts.ctypes.data, len(counts), out.ctypes.data, status.ctypes.data)
+        res.append((done, out, status))
+    (da, oa, sa), (db, ob, sb) = res
+    assert da == db, (name, da, db, sa, sb)
+    assert np.array_equal(np.sign(sa), np.where(sb == -2, 1, sb)), (name, sa, sb)  # 0 / end of file (< 0 in Fortran, -1 here) / bad value (> 0, -2 here)
+    k = int(counts[:da].sum())
+    assert np.array_equal(oa[:k].view(np.uint64), ob[:k].view(np.uint64)), (name, oa[:k], ob[:k])
+    if name == "truncated":
+        assert da == 2 and sa[2] < 0
+    if name == "bad_number":
+        assert da == 1 and sa[1] > 0
+    if name.startswith("newray"):
+        assert da >= 7
