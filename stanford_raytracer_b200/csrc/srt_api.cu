@@ -435,7 +435,7 @@ int launch_trace(DevCtx* c, srt_model* m, const SrtRunParams& P, const SrtBatch&
   B.order_mul = ray_order_mul(B.nrays);
   {
     const char* env = getenv("SRT_TEAM_SHADOW");  // A/B hook: 0 = no shadow teams
-    B.shadow = (env && env[0] == '0') ? 0 : 1;
+    B.shadow = !env ? 1 : (env[0] == '0' ? 0 : (env[0] == '4' ? 4 : 1));  // 4: a primary and three shadows where the live rays fit four times
   }
   int mode, block, grid;
   int rc = launch_config(c, m, B.nrays, &mode, &block, &grid, nullptr);

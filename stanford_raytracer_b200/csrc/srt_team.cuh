@@ -117,18 +117,26 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
   // shadow's work is dropped.  After each estimate round both teams take the state of the live one and the shadow sets up
   // its next guess.  Pure scheduling of identical arithmetic: no result changes (tests/test_gpu_parity.py,
   // test_gpu_c3_long.py and the bench's parity check run whole batches in this mode).
-  bool pairs_on = false;       // block-uniform: team slots are (primary, shadow) pairs
-  bool shadow_ready = false;   // pair-uniform: the shadow runs the current attempt alongside the primary
-  int live_is_S = 0, did_est = 0;
-  int shadow_kind = 2;         // shadow: the kind of failure whose retry it is running
+  // Round 2, later: with B.shadow >= 4 a ray gets THREE shadows (a whole warp per ray) as soon as the live rays fit four times:
+  // the shadow of depth q runs the retry after q failures of the kind last seen (0.8^q dt, or dt / 2^q after the growth guess),
+  // and the chain of valid shadows is resolved in the estimate round (srt_team_est.inl).  tools/shadow_predict.cpp replays this.
+  int group = 1;               // block-uniform: team slots are groups of 1, 2 or 4 (a primary and its shadows)
+  int gq = 0, gbase = 0;       // my team's index in its group; first lane of the group
+  unsigned gmask = full;       // lanes of my group
+  bool shadow_ready = false;   // group-uniform: the shadows run the current attempt alongside the primary
+  int live_is_S = 0, did_est = 0;  // live_is_S: index in the group of the team whose state is the ray's after this estimate round
+  int shadow_kind = 2;         // shadow: the kind of failure whose retries the shadows are running
   int err_small = 1;           // the most recent error estimate of this ray was below maxerr / 100 (the growth test's condition)
   int last_fail = 0;           // kind of this ray's most recent failed attempt: 1 error test (dt -> 0.8 dt), 2 cone test (dt -> dt / 2)
   double dt_p = 0.0;           // shadow: the primary's dt (the stop test at the attempt start is the primary's)
   unsigned long long my_spec = 0;
-  const bool odd_team = (lane & 8) != 0;
-  const unsigned pmask = 0xffffu << (lane & 16);
-  const int pbase = lane & 16;
-  (void)last_fail; (void)err_small; (void)shadow_kind; (void)pairs_on; (void)shadow_ready; (void)live_is_S; (void)did_est; (void)dt_p; (void)odd_team; (void)pmask; (void)pbase; (void)my_spec;
+  auto set_group = [&](int g) {
+    group = g;
+    gq = g == 4 ? (lane >> 3) : (g == 2 ? ((lane >> 3) & 1) : 0);
+    gbase = g == 4 ? 0 : (lane & 16);
+    gmask = g == 4 ? 0xffffffffu : (0xffffu << (lane & 16));
+  };
+  (void)last_fail; (void)err_small; (void)shadow_kind; (void)group; (void)shadow_ready; (void)live_is_S; (void)did_est; (void)dt_p; (void)gq; (void)gmask; (void)gbase; (void)my_spec; (void)set_group;
   for (;;) {
     // ================= refill: idle teams take the next ray; one atomic per warp
 #if defined(SRT_TEAM_BLOCK_SYNC)
@@ -186,7 +194,7 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
         }
       }
     }
-    bool is_shadow = pairs_on && odd_team;
+    bool is_shadow = group > 1 && gq != 0;
 #if defined(SRT_TEAM_BLOCK_SYNC)
     // block-synchronous rounds: the warps of a block walk the round's code in phase and share instruction lines
     // live teams of this block; a team waiting for its refill round (phase alignment) still has the queue to look at
@@ -196,7 +204,9 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
     // spread over all its warps still issues every warp.  When at most half of the team slots in use are live, the
     // live teams are re-packed into the lowest warps through shared memory (pure data movement: results unchanged);
     // the emptied warps then only attend the barrier.  Config 2 spends most of its time in this regime.
-    if ((++sync_iter & 31u) == 0u && live * (pairs_on ? 4 : 2) <= cap_teams && cap_teams > 4) {
+    const int nteams = (int)(blockDim.x >> 3);
+    const bool regroup = adaptive && B.shadow >= 4 && group == 2 && live * 4 <= nteams;  // pairs may become quads before the live rays have halved
+    if ((++sync_iter & 31u) == 0u && (live * 2 * group <= cap_teams || regroup) && cap_teams > 4) {
       if (__syncthreads_or(exhausted ? 1 : 0)) {
         unsigned long long* pk = srt_pack_smem;
         const int nslots = (int)(blockDim.x >> 1);  // lane slots available: half a block
@@ -219,11 +229,13 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
         }
         __syncthreads();
         const int nlive = srt_pack_count;
-        // the live rays fit twice (nlive <= cap_teams / 2): adaptive runs seat them as (primary, shadow) pairs
-        const bool want_pairs = adaptive && B.shadow != 0;
+        // the live rays fit twice (nlive <= cap_teams / 2): adaptive runs seat them as (primary, shadow) pairs, or, where they fit
+        // four times and B.shadow asks for it, as a primary and three shadows
+        const int want_group = !(adaptive && B.shadow != 0) ? 1 : ((B.shadow >= 4 && nlive * 4 <= nteams) ? 4 : (nlive * 2 <= nteams ? 2 : 1));
+        set_group(want_group);
         const int seat = (int)(threadIdx.x >> 3);
-        const int src_team = want_pairs ? (seat >> 1) : seat;
-        if (src_team < nlive && !(want_pairs && odd_team)) {
+        const int src_team = seat / want_group;
+        if (src_team < nlive && gq == 0) {
           const int o = src_team * 8 + r;
           double dv[20];
 #pragma unroll
@@ -245,12 +257,11 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
           phase = SRT_PH_IDLE;
           exhausted = true;
         }
-        pairs_on = want_pairs;
         last_fail = 0;
         shadow_ready = false;  // the shadows join at the end of their primary's next estimate round
         did_est = 0;
-        cap_teams = ((want_pairs ? 2 * nlive : nlive) + 3) & ~3;  // whole warps
-        is_shadow = pairs_on && odd_team;
+        cap_teams = ((want_group * nlive) + 3) & ~3;  // whole warps
+        is_shadow = group > 1 && gq != 0;
         __syncthreads();
       }
     }
@@ -396,35 +407,36 @@ __global__ void __launch_bounds__(MAXT, 1) srt_trace_team_kernel(const __grid_co
       }
     }
 #if defined(SRT_TEAM_BLOCK_SYNC)
-    // ================= shadow pairs: after the primary's estimate round both teams take the state of the live one
-    if (pairs_on) {
-      const int fl = __shfl_sync(pmask, did_est | (live_is_S << 1), pbase);
+    // ================= shadow groups: after the primary's estimate round every team of the group takes the state of the live one
+    if (group > 1) {
+      const int fl = __shfl_sync(gmask, did_est | (live_is_S << 1), gbase);
       did_est = 0;
       if (fl & 1) {
-        const int src = pbase + ((fl & 2) ? 8 : 0) + r;
-        w = __shfl_sync(pmask, w, src); wl = __shfl_sync(pmask, wl, src); t = __shfl_sync(pmask, t, src); dt = __shfl_sync(pmask, dt, src);
-        dfdw_rec = __shfl_sync(pmask, dfdw_rec, src);
-        vg[0] = __shfl_sync(pmask, vg[0], src); vg[1] = __shfl_sync(pmask, vg[1], src); vg[2] = __shfl_sync(pmask, vg[2], src);
-        xc = __shfl_sync(pmask, xc, src); dfdk_c = __shfl_sync(pmask, dfdk_c, src); rhs1c = __shfl_sync(pmask, rhs1c, src);
-        slot = __shfl_sync(pmask, slot, src);
+        const int src = gbase + 8 * (fl >> 1) + r;
+        w = __shfl_sync(gmask, w, src); wl = __shfl_sync(gmask, wl, src); t = __shfl_sync(gmask, t, src); dt = __shfl_sync(gmask, dt, src);
+        dfdw_rec = __shfl_sync(gmask, dfdw_rec, src);
+        vg[0] = __shfl_sync(gmask, vg[0], src); vg[1] = __shfl_sync(gmask, vg[1], src); vg[2] = __shfl_sync(gmask, vg[2], src);
+        xc = __shfl_sync(gmask, xc, src); dfdk_c = __shfl_sync(gmask, dfdk_c, src); rhs1c = __shfl_sync(gmask, rhs1c, src);
+        slot = __shfl_sync(gmask, slot, src);
         unsigned f1 = (dropped ? 1u : 0u) | (attempt_start ? 2u : 0u) | (finish_now ? 4u : 0u) | (cone_exit ? 8u : 0u) |
                       ((unsigned)lastrefinedown << 4) | ((unsigned)phase << 8) | ((unsigned)stage << 12) | ((unsigned)stopcond << 16) |
                       ((unsigned)last_fail << 20) | ((unsigned)err_small << 24);
-        f1 = __shfl_sync(pmask, f1, src);
+        f1 = __shfl_sync(gmask, f1, src);
         dropped = f1 & 1u; attempt_start = f1 & 2u; finish_now = f1 & 4u; cone_exit = (f1 >> 3) & 1u;
         lastrefinedown = (int)((f1 >> 4) & 0xfu); phase = (int)((f1 >> 8) & 0xfu); stage = (int)((f1 >> 12) & 0xfu);
         stopcond = (int)((f1 >> 16) & 0xfu); last_fail = (int)((f1 >> 20) & 0xfu); err_small = (int)((f1 >> 24) & 1u);
-        nstep = __shfl_sync(pmask, nstep, src); nrej = __shfl_sync(pmask, nrej, src); ncone = __shfl_sync(pmask, ncone, src);
-        nlog = __shfl_sync(pmask, nlog, src);
+        nstep = __shfl_sync(gmask, nstep, src); nrej = __shfl_sync(gmask, nrej, src); ncone = __shfl_sync(gmask, ncone, src);
+        nlog = __shfl_sync(gmask, nlog, src);
         exhausted = true;
         dt_p = dt;
-        if (odd_team) {
-          // The retry the shadow prepares is the one after the kind of failure this ray met last.  Error test
-          // (raytracer.f95:790-798): dt -> 0.8 dt from the same state, `w` of :821 not yet set by that attempt.  Cone test
-          // (:891-899), reached after the growth test of :800-812, taken to go the way this ray's last error estimate would have
-          // sent it: dt -> (dt or 1.25 dt) / 2, `w` set.
-          shadow_kind = last_fail == 1 ? 1 : 2;
-          if (last_fail == 1) {
+        // The retries the shadows prepare are those after failures of the kind this ray met last.  Error test
+        // (raytracer.f95:790-798): dt -> 0.8 dt from the same state, `w` of :821 not yet set by that attempt.  Cone test
+        // (:891-899), reached after the growth test of :800-812, taken to go the way this ray's last error estimate would have
+        // sent it: dt -> (dt or 1.25 dt) / 2, `w` set; a further refinement halves again (no growth after a refinement).
+        // The shadow of depth gq applies gq such failures.
+        shadow_kind = last_fail == 1 ? 1 : 2;
+        for (int q = 0; q < gq; ++q) {
+          if (shadow_kind == 1) {
             dt = 0.8 * dt;
             nrej++;
           } else {

@@ -92,22 +92,29 @@
             }
           }
         }
-        // ---- shadow pairs (srt_team.cuh): is the retry the primary now needs the attempt its shadow has just finished?
-        bool i_live = true;
+        // ---- shadow groups (srt_team.cuh): are the retries the ray now needs the attempts its shadows have just finished?  The shadow
+        // of depth q is valid if every team before it failed the way the shadows prepared for and arrived at exactly its dt.
+        bool i_live = true, valid_me = true;
         live_is_S = 0;
 #if defined(SRT_TEAM_BLOCK_SYNC)
         if (outcome == 1 || outcome == 2) last_fail = outcome;
-        if (pairs_on && shadow_ready) {
-          const int out_p = __shfl_sync(pmask, outcome, pbase);
-          const long long dt_next_p = __shfl_sync(pmask, __double_as_longlong(dt), pbase);
-          const int prepared = __shfl_sync(pmask, shadow_kind, pbase + 8);
-          int hit = (odd_team && out_p == prepared && dt_next_p == __double_as_longlong(dt_used) && !(dt_used < (double)1e-14f)) ? 1 : 0;
-          hit = __shfl_sync(pmask, hit, pbase + 8);
-          live_is_S = hit;
-          i_live = odd_team ? (hit != 0) : (hit == 0);
-          if (hit && odd_team && r == 0) ++my_spec;
-          // the live attempt's failure, else the primary's, is the ray's most recent one
-          if (odd_team && hit && outcome != 1 && outcome != 2) last_fail = out_p;
+        if (group > 1 && shadow_ready) {
+          const int prepared = __shfl_sync(gmask, shadow_kind, gbase + 8);
+          int live_q = 0;
+          bool chain = true;
+          for (int q = 1; q < group; ++q) {
+            const int out_prev = __shfl_sync(gmask, outcome, gbase + 8 * (q - 1));
+            const long long dt_next_prev = __shfl_sync(gmask, __double_as_longlong(dt), gbase + 8 * (q - 1));
+            const long long dt_used_q = __shfl_sync(gmask, __double_as_longlong(dt_used), gbase + 8 * q);
+            chain = chain && out_prev == prepared && dt_next_prev == dt_used_q && !(__longlong_as_double(dt_used_q) < (double)1e-14f);
+            if (chain) live_q = q;
+          }
+          live_is_S = live_q;
+          i_live = gq == live_q;
+          valid_me = gq <= live_q;
+          if (gq >= 1 && valid_me && r == 0) ++my_spec;
+          // the live attempt's failure, else the one before it in the chain, is the ray's most recent one
+          if (i_live && gq >= 1 && outcome != 1 && outcome != 2) last_fail = prepared;
         }
 #endif
         {
@@ -191,7 +198,7 @@
           }
         }
         if (retry) {
-          if (r == 0 && (i_live || !odd_team || !pairs_on)) ++my_attempts;  // a primary's failed attempt counts; a shadow's only when it is the live one
+          if (r == 0 && valid_me) ++my_attempts;  // a primary's failed attempt counts; a shadow's only when it is one of the ray's attempts
           phase = SRT_PH_STAGE;
           attempt_start = true;
         }
