@@ -37,7 +37,8 @@ struct SrtBatch {
                                     // [5] steps of all-NaN states taken by the fast-forward (srt_nan_fastforward), team kernel: [6] attempts that were a shadow team's (computed alongside the attempt they retry), [7] max over blocks of rounds
   unsigned* nlogged;                // optional [nrays]: rows this ray put in the log
   unsigned long long order_mul;     // queue position q is ray (q * order_mul) mod nrays; coprime to nrays (1 = input order)
-  int shadow;                       // team kernel: free team slots run shadow attempts once the queue is empty (srt_team.cuh); set by launch_trace
+  int shadow;                       // team kernel: free team slots run shadow attempts once the queue is empty (srt_team.cuh): 0 none, 1 pairs, 4 a primary
+                                    // and three shadows where the live rays fit four times; set by launch_trace
 };
 
 // Queue position -> ray index.  A batch of the size of one machine fill (config 2) is handed out once: in input order
