@@ -78,6 +78,21 @@ const char* srt_last_cuda_error(void);
 int srt_model_ngo(srt_model** m, const char* ngo_configfile, int yearday, int milliseconds_day, int use_igrf, int use_tsyganenko);
 /* modelnum 3 -- interpsetup + interpStateData (driver:497-615; interp_dens_model_adapter.f95:16-39,52-134) */
 int srt_model_grid(srt_model** m, const char* interp_interpfile, int yearday, int milliseconds_day, int use_igrf, int use_tsyganenko);
+/* modelnum 4 -- scatteredinterpsetup + scatteredinterpStateData (driver:617-770; fortran/scattered_interp_dens_model_adapter.f95:17-48,
+ * 63-212): density by moving least squares (fortran/lsinterp_mod.f95:255-449) over the samples of `interp_interpfile` within
+ * window_scale * (largest nearest-neighbour distance of the file); order 0..3 = degree of the monomials; exact, scaled,
+ * local_window_scale as the driver's --scattered_interp_* options (driver:704-729; the driver always passes scaled = 0).
+ * nspec <= 4; order > 3 returns SRT_E_UNSUPPORTED.  The reference's kd-tree (fortran/kdtree_mod.f95) is replaced by a cell
+ * list with the same neighbour sets; what that means for the last bits is stated in csrc/srt_scattered.h. */
+int srt_model_scattered(srt_model** m, const char* interp_interpfile, int yearday, int milliseconds_day, int use_igrf, int use_tsyganenko,
+                        double window_scale, int order, int exact, int scaled, double local_window_scale);
+/* what set-up found: samples kept, the largest nearest-neighbour distance (adapter :160-192), the search radius, the number
+ * of monomials, the dimensions of the cell list (any pointer may be NULL) */
+int srt_model_scattered_info(const srt_model* m, int64_t* npoints, double* maxnearest, double* radius, int* nmono, int* cells /*[3]*/);
+/* the samples set-up kept (repeated positions dropped, adapter :143-155), in the order a query walks them:
+ * recs[npoints][8] = x, y, z, log-density of species 1..4, distance to the nearest other sample (adapter :160-191; 1.0 for a
+ * sample inside the Earth).  capacity in doubles; recs = NULL only counts.  Returns npoints, or an error code < 0. */
+int64_t srt_model_scattered_samples(const srt_model* m, double* recs, int64_t capacity);
 /* use_tsyganenko = 1 (fortran/ngo_dens_model_adapter.f95:157-166,183-187): the TS05 external field T04_s
  * (tsyganenko/TS05_aka_TS04.for:5-116) is added to the base field.  parmod[10] = Pdyn, Dst, ByIMF, BzIMF, W1..W6, the
  * driver's --tsyganenko_* options (fortran/raytracer_driver.f95:262-291).  Also switches the term on for a model that

@@ -6,6 +6,7 @@
 #include "orc_models.h"
 #ifdef ORC_HAVE_GRID
 #include "orc_grid.h"
+#include "orc_scattered.h"
 #endif
 
 using namespace orc;
@@ -42,6 +43,49 @@ void* orc_model_grid(const char* gridfile, int yearday, int msec, int use_igrf, 
   m->field.use_igrf = use_igrf;
   if (!orc_attach_igrf(m->field, yearday, msec, faithful_cost)) { delete m; return nullptr; }
   return (Model*)m;
+}
+#endif
+
+#ifdef ORC_HAVE_GRID
+// modelnum 4.  perm[nperm]: the insertion order of the samples (0-based file indices; nperm = 0: file order), the part of the
+// reference's set-up its source leaves to an unseeded random_number; root_quirk: see orc_scattered.h
+void* orc_model_scattered(const char* file, int yearday, int msec, int use_igrf, double window_scale, int order, int exact, int scaled,
+                          double local_window_scale, const long* perm, long nperm, int root_quirk) {
+  ScatteredModel* m = new ScatteredModel();
+  std::vector<long> pv(perm, perm + (perm ? nperm : 0));
+  if (m->setup(file, pv, root_quirk != 0) != 0) { delete m; return nullptr; }
+  m->window_scale = window_scale; m->order = order; m->exact = exact; m->scaled = scaled; m->local_window_scale = local_window_scale;
+  m->del = 1.0e-6;  // delDP, driver:1176
+  m->field.tilt.init(yearday, msec);
+  m->field.use_igrf = use_igrf;
+  if (!orc_attach_igrf(m->field, yearday, msec, 0)) { delete m; return nullptr; }
+  return (Model*)m;
+}
+// out: maxnearest, samples kept, duplicates ignored, nearest distance stored with the root sample
+void orc_scattered_info(void* mv, double* out) {
+  ScatteredModel* m = (ScatteredModel*)(Model*)mv;
+  out[0] = m->maxnearest; out[1] = (double)m->nkept; out[2] = (double)m->nduplicates; out[3] = m->tree ? m->tree->val.back() : -1.0;
+}
+// radius query at x: the neighbours in the tree's traversal order, recs[cap][3 + nspec + 1]; returns how many there are
+long orc_scattered_search(void* mv, const double* x, double* recs, long cap) {
+  ScatteredModel* m = (ScatteredModel*)(Model*)mv;
+  std::vector<KdTree*> found;
+  m->search(x, found);
+  const int w = 3 + m->nspec + 1;
+  for (long i = 0; i < (long)found.size() && i < cap; ++i) {
+    for (int k = 0; k < 3; ++k) recs[i * w + k] = found[i]->point[k];
+    for (int k = 0; k <= m->nspec; ++k) recs[i * w + 3 + k] = found[i]->val[k];
+  }
+  return (long)found.size();
+}
+long orc_scattered_impose_order(void* mv, long n, const double* pts) { return ((ScatteredModel*)(Model*)mv)->impose_order(n, pts); }
+int orc_scattered_interpolate(void* mv, const double* x, double* fi) { return ((ScatteredModel*)(Model*)mv)->interpolate(x, fi); }
+// lsinterp on neighbour arrays given in the caller's order: pts[I][3], vals[I][nval]
+int orc_lsinterp_found(const double* x, long I, const double* pts, const double* vals, int nval, double radius, int order, int exact, int scaled,
+                       double local_window_scale, double* fi) {
+  std::vector<const double*> fp(I), fv(I);
+  for (long i = 0; i < I; ++i) { fp[i] = pts + 3 * i; fv[i] = vals + (size_t)nval * i; }
+  return lsinterp_found(x, fp, fv, nval, radius, order, exact, scaled, local_window_scale, fi);
 }
 #endif
 

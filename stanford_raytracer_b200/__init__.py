@@ -50,6 +50,10 @@ def lib():
     L.srt_last_cuda_error.restype = C.c_char_p
     L.srt_model_ngo.argtypes = [C.POINTER(vp), C.c_char_p, i, i, i, i]
     L.srt_model_grid.argtypes = [C.POINTER(vp), C.c_char_p, i, i, i, i]
+    L.srt_model_scattered.argtypes = [C.POINTER(vp), C.c_char_p, i, i, i, i, d, i, i, i, d]
+    L.srt_model_scattered_info.argtypes = [vp, C.POINTER(i64), C.POINTER(d), C.POINTER(d), C.POINTER(i), vp]
+    L.srt_model_scattered_samples.restype = i64
+    L.srt_model_scattered_samples.argtypes = [vp, vp, i64]
     L.srt_model_free.argtypes = [vp]
     L.srt_model_free.restype = None
     L.srt_model_species.argtypes = [vp, C.POINTER(i), vp, vp, vp]
@@ -188,6 +192,32 @@ def interpsetup(interp_interpfile, yearday=0, milliseconds_day=0, use_igrf=0, us
     _check(lib().srt_model_grid(C.byref(h), os.fsencode(interp_interpfile), int(yearday), int(milliseconds_day), int(use_igrf), int(use_tsyganenko)),
            "srt_model_grid")
     return Model(h, "grid")
+
+
+def scatteredinterpsetup(interp_interpfile, window_scale, order, exact, local_window_scale, scaled=0, yearday=0, milliseconds_day=0, use_igrf=0,
+                         use_tsyganenko=0):
+    """modelnum 4 (driver:617-770): density by moving least squares over scattered samples; the driver's
+    --scattered_interp_window_scale, _order, _exact, _local_window_scale (scaled is 0 in the driver)."""
+    h = C.c_void_p()
+    _check(lib().srt_model_scattered(C.byref(h), os.fsencode(interp_interpfile), int(yearday), int(milliseconds_day), int(use_igrf),
+                                     int(use_tsyganenko), float(window_scale), int(order), int(exact), int(scaled), float(local_window_scale)),
+           "srt_model_scattered")
+    m = Model(h, "scattered")
+    n, mx, rad, nm = C.c_int64(), C.c_double(), C.c_double(), C.c_int()
+    cells = (C.c_int * 3)()
+    _check(lib().srt_model_scattered_info(h, C.byref(n), C.byref(mx), C.byref(rad), C.byref(nm), cells), "srt_model_scattered_info")
+    m.npoints, m.maxnearest, m.radius, m.nmono, m.cells = n.value, mx.value, rad.value, nm.value, tuple(cells)
+    return m
+
+
+def scattered_samples(model):
+    """The samples set-up kept, in the order a query walks them: [npoints][8] = x, y, z, log-density of species 1..4,
+    distance to the nearest other sample."""
+    out = np.empty((model.npoints, 8))
+    got = lib().srt_model_scattered_samples(model._h, _ptr(out), out.size)
+    if got != model.npoints:
+        raise SrtError("srt_model_scattered_samples: %d" % got)
+    return out
 
 
 class RayOutput:

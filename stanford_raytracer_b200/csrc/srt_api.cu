@@ -20,6 +20,7 @@
 #include "srt_team_tu.h"
 #include "srt_host_setup.h"
 #include "srt_grid_setup.h"
+#include "srt_scattered_setup.h"
 #include "srt_igrf_setup.h"
 #include "../../include/srt.h"
 
@@ -159,17 +160,20 @@ typedef void (*trace_kernel_t)(const SrtRunParams, const SrtBatch);
 typedef void (*eval_kernel_t)(long long, const double*, double*);
 
 // kernels are instantiated per density kind and field code (bit 0 IGRF, bit 1 TS05 external field)
+int density_slot(const SrtModel& M) { return M.density == SRT_DENS_NGO ? 0 : (M.density == SRT_DENS_SCAT ? 2 : 1); }
 trace_kernel_t pick_trace(const SrtModel& M) {
-  static const trace_kernel_t k[2][4] = {
+  static const trace_kernel_t k[3][4] = {
       {srt_trace_kernel<SRT_DENS_NGO, 0>, srt_trace_kernel<SRT_DENS_NGO, 1>, srt_trace_kernel<SRT_DENS_NGO, 2>, srt_trace_kernel<SRT_DENS_NGO, 3>},
-      {srt_trace_kernel<SRT_DENS_GRID, 0>, srt_trace_kernel<SRT_DENS_GRID, 1>, srt_trace_kernel<SRT_DENS_GRID, 2>, srt_trace_kernel<SRT_DENS_GRID, 3>}};
-  return k[M.density == SRT_DENS_NGO ? 0 : 1][(M.use_igrf ? 1 : 0) | (M.ts.on ? 2 : 0)];
+      {srt_trace_kernel<SRT_DENS_GRID, 0>, srt_trace_kernel<SRT_DENS_GRID, 1>, srt_trace_kernel<SRT_DENS_GRID, 2>, srt_trace_kernel<SRT_DENS_GRID, 3>},
+      {srt_trace_kernel<SRT_DENS_SCAT, 0>, srt_trace_kernel<SRT_DENS_SCAT, 1>, srt_trace_kernel<SRT_DENS_SCAT, 2>, srt_trace_kernel<SRT_DENS_SCAT, 3>}};
+  return k[density_slot(M)][(M.use_igrf ? 1 : 0) | (M.ts.on ? 2 : 0)];
 }
 eval_kernel_t pick_eval(const SrtModel& M) {
-  static const eval_kernel_t k[2][4] = {
+  static const eval_kernel_t k[3][4] = {
       {srt_eval_kernel<SRT_DENS_NGO, 0>, srt_eval_kernel<SRT_DENS_NGO, 1>, srt_eval_kernel<SRT_DENS_NGO, 2>, srt_eval_kernel<SRT_DENS_NGO, 3>},
-      {srt_eval_kernel<SRT_DENS_GRID, 0>, srt_eval_kernel<SRT_DENS_GRID, 1>, srt_eval_kernel<SRT_DENS_GRID, 2>, srt_eval_kernel<SRT_DENS_GRID, 3>}};
-  return k[M.density == SRT_DENS_NGO ? 0 : 1][(M.use_igrf ? 1 : 0) | (M.ts.on ? 2 : 0)];
+      {srt_eval_kernel<SRT_DENS_GRID, 0>, srt_eval_kernel<SRT_DENS_GRID, 1>, srt_eval_kernel<SRT_DENS_GRID, 2>, srt_eval_kernel<SRT_DENS_GRID, 3>},
+      {srt_eval_kernel<SRT_DENS_SCAT, 0>, srt_eval_kernel<SRT_DENS_SCAT, 1>, srt_eval_kernel<SRT_DENS_SCAT, 2>, srt_eval_kernel<SRT_DENS_SCAT, 3>}};
+  return k[density_slot(M)][(M.use_igrf ? 1 : 0) | (M.ts.on ? 2 : 0)];
 }
 
 // ---- set-up kernel of the gridded model: tricubic_compute_finite_difference_derivatives (libtricubic.f95:722-793).
@@ -245,6 +249,9 @@ struct GridReplica {
   double* d_nodes = nullptr;
   double* d_axes = nullptr;
   double* d_coef = nullptr;  // per-cell tricubic coefficients (NULL: on-the-fly path, SRT_GRID_COEF=0)
+  // modelnum 4: the sample records sorted by cell, and the first record of every cell
+  double* d_scat_pts = nullptr;
+  int* d_scat_cells = nullptr;
 };
 
 struct srt_model {
@@ -253,6 +260,7 @@ struct srt_model {
   double nus[SRT_NSPEC];
   // host copy of the grid file: f only (derivative slots zero) unless the file carried derivatives
   std::vector<double> h_nodes, h_axes;
+  srt_host::HostScat h_scat;  // modelnum 4: host copy of the sample records and the cell list
   bool file_has_derivatives = false;
   bool use_coef = true;
   std::mutex replica_mutex;
@@ -280,7 +288,7 @@ int launch_config(DevCtx* c, srt_model* m, long long nrays, int* mode_out, int* 
   int block = SRT_BLOCK_THREADS, nb = 1;
   if (mode) {
     block = srt_team_block_threads(nrays, c->num_sms);
-    if (m->M.ts.on && block > 512) block = 512;  // the kernels with the external field exist in the 128-register budget only
+    if ((m->M.ts.on || m->M.density == SRT_DENS_SCAT) && block > 512) block = 512;  // the kernels with the external field, and those of the scattered-sample model, exist in the 128-register budget only
     CK(srt_team_occupancy(m->M, block, &nb));
   } else {
     std::lock_guard<std::mutex> lk(m->replica_mutex);
@@ -318,11 +326,28 @@ unsigned long long ray_order_mul(long long nrays) {
 // finite-difference derivative passes and the per-cell coefficient table, once per device.
 int ensure_replica(DevCtx* c, srt_model* m, GridReplica* out) {
   *out = GridReplica();
-  if (m->M.density != SRT_DENS_GRID) return SRT_OK;
+  if (m->M.density != SRT_DENS_GRID && m->M.density != SRT_DENS_SCAT) return SRT_OK;
   std::lock_guard<std::mutex> lk(m->replica_mutex);
   auto it = m->replicas.find(c->dev);
   if (it != m->replicas.end()) { *out = it->second; return SRT_OK; }
   GridReplica r;
+  if (m->M.density == SRT_DENS_SCAT) {
+    const size_t pb = m->h_scat.pts.size() * sizeof(double), cb = m->h_scat.cell_start.size() * sizeof(int);
+    if (cudaMalloc(&r.d_scat_pts, pb) != cudaSuccess || cudaMalloc(&r.d_scat_cells, cb) != cudaSuccess) {
+      int rc = cuda_fail(cudaGetLastError(), "cudaMalloc(scattered samples)");
+      if (r.d_scat_pts) cudaFree(r.d_scat_pts);
+      return rc;
+    }
+    cudaError_t e = cudaMemcpy(r.d_scat_pts, m->h_scat.pts.data(), pb, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(r.d_scat_cells, m->h_scat.cell_start.data(), cb, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+      cudaFree(r.d_scat_pts); cudaFree(r.d_scat_cells);
+      return cuda_fail(e, "upload of the scattered samples");
+    }
+    m->replicas[c->dev] = r;
+    *out = r;
+    return SRT_OK;
+  }
   const SrtGrid& g = m->M.grid;
   const size_t nb = m->h_nodes.size() * sizeof(double), ax = m->h_axes.size() * sizeof(double);
   const size_t ncells = (m->use_coef && g.nx > 1 && g.ny > 1 && g.nz > 1) ? srt_grid_cell_count(g) : 0;
@@ -384,6 +409,12 @@ int device_model(DevCtx* c, srt_model* m, SrtModel* out) {
     out->grid.xs = r.d_axes;
     out->grid.ys = r.d_axes + m->M.grid.nx;
     out->grid.zs = r.d_axes + m->M.grid.nx + m->M.grid.ny;
+  } else if (m->M.density == SRT_DENS_SCAT) {
+    GridReplica r;
+    int rc = ensure_replica(c, m, &r);
+    if (rc) return rc;
+    out->scat.pts = r.d_scat_pts;
+    out->scat.cell_start = r.d_scat_cells;
   }
   return SRT_OK;
 }
@@ -593,6 +624,57 @@ int srt_model_grid(srt_model** m, const char* path, int yearday, int msec, int u
   return SRT_OK;
 }
 
+int srt_model_scattered(srt_model** m, const char* path, int yearday, int msec, int use_igrf, int use_tsyganenko, double window_scale, int order,
+                        int exact, int scaled, double local_window_scale) {
+  if (!m || !path) return SRT_E_ARG;
+  *m = nullptr;
+  std::vector<DevCtx*> devs;
+  int rc = active_devices(devs);
+  if (rc) return rc;
+  srt_model* mm = new (std::nothrow) srt_model();
+  if (!mm) return SRT_E_NOMEM;
+  memset(&mm->M, 0, sizeof mm->M);
+  const srt_host::ScatOptions opt = {window_scale, order, exact, scaled, local_window_scale};
+  rc = srt_host::load_scattered(path, opt, mm->M, mm->h_scat);
+  if (rc != 0) { delete mm; return rc == -3 ? SRT_E_UNSUPPORTED : SRT_E_IO; }
+  rc = finish_model(mm, yearday, msec, use_igrf, use_tsyganenko);
+  if (rc) { delete mm; return rc; }
+  mm->M.scat.pts = nullptr;  // filled per device at launch time
+  mm->M.scat.cell_start = nullptr;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  for (DevCtx* c : devs) {
+    GridReplica r;
+    if (cudaSetDevice(c->dev) != cudaSuccess) { rc = cuda_fail(cudaGetLastError(), "cudaSetDevice"); break; }
+    if ((rc = ensure_replica(c, mm, &r))) break;
+  }
+  cudaSetDevice(prev);
+  if (rc) { srt_model_free(mm); return rc; }
+  *m = mm;
+  return SRT_OK;
+}
+
+int srt_model_scattered_info(const srt_model* m, int64_t* npoints, double* maxnearest, double* radius, int* nmono, int* cells /*[3]*/) {
+  if (!m || m->M.density != SRT_DENS_SCAT) return SRT_E_ARG;
+  const SrtScat& s = m->M.scat;
+  if (npoints) *npoints = s.npts;
+  if (maxnearest) *maxnearest = s.maxnearest;
+  if (radius) *radius = s.radius;
+  if (nmono) *nmono = s.nmono;
+  if (cells) { cells[0] = s.ncx; cells[1] = s.ncy; cells[2] = s.ncz; }
+  return SRT_OK;
+}
+
+int64_t srt_model_scattered_samples(const srt_model* m, double* recs, int64_t capacity) {
+  if (!m || m->M.density != SRT_DENS_SCAT) return SRT_E_ARG;
+  const int64_t n = (int64_t)m->h_scat.pts.size();
+  if (recs) {
+    if (capacity < n) return SRT_E_ARG;
+    memcpy(recs, m->h_scat.pts.data(), sizeof(double) * (size_t)n);
+  }
+  return n / SRT_SCAT_REC;
+}
+
 void srt_model_free(srt_model* m) {
   if (!m) return;
   int prev = 0;
@@ -604,6 +686,8 @@ void srt_model_free(srt_model* m) {
     if (kv.second.d_nodes) cudaFree(kv.second.d_nodes);
     if (kv.second.d_axes) cudaFree(kv.second.d_axes);
     if (kv.second.d_coef) cudaFree(kv.second.d_coef);
+    if (kv.second.d_scat_pts) cudaFree(kv.second.d_scat_pts);
+    if (kv.second.d_scat_cells) cudaFree(kv.second.d_scat_cells);
   }
   if (!m->replicas.empty()) cudaSetDevice(prev);
   delete m;
@@ -695,6 +779,15 @@ int srt_model_eval_noalloc(const srt_model* m, int64_t n, const double* x, doubl
     Md.grid.xs = it->second.d_axes;
     Md.grid.ys = it->second.d_axes + mm->M.grid.nx;
     Md.grid.zs = it->second.d_axes + mm->M.grid.nx + mm->M.grid.ny;
+  } else if (mm->M.density == SRT_DENS_SCAT) {
+    std::lock_guard<std::mutex> lk(mm->replica_mutex);
+    auto it = mm->replicas.find(c->dev);
+    if (it == mm->replicas.end()) {
+      snprintf(g_cuda_err, sizeof g_cuda_err, "srt_model_eval_noalloc: the scattered-sample model is not yet on device %d; one srt_model_eval or trace call places it", c->dev);
+      return SRT_E_UNSUPPORTED;
+    }
+    Md.scat.pts = it->second.d_scat_pts;
+    Md.scat.cell_start = it->second.d_scat_cells;
   }
   std::lock_guard<std::mutex> bl(c->batch_mutex);
   if (!c->eval_static) {  // once per device, with that device current (current_ctx)

@@ -3,7 +3,7 @@
 // Same `--name=value` options (driver:181-228 common, :263-337 Ngo, :502-575 interp), same input ray file
 // (driver:1146), same output file byte for byte (driver:1197-1217).  The per-ray loop of the reference
 // (read a ray, raytracer_run, write its rows; driver:1144-1232) becomes: read all rays, srt_trace_batch on the GPU,
-// write all rows.  Models: --modelnum=1 (Ngo) and 3 (gridded); the others are not on the GPU path and are refused.
+// write all rows.  Models: --modelnum=1 (Ngo), 3 (gridded) and 4 (scattered samples); the others are not on the GPU path and are refused.
 //
 // Option parsing follows getopt_named (fortran/util.f95:53-84): an argument counts if it contains '=', its name is
 // the text between the first two characters and the first '=', the first match wins.  Integers are read as reals and
@@ -85,13 +85,20 @@ void usage() {
        "--outputper     output fields only every \"outputper\" steps\n"
        "--modelnum      (1) Ngo model\n"
        "                (3) Interpolated model (gridded data)\n"
-       "                (2, 4-7 are not available on the GPU path)\n"
+       "                (4) Interpolated model (scattered data)\n"
+       "                (2, 5-7 are not available on the GPU path)\n"
        "\n"
        " Ngo parameters (model 1):\n"
        "   --ngo_configfile     newray input filename\n"
        " Interp parameters (model 3):\n"
        "   --interp_interpfile  grid filename\n"
-       " Both:\n"
+       " Scattered interp parameters (model 4):\n"
+       "   --interp_interpfile  data filename\n"
+       "   --scattered_interp_window_scale        window radius as a factor of the maximum sample spacing\n"
+       "   --scattered_interp_order               monomial order (0..3)\n"
+       "   --scattered_interp_exact               exact (1) or inexact (0) weighting window\n"
+       "   --scattered_interp_local_window_scale  window width above the local average sample spacing\n"
+       " All:\n"
        "   --yearday            year and day, e.g., 1999098\n"
        "   --milliseconds_day   milliseconds of day\n"
        "   --use_igrf           (1=use, 0=do not use)\n"
@@ -158,8 +165,15 @@ int main(int argc, char** argv) {
   } else if (modelnum == 3) {
     if (!getopt_named("interp_interpfile", modelfile)) die(2, "--interp_interpfile is required for --modelnum=3");
     rc = srt_model_grid(&model, modelfile.c_str(), yearday, msec, use_igrf, use_tsy);
+  } else if (modelnum == 4) {  // driver:617-770 (scaled is fixed at 0 there, :722)
+    if (!getopt_named("interp_interpfile", modelfile)) die(2, "--interp_interpfile is required for --modelnum=4");
+    const double window_scale = need_real("scattered_interp_window_scale");
+    const int order = (int)std::floor(need_real("scattered_interp_order"));
+    const int exact = (int)std::floor(need_real("scattered_interp_exact"));
+    const double local_window_scale = need_real("scattered_interp_local_window_scale");
+    rc = srt_model_scattered(&model, modelfile.c_str(), yearday, msec, use_igrf, use_tsy, window_scale, order, exact, 0, local_window_scale);
   } else {
-    die(3, "--modelnum=" + std::to_string(modelnum) + " is not available on the GPU path (1 = Ngo, 3 = gridded)");
+    die(3, "--modelnum=" + std::to_string(modelnum) + " is not available on the GPU path (1 = Ngo, 3 = gridded, 4 = scattered samples)");
   }
   if (!rc && use_tsy == 1) {  // the parameters the driver reads into the adapter's state (raytracer_driver.f95:291-340)
     static const char* names[10] = {"tsyganenko_Pdyn", "tsyganenko_Dst", "tsyganenko_ByIMF", "tsyganenko_BzIMF", "tsyganenko_W1",

@@ -18,7 +18,7 @@
 #define SRT_MAX_DUCTS 10
 #define SRT_NSPEC 4
 
-enum SrtDensityKind { SRT_DENS_NGO = 0, SRT_DENS_GRID = 1 };
+enum SrtDensityKind { SRT_DENS_NGO = 0, SRT_DENS_GRID = 1, SRT_DENS_SCAT = 2 };
 
 struct SrtNgo {
   int num;     // number of species incl. electrons (NUM card), 2..4
@@ -58,6 +58,24 @@ struct SrtGrid {
   const double* zs;
 };
 
+// modelnum 4 (csrc/srt_scattered.h): scatteredinterpStateData (fortran/scattered_interp_dens_model_adapter.f95:17-48) with the
+// kd-tree replaced by a uniform cell list over the samples' bounding box
+struct SrtScat {
+  int npts, nspec;
+  int order, exact, scaled;  // lsinterp's arguments (driver:709-722: scaled is always 0 there)
+  int nmono;                 // J, monomials of degree <= order
+  unsigned char mono[64];    // exponents [J][3] in the order of tabular_monomials (lsinterp_mod.f95:73-95)
+  double maxnearest, window_scale;
+  double radius;             // maxnearest * window_scale, the search radius (adapter :247)
+  double local_scale;        // local_window_scale
+  double ox, oy, oz;         // corner of cell (0,0,0)
+  double inv_cell;           // 1 / cell edge
+  int ncx, ncy, ncz;
+  // device (or, in the CPU test build, host) pointers
+  const double* pts;         // [npts][8]: x, y, z, log-density of species 1..4, distance to the nearest other sample; sorted by cell
+  const int* cell_start;     // [ncx*ncy*ncz + 1]: first record of each cell (x fastest)
+};
+
 struct SrtIgrf {
   // Schmidt-normalised coefficients and recursion constants after RECALC_08
   // (geopack2008.for:883-1029), fp32 as in the reference
@@ -86,6 +104,7 @@ struct SrtModel {
   double cos_mu, sin_mu;  // cos/sin of the dipole tilt angle mu (T4.f95:13)
   SrtNgo ngo;
   SrtGrid grid;
+  SrtScat scat;
   SrtIgrf igrf;
   SrtTs05 ts;
 };

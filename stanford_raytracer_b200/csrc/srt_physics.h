@@ -273,11 +273,14 @@ SRT_HD void srt_field_sm(SrtModelRef MR, const double x[3], const double p[3], d
 
 // gridded log-density (srt_tricubic.h)
 SRT_HDN void srt_grid_density(const SrtGrid& g, const double x[3], double Ns[SRT_NSPEC]);
+// scattered samples, moving least squares (modelnum 4)
+#include "srt_scattered.h"
 
 // ------------------------------------------------------------------ funcPlasmaParams
 // DENS = SrtDensityKind, USE_IGRF = the field code: bit 0 IGRF instead of the dipole, bit 1 TS05 external field added.
 //   Ngo:  fortran/ngo_dens_model_adapter.f95:63-207
 //   grid: fortran/interp_dens_model_adapter.f95:148-269
+//   scattered samples: fortran/scattered_interp_dens_model_adapter.f95:214-370 (the same field block)
 template <int DENS, int USE_IGRF>
 SRT_HDP void srt_plasma(SrtModelRef MR, const double x[3], SrtPlasma& o) {
   SRT_COUNT(SRT_T_PLASMA);
@@ -303,6 +306,8 @@ SRT_HDP void srt_plasma(SrtModelRef MR, const double x[3], SrtPlasma& o) {
     o.Ns[1] = 1.0e6 * ani[1];
     o.Ns[2] = 1.0e6 * ani[2];
     o.Ns[3] = 1.0e6 * ani[3];
+  } else if (DENS == SRT_DENS_SCAT) {
+    srt_scat_density(M.scat, x, o.Ns);
   } else {
     srt_grid_density(M.grid, x, o.Ns);
   }

@@ -36,7 +36,15 @@ static team_kernel_t pick_team_ts(const SrtModel& M) {
   if (M.density == SRT_DENS_NGO) return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_NGO, 3, SRT_TEAM_MAXT_SMALL> : srt_trace_team_kernel<SRT_DENS_NGO, 2, SRT_TEAM_MAXT_SMALL>;
   return M.use_igrf ? srt_trace_team_kernel<SRT_DENS_GRID, 3, SRT_TEAM_MAXT_SMALL> : srt_trace_team_kernel<SRT_DENS_GRID, 2, SRT_TEAM_MAXT_SMALL>;
 }
+// modelnum 4 (scattered samples): a plasma evaluation is a moving-least-squares fit over the neighbours of the point, far
+// heavier than the rest of the attempt, and keeps a packed normal matrix per lane: the 128-register budget only
+static team_kernel_t pick_team_scat(const SrtModel& M) {
+  static const team_kernel_t k[4] = {srt_trace_team_kernel<SRT_DENS_SCAT, 0, SRT_TEAM_MAXT_SMALL>, srt_trace_team_kernel<SRT_DENS_SCAT, 1, SRT_TEAM_MAXT_SMALL>,
+                                     srt_trace_team_kernel<SRT_DENS_SCAT, 2, SRT_TEAM_MAXT_SMALL>, srt_trace_team_kernel<SRT_DENS_SCAT, 3, SRT_TEAM_MAXT_SMALL>};
+  return k[(M.use_igrf ? 1 : 0) | (M.ts.on ? 2 : 0)];
+}
 static team_kernel_t pick_team(const SrtModel& M, int block) {
+  if (M.density == SRT_DENS_SCAT) return pick_team_scat(M);
   if (M.ts.on) return pick_team_ts(M);
   return block > SRT_TEAM_MAXT_SMALL ? pick_team_t<1024>(M) : pick_team_t<SRT_TEAM_MAXT_SMALL>(M);
 }

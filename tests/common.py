@@ -120,6 +120,83 @@ class HostEmu:
         return dict(rows=rows[:n].copy(), stopcond=sc.value, nrejected=nr.value, ncone=nc.value, fixed_cone_exit=ce.value, dir0=dir0)
 
 
+class HostEmuScattered(HostEmu):
+    """modelnum 4 through the product's own set-up and device code, compiled for the CPU (test-only)."""
+
+    def __init__(self, path, window_scale, order, exact, local_window_scale, scaled=0, yearday=2010001, msec=0, use_igrf=0):
+        build_hostemu()
+        E = C.CDLL(os.path.join(BUILD, "libsrt_hostemu.so"))
+        d, i, vp, l = C.c_double, C.c_int, C.c_void_p, C.c_long
+        E.emu_model_scattered.restype = vp
+        E.emu_model_scattered.argtypes = [C.c_char_p, i, i, i, d, i, i, i, d]
+        E.emu_scattered_state.restype = l
+        E.emu_scattered_state.argtypes = [vp, vp, l, vp, vp]
+        E.emu_scattered_neighbours.restype = l
+        E.emu_scattered_neighbours.argtypes = [vp, vp, vp, l]
+        E.emu_scattered_lsinterp.restype = i
+        E.emu_scattered_lsinterp.argtypes = [vp, vp, vp]
+        E.emu_plasma.argtypes = [vp, l, vp, vp]
+        E.emu_model_tsyganenko.argtypes = [vp, vp, i, i]
+        E.emu_trace.restype = l
+        E.emu_trace.argtypes = [vp, vp, vp, d, d, d, d, i, d, i, d, i, vp, l, vp, vp, vp, vp]
+        self.E, self.yearday, self.msec = E, yearday, msec
+        self.h = E.emu_model_scattered(path.encode(), yearday, msec, use_igrf, window_scale, order, exact, scaled, local_window_scale)
+        if not self.h:
+            raise RuntimeError("hostemu scattered model setup failed")
+        info = np.zeros(5, dtype=np.int32)
+        dinfo = np.zeros(2)
+        E.emu_scattered_state(self.h, None, 0, info.ctypes.data, dinfo.ctypes.data)
+        self.npts, self.nmono, self.cells = int(info[0]), int(info[1]), tuple(int(v) for v in info[2:5])
+        self.maxnearest, self.radius = dinfo[0], dinfo[1]
+        self.records = np.empty((self.npts, 8))
+        E.emu_scattered_state(self.h, self.records.ctypes.data, self.records.size, info.ctypes.data, dinfo.ctypes.data)
+
+    def neighbours(self, x):
+        """indices into self.records, in the order the device code walks them"""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        n = self.E.emu_scattered_neighbours(self.h, x.ctypes.data, None, 0)
+        out = np.empty(n, dtype=np.int32)
+        self.E.emu_scattered_neighbours(self.h, x.ctypes.data, out.ctypes.data, n)
+        return out
+
+    def lsinterp(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        fi = np.zeros(4)
+        st = self.E.emu_scattered_lsinterp(self.h, x.ctypes.data, fi.ctypes.data)
+        return st, fi
+
+
+def write_scattered_file(path, n, seed=1, rmin=1.05, rmax=5.0, nspec=4, duplicates=0, inside=0, digits=17):
+    """A sample file for modelnum 4 in the format of gcpm_dens_model_buildgrid_random (header, qs, ms, then `pos, log(Ns)` per
+    sample): positions drawn with a density falling with radius inside a spherical shell (SM, metres), log-densities of the
+    Ngo model there (the product's own srt_model_eval is NOT used: values come from the CPU oracle).  duplicates: that many
+    samples repeated verbatim with another value; inside: that many samples inside the Earth."""
+    rng = np.random.default_rng(seed)
+    r = R_E * (rmin + (rmax - rmin) * rng.random(n) ** 1.7)
+    u = rng.normal(size=(n, 3))
+    u /= np.linalg.norm(u, axis=1)[:, None]
+    pos = r[:, None] * u
+    if inside:
+        pos[:inside] *= (0.5 * R_E / r[:inside])[:, None]
+    om = ol.OracleModel("ngo", NGO_CFG)
+    pl = om.plasma(pos)
+    om.close()
+    logn = np.log(np.maximum(pl[:, 4:4 + nspec], 1e-30))
+    if inside:
+        logn[:inside] = 0.0
+    if duplicates:
+        pos = np.vstack([pos, pos[5:5 + duplicates]])
+        logn = np.vstack([logn, logn[5:5 + duplicates] + 1.0])
+    with open(path, "w") as f:
+        f.write("%d %.17e %.17e %.17e %.17e %.17e %.17e\n" % ((nspec,) + tuple(np.ravel([pos.min(0), pos.max(0)], order="F"))))
+        f.write(" ".join("%.17e" % v for v in pl[0, 0:nspec]) + "\n")
+        f.write(" ".join("%.17e" % v for v in pl[0, 8:8 + nspec]) + "\n")
+        fmt = "%%.%de" % digits
+        for p, v in zip(pos, logn):
+            f.write(" ".join(fmt % t for t in list(p) + list(v)) + "\n")
+    return pos, logn
+
+
 # Rays whose FIRST attempt that passes the error test leaves the resonance cone (launched 1-5 degrees inside the cone with a
 # large dt0): raytracer.f95:821 sets the local `w` before the cone test at :891, so the retry already carries the dF/dk
 # error term (ADVICE r1: with `w` set only on acceptance, 57 of 95 such rays differed from the oracle).

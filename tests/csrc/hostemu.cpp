@@ -10,6 +10,7 @@
 #ifdef EMU_HAVE_GRID
 #include "../../stanford_raytracer_b200/csrc/srt_grid_setup.h"
 #include "../../stanford_raytracer_b200/csrc/srt_igrf_setup.h"
+#include "../../stanford_raytracer_b200/csrc/srt_scattered_setup.h"
 #endif
 
 #if defined(SRT_TALLY)
@@ -96,6 +97,10 @@ static void plasma_n(const SrtModel& M, long n, const double* x, double* out) {
       constexpr int D = 0;                                                                         \
       if (f_ == 0) { constexpr int I = 0; CALL; } else if (f_ == 1) { constexpr int I = 1; CALL; } \
       else if (f_ == 2) { constexpr int I = 2; CALL; } else { constexpr int I = 3; CALL; }         \
+    } else if ((M).density == SRT_DENS_SCAT) {                                                     \
+      constexpr int D = 2;                                                                         \
+      if (f_ == 0) { constexpr int I = 0; CALL; } else if (f_ == 1) { constexpr int I = 1; CALL; } \
+      else if (f_ == 2) { constexpr int I = 2; CALL; } else { constexpr int I = 3; CALL; }         \
     } else {                                                                                       \
       constexpr int D = 1;                                                                         \
       if (f_ == 0) { constexpr int I = 0; CALL; } else if (f_ == 1) { constexpr int I = 1; CALL; } \
@@ -141,6 +146,44 @@ void* emu_model_grid(const char* path, int yearday, int msec, int use_igrf) {
   srt_host::igrf_recalc(yearday, msec, M->igrf);
   return M;  // hg leaks with the model: test-only
 }
+#endif
+#ifdef EMU_HAVE_GRID
+// modelnum 4 through the product's own set-up (csrc/srt_scattered_setup.h)
+void* emu_model_scattered(const char* path, int yearday, int msec, int use_igrf, double window_scale, int order, int exact, int scaled,
+                          double local_window_scale) {
+  SrtModel* M = new SrtModel();
+  memset(M, 0, sizeof *M);
+  srt_host::HostScat* hs = new srt_host::HostScat();
+  const srt_host::ScatOptions opt = {window_scale, order, exact, scaled, local_window_scale};
+  if (srt_host::load_scattered(path, opt, *M, *hs) != 0) { delete M; delete hs; return nullptr; }
+  srt_host::set_time(*M, yearday, msec);
+  M->use_igrf = use_igrf;
+  srt_host::igrf_recalc(yearday, msec, M->igrf);
+  return M;  // hs leaks with the model: test-only
+}
+// the samples as set-up laid them out: records [npts][8] in cell order; info = npts, nmono, ncx, ncy, ncz; dinfo = maxnearest, radius
+long emu_scattered_state(void* m, double* recs, long cap, int* info, double* dinfo) {
+  const SrtScat& s = ((const SrtModel*)m)->scat;
+  info[0] = s.npts; info[1] = s.nmono; info[2] = s.ncx; info[3] = s.ncy; info[4] = s.ncz;
+  dinfo[0] = s.maxnearest; dinfo[1] = s.radius;
+  if (recs && cap >= (long)s.npts * SRT_SCAT_REC) memcpy(recs, s.pts, sizeof(double) * (size_t)s.npts * SRT_SCAT_REC);
+  return s.npts;
+}
+// the neighbours of x in the order the device code walks them: indices into the records above
+long emu_scattered_neighbours(void* m, const double* x, int* out, long cap) {
+  const SrtScat& s = ((const SrtModel*)m)->scat;
+  SrtScatWalk w;
+  double d2;
+  long n = 0;
+  srt_scat_walk_begin(s, x, w);
+  while (const double* p = srt_scat_walk_next(s, x, s.radius * s.radius, w, d2)) {
+    if (n < cap) out[n] = (int)((p - s.pts) / SRT_SCAT_REC);
+    ++n;
+  }
+  return n;
+}
+// lsinterp alone: fi[4] and the status
+int emu_scattered_lsinterp(void* m, const double* x, double* fi) { return srt_scat_lsinterp(((const SrtModel*)m)->scat, x, fi); }
 #endif
 #ifdef EMU_HAVE_GRID
 // what load_grid read: dims = nspec nx ny nz; out[q][node][s] for the eight arrays q (f and the seven derivative arrays)

@@ -179,6 +179,70 @@ class OracleModel:
         return dict(accepted=acc, last_row=last, nrows=nrows, stopcond=stop, nrejected=nrej)
 
 
+class OracleScattered(OracleModel):
+    """modelnum 4 (oracle/orc_scattered.h): kd-tree + lsinterp as the reference states them.  perm = the insertion order the
+    reference leaves to an unseeded random_number (None: file order); root_quirk: the root sample's nearest distance 0."""
+
+    def __init__(self, path, window_scale, order, exact, local_window_scale, scaled=0, yearday=2010001, msec=0, use_igrf=0, perm=None,
+                 root_quirk=False, libm=False):
+        self.L = lib(libm)
+        L, d, i, l, vp = self.L, C.c_double, C.c_int, C.c_long, C.c_void_p
+        L.orc_model_scattered.restype = vp
+        L.orc_model_scattered.argtypes = [C.c_char_p, i, i, i, d, i, i, i, d, vp, l, i]
+        L.orc_scattered_info.argtypes = [vp, vp]
+        L.orc_scattered_search.restype = l
+        L.orc_scattered_search.argtypes = [vp, vp, vp, l]
+        L.orc_scattered_impose_order.restype = l
+        L.orc_scattered_impose_order.argtypes = [vp, l, vp]
+        L.orc_scattered_interpolate.restype = i
+        L.orc_scattered_interpolate.argtypes = [vp, vp, vp]
+        L.orc_lsinterp_found.restype = i
+        L.orc_lsinterp_found.argtypes = [vp, l, vp, vp, i, d, i, i, i, d, vp]
+        pm = None if perm is None else np.ascontiguousarray(perm, dtype=np.int64)
+        self.h = L.orc_model_scattered(path.encode(), yearday, msec, use_igrf, window_scale, order, exact, scaled, local_window_scale, _p(pm),
+                                       0 if pm is None else len(pm), int(root_quirk))
+        if not self.h:
+            raise RuntimeError("oracle scattered model setup failed: %s" % path)
+        self.del_ = L.orc_model_del(self.h)
+        self.opts = (order, exact, scaled, local_window_scale)
+        info = np.empty(4)
+        L.orc_scattered_info(self.h, _p(info))
+        self.maxnearest, self.nkept, self.nduplicates, self.root_nearest = info[0], int(info[1]), int(info[2]), info[3]
+        self.radius = self.maxnearest * window_scale
+
+    def search(self, x, nspec):
+        """neighbours of x in the tree's traversal order: [I][3 + nspec + 1]"""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        n = self.L.orc_scattered_search(self.h, _p(x), None, 0)
+        out = np.empty((n, 3 + nspec + 1))
+        self.L.orc_scattered_search(self.h, _p(x), _p(out), n)
+        return out
+
+    def impose_order(self, pts):
+        """from now on a query returns its neighbours in the order of pts [n][3] (the one thing the reference's source leaves
+        open); every sample must be among them"""
+        pts = np.ascontiguousarray(pts, dtype=np.float64)
+        missing = self.L.orc_scattered_impose_order(self.h, len(pts), _p(pts))
+        assert missing == 0 and len(pts) == self.nkept
+        return self
+
+    def interpolate(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        fi = np.zeros(4)
+        st = self.L.orc_scattered_interpolate(self.h, _p(x), _p(fi))
+        return st, fi
+
+    def lsinterp_found(self, x, pts, vals):
+        """lsinterp on neighbour arrays in the caller's order (vals: [I][nspec + 1], last = nearest distance)"""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        pts = np.ascontiguousarray(pts, dtype=np.float64)
+        vals = np.ascontiguousarray(vals, dtype=np.float64)
+        fi = np.zeros(4)
+        order, exact, scaled, lws = self.opts
+        st = self.L.orc_lsinterp_found(_p(x), len(pts), _p(pts), _p(vals), vals.shape[1], self.radius, order, exact, scaled, lws, _p(fi))
+        return st, fi
+
+
 class DedupModel:
     """oracle/_build/libsrt_dedup.so: the GPU kernels' evaluation order on the host at -O3 (bench.py cpu_baseline,
     "deduplicated" mode).  Read-only during a trace: one instance serves every worker thread."""

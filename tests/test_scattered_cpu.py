@@ -1,0 +1,249 @@
+"""modelnum 4 (scattered samples, moving least squares) on the CPU: the oracle's restatement of the reference
+(oracle/orc_scattered.h: kd-tree, lsinterp, dposv as the Fortran states them) against known answers, and the product's
+set-up and device code (csrc/srt_scattered*.h, compiled for the host by tests/csrc/hostemu.cpp) against the oracle.
+
+What can be equal and what cannot: the reference inserts its samples in the order of an unseeded random permutation
+(fortran/scattered_interp_dens_model_adapter.f95:141), so the ORDER in which a radius query returns its neighbours is not
+defined by the reference's source; the SET is.  Hence:
+  * neighbour sets: equal, exactly;
+  * lsinterp given the product's neighbour order: equal bit for bit;
+  * end to end (each side in its own order): equal to the rounding of sums taken in another order -- the tolerance below is
+    measured against the difference between two insertion orders of the oracle itself.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import common
+import oracle_lib as ol
+
+R_E = common.R_E
+OPTS = dict(window_scale=1.6, order=2, exact=0, local_window_scale=3.0)
+
+
+@pytest.fixture(scope="module")
+def sample_file(tmp_path_factory):
+    path = str(tmp_path_factory.mktemp("scat") / "samples.txt")
+    pos, logn = common.write_scattered_file(path, 3000, seed=3, duplicates=7, inside=4)
+    return path, pos, logn
+
+
+@pytest.fixture(scope="module")
+def models(sample_file):
+    path = sample_file[0]
+    return common.HostEmuScattered(path, **OPTS), ol.OracleScattered(path, **OPTS)
+
+
+def query_points(n, seed=11, rmin=1.2, rmax=4.5):
+    rng = np.random.default_rng(seed)
+    u = rng.normal(size=(n, 3))
+    u /= np.linalg.norm(u, axis=1)[:, None]
+    return R_E * (rmin + (rmax - rmin) * rng.random(n))[:, None] * u
+
+
+def test_polynomial_reproduction_of_the_oracle(tmp_path):
+    """Moving least squares of degree p reproduces every polynomial of degree <= p exactly (Levin): a known answer that owes
+    nothing to the reference's source.  Samples of a quadratic in a box outside the Earth, orders 2 and 3, both windows."""
+    rng = np.random.default_rng(5)
+    n = 1500
+    pos = np.array([3.0, 0.0, 0.0]) * R_E + (rng.random((n, 3)) - 0.5) * 0.6 * R_E
+    s = (pos - pos.mean(0)) / (0.3 * R_E)
+    f = 1.0 + 0.5 * s[:, 0] - 0.25 * s[:, 1] + 0.1 * s[:, 2] + 0.3 * s[:, 0] * s[:, 1] - 0.2 * s[:, 2] ** 2
+    path = str(tmp_path / "quad.txt")
+    with open(path, "w") as fh:
+        fh.write("1 0 0 0 0 0 0\n-1.602e-19\n9.10938188e-31\n")
+        for p, v in zip(pos, f):
+            fh.write("%.17e %.17e %.17e %.17e\n" % (p[0], p[1], p[2], v))
+    q = np.array([3.0, 0.0, 0.0]) * R_E + (rng.random((40, 3)) - 0.5) * 0.3 * R_E
+    sq = (q - pos.mean(0)) / (0.3 * R_E)
+    want = 1.0 + 0.5 * sq[:, 0] - 0.25 * sq[:, 1] + 0.1 * sq[:, 2] + 0.3 * sq[:, 0] * sq[:, 1] - 0.2 * sq[:, 2] ** 2
+    for order in (2, 3):
+        for exact in (0, 1):
+            om = ol.OracleScattered(path, window_scale=2.5, order=order, exact=exact, local_window_scale=3.0)
+            he = common.HostEmuScattered(path, window_scale=2.5, order=order, exact=exact, local_window_scale=3.0)
+            for x, w in zip(q, want):
+                st, fi = om.interpolate(x)
+                assert st == 0
+                assert abs(fi[0] - w) < 2e-7, (order, exact, fi[0], w)
+                st2, fi2 = he.lsinterp(x)
+                assert st2 == 0 and abs(fi2[0] - w) < 2e-7
+            om.close()
+    # order 1 does not reproduce a quadratic: the test above is not vacuous
+    om = ol.OracleScattered(path, window_scale=2.5, order=1, exact=0, local_window_scale=3.0)
+    assert max(abs(om.interpolate(x)[1][0] - w) for x, w in zip(q, want)) > 1e-3
+    om.close()
+
+
+def test_setup_equals_the_oracle(sample_file, models):
+    """samples kept (repeated positions dropped), every sample's nearest distance, maxnearest: product's cell lists == kd-tree"""
+    path, pos, logn = sample_file
+    he, om = models
+    assert om.nduplicates == 7 and he.npts == om.nkept == 3000
+    assert he.maxnearest == om.maxnearest and he.radius == om.radius
+    # brute force over the file's distinct positions
+    p = pos[:3000]
+    d2 = ((p[:, None, :] - p[None, :, :]) ** 2)
+    d2 = (d2[:, :, 0] + d2[:, :, 1]) + d2[:, :, 2]
+    np.fill_diagonal(d2, np.inf)
+    nearest = np.sqrt(d2.min(1))
+    outside = (p[:, 0] * p[:, 0] + p[:, 1] * p[:, 1]) + p[:, 2] * p[:, 2] >= R_E * R_E
+    assert outside.sum() == 2996
+    assert he.maxnearest == nearest[outside].max()
+    rec = he.records
+    key = {tuple(v): i for i, v in enumerate(p)}
+    idx = np.array([key[tuple(v)] for v in rec[:, :3]])
+    assert len(set(idx)) == 3000
+    assert np.array_equal(rec[:, 3:7], logn[idx])  # of two samples at one position the first in the file stays
+    assert np.array_equal(rec[:, 7], np.where(outside[idx], nearest[idx], 1.0))
+
+
+def test_root_quirk_of_the_reference_is_restated(sample_file):
+    """kdtree_nearest starts from best = root: the root sample's own nearest distance comes out 0 (kdtree_mod.f95:397-418).
+    The oracle restates it (root_quirk=True); the product and the comparisons above use the true distance."""
+    path = sample_file[0]
+    perm = np.r_[10, 0:10, 11:3007]  # (samples 0-3 of the file lie inside the Earth and get no nearest distance at all)
+    q = ol.OracleScattered(path, root_quirk=True, perm=perm, **OPTS)
+    t = ol.OracleScattered(path, root_quirk=False, perm=perm, **OPTS)
+    assert q.root_nearest == 0.0 and t.root_nearest > 1.0e3
+    assert q.maxnearest == t.maxnearest  # (unless the root happens to hold the largest distance)
+    q.close(); t.close()
+
+
+def test_neighbour_sets_equal_and_lsinterp_bitwise_in_the_same_order(models):
+    he, om = models
+    xs = query_points(300)
+    nb_counts = []
+    for x in xs:
+        mine = he.neighbours(x)
+        theirs = om.search(x, 4)
+        nb_counts.append(len(mine))
+        a = he.records[mine]
+        # the same set (compared as sorted rows), not the same order
+        assert len(a) == len(theirs)
+        ka = a[np.lexsort(a[:, :3].T[::-1])]
+        kb = theirs[np.lexsort(theirs[:, :3].T[::-1])]
+        assert np.array_equal(ka, kb)
+        # the oracle's lsinterp fed the product's order == the product's device code, bit for bit
+        st_o, fi_o = om.lsinterp_found(x, a[:, :3], a[:, 3:8])
+        st_p, fi_p = he.lsinterp(x)
+        assert st_o == st_p
+        assert np.array_equal(fi_o, fi_p), (fi_o, fi_p)
+    assert min(nb_counts) >= 10 and max(nb_counts) > 100  # sparse and dense neighbourhoods both occur
+
+
+@pytest.mark.parametrize("order,exact,scaled", [(0, 0, 0), (1, 1, 0), (2, 1, 0), (3, 0, 0), (2, 0, 1), (3, 1, 1)])
+def test_every_option_bitwise_in_the_same_order(sample_file, order, exact, scaled):
+    path = sample_file[0]
+    kw = dict(window_scale=1.8, order=order, exact=exact, local_window_scale=2.5, scaled=scaled)
+    he, om = common.HostEmuScattered(path, **kw), ol.OracleScattered(path, **kw)
+    for x in query_points(60, seed=order * 7 + exact):
+        a = he.records[he.neighbours(x)]
+        st_o, fi_o = om.lsinterp_found(x, a[:, :3], a[:, 3:8])
+        st_p, fi_p = he.lsinterp(x)
+        assert st_o == st_p and np.array_equal(fi_o, fi_p)
+    om.close()
+
+
+def test_failures_as_the_reference(sample_file):
+    """too few points in the sphere: status 2, fi = 0, density exp(0) = 1 (adapter :247-262); inside the Earth: density 0"""
+    path = sample_file[0]
+    kw = dict(window_scale=0.05, order=2, exact=0, local_window_scale=3.0)
+    he, om = common.HostEmuScattered(path, **kw), ol.OracleScattered(path, **kw)
+    x = np.array([[4.4 * R_E, 0.3 * R_E, 0.1 * R_E], [0.5 * R_E, 0.0, 0.0], [np.inf, 0.0, 0.0], [np.nan, 1.0, 1.0]])
+    st, fi = he.lsinterp(x[0])
+    assert st == 2 and om.interpolate(x[0])[0] == 2 and not fi.any()
+    a, b = he.plasma(x), om.plasma(x)
+    assert np.array_equal(a[:, 4:8], b[:, 4:8], equal_nan=True)
+    assert np.array_equal(a[0, 4:8], np.ones(4)) and not a[1, 4:8].any() and np.array_equal(a[2, 4:8], np.ones(4)) and not a[3, 4:8].any()
+    om.close()
+
+
+def test_end_to_end_plasma_against_the_oracle(sample_file, models):
+    """funcPlasmaParams, each side in its own neighbour order.  The yardstick for the tolerance is the reference's own
+    indeterminacy: the oracle under two insertion orders."""
+    path = sample_file[0]
+    he, om = models
+    rng = np.random.default_rng(2)
+    om2 = ol.OracleScattered(path, perm=np.r_[rng.permutation(3000), 3000:3007], **OPTS)  # (the repeated positions last: the same survivors)
+    xs = query_points(400, seed=21)
+    a, b, c = he.plasma(xs), om.plasma(xs), om2.plasma(xs)
+    assert np.array_equal(a[:, 16:19], b[:, 16:19])  # the field block is the adapters' common one: bit for bit
+    assert np.array_equal(a[:, 0:4], b[:, 0:4]) and np.array_equal(a[:, 8:12], b[:, 8:12])
+    rel_self = np.abs(c[:, 4:8] / b[:, 4:8] - 1.0).max()
+    rel = np.abs(a[:, 4:8] / b[:, 4:8] - 1.0).max()
+    print("relative difference of Ns: product vs oracle %.3g; oracle vs oracle under another insertion order %.3g" % (rel, rel_self))
+    assert rel < 1e-9 and rel < 50 * max(rel_self, 1e-15)
+    # and the interpolant is the Ngo model the samples came from, to the accuracy 3000 samples allow
+    ngo = ol.OracleModel("ngo", common.NGO_CFG).plasma(xs)
+    err = np.abs(np.log(a[:, 4] / ngo[:, 4]))
+    assert np.median(err) < 0.15
+    om2.close()
+
+
+def test_whole_rays_bitwise_given_the_neighbour_order(sample_file, models):
+    """raytracer_run over modelnum 4.  With the one thing the reference leaves open -- the order of a query's neighbours --
+    set to the product's (OracleScattered.impose_order), the oracle's kd-tree + lsinterp + integrator and the product's cell
+    list + device code give the same rows bit for bit: adaptive and fixed step, IGRF and dipole."""
+    path = sample_file[0]
+    he = models[0]
+    pos0, dir0, w0 = common.launch_grid([2000.0, 8000.0], [25.0, 40.0], alt_km=3000.0)
+    for use_igrf, fixed in ((0, 0), (1, 0), (0, 1)):
+        h = common.HostEmuScattered(path, use_igrf=use_igrf, **OPTS)
+        om = ol.OracleScattered(path, use_igrf=use_igrf, **OPTS).impose_order(h.records[:, :3])
+        xs = query_points(100, seed=33)
+        assert np.array_equal(h.plasma(xs), om.plasma(xs))
+        prm = dict(common.C2, maxsteps=60, tmax=0.5, fixedstep=fixed)
+        steps = 0
+        for r in range(len(w0)):
+            o = om.trace(pos0[r], [0, 0, 0], w0[r], **prm)
+            g = h.trace(pos0[r], [0, 0, 0], w0[r], **prm)
+            assert g["stopcond"] == o["stopcond"] and g["rows"].shape == o["rows"].shape
+            assert np.array_equal(g["rows"], o["rows"], equal_nan=True)
+            assert g["nrejected"] == o["nrejected"] and g["ncone"] == o["ncone"]
+            steps += len(g["rows"])
+        assert steps > 100
+        om.close()
+
+
+def test_whole_rays_spread_of_the_reference_itself(sample_file, models):
+    """Without that: the normal equations of lsinterp are formed from monomials in metres (entries 1 ... 1e24), a fit keeps
+    about 8 digits, and dF/dx differences it over del = 1e-6: the reference's own rays move by per cent between two of its
+    insertion orders after a few dozen steps.  The product, in its order, stays within that spread."""
+    path = sample_file[0]
+    he, om = models
+    om2 = ol.OracleScattered(path, perm=np.r_[np.random.default_rng(2).permutation(3000), 3000:3007], **OPTS)
+    pos0, dir0, w0 = common.launch_grid([2000.0, 8000.0], [25.0, 40.0], alt_km=3000.0)
+    prm = dict(common.C2, maxsteps=12, tmax=0.5, fixedstep=1)
+    mine, own = 0.0, 0.0
+    for r in range(len(w0)):
+        o = om.trace(pos0[r], [0, 0, 0], w0[r], **prm)
+        o2 = om2.trace(pos0[r], [0, 0, 0], w0[r], **prm)
+        g = he.trace(pos0[r], [0, 0, 0], w0[r], **prm)
+        assert g["rows"].shape == o["rows"].shape == o2["rows"].shape
+        scale = np.abs(o["rows"][:, 1:4]).max() + 1e-300
+        mine = max(mine, np.abs(g["rows"][:, 1:4] - o["rows"][:, 1:4]).max() / scale)
+        own = max(own, np.abs(o2["rows"][:, 1:4] - o["rows"][:, 1:4]).max() / scale)
+    print("positions after 12 fixed steps: product vs oracle %.3g, oracle vs oracle under another insertion order %.3g" % (mine, own))
+    assert mine < 1e-3 and own < 1e-3
+    om2.close()
+
+
+def test_file_reader_follows_list_directed_rules(tmp_path):
+    """commas, D exponents, records continuing over lines, and the list ending at the first bad READ (adapter :107-110)"""
+    path = str(tmp_path / "odd.txt")
+    with open(path, "w") as fh:
+        fh.write("2, 0 0 0 0 0 0\n-1.602D-19 1.602d-19\n9.1e-31,\n1.67e-27\n")
+        for i in range(30):
+            fh.write("%.6e,%.6e\n%.6e %.3f %.3f\n" % (2e7 + 1e5 * i, 1e5 * (i % 5), 2e5 * (i % 3), 20.0 + 0.01 * i, 19.0))
+    clean = str(tmp_path / "clean.txt")
+    with open(clean, "w") as fh:
+        fh.write(open(path).read())
+    with open(path, "a") as fh:
+        fh.write("oops 1 2 3 4\n3e7 0 0 1 1\n")  # iostat /= 0 ends the list: the record after it is never read
+    he = common.HostEmuScattered(path, window_scale=30.0, order=1, exact=0, local_window_scale=3.0)
+    om = ol.OracleScattered(clean, window_scale=30.0, order=1, exact=0, local_window_scale=3.0)  # (the oracle's reader knows clean files only)
+    assert he.npts == om.nkept == 30 and he.maxnearest == om.maxnearest
+    out = he.plasma(np.array([[2.15e7, 2e5, 2e5]]))
+    assert out[0, 0] == -1.602e-19 and out[0, 1] == 1.602e-19 and out[0, 9] == 1.67e-27 and out[0, 6] == 0.0
+    om.close()

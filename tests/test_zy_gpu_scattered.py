@@ -1,0 +1,113 @@
+"""modelnum 4 (scattered samples, moving least squares; SURVEY.md section 8 row f4, second half) on the GPU, through the C ABI,
+against the CPU oracle (oracle/orc_scattered.h: the reference's kd-tree, lsinterp and dposv restated).
+
+The reference leaves one thing open -- the order in which a query returns its neighbours (its kd-tree is filled in the order of
+an unseeded random permutation) -- so the oracle is handed the product's order (OracleScattered.impose_order, the samples as
+srt_model_scattered_samples returns them); with it the comparison is BIT-EXACT: evaluation kernel and both trace kernels.
+tests/test_scattered_cpu.py holds the CPU side (known answers, neighbour sets, set-up, spread of the reference itself).
+
+The file name sorts after the other GPU tests and before test_zz_no_alloc.py: written in the last session of the round, after
+the GPU budget was spent -- a failure here hides nothing but the allocation-free entry point's test."""
+import os
+
+import numpy as np
+import pytest
+
+import common
+import oracle_lib as ol
+from test_scattered_cpu import OPTS, query_points
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def srt(built):
+    import stanford_raytracer_b200 as s
+    s.init(0)
+    return s
+
+
+@pytest.fixture(scope="module")
+def sample_path(tmp_path_factory):
+    path = str(tmp_path_factory.mktemp("scat_gpu") / "samples.txt")
+    common.write_scattered_file(path, 3000, seed=3, duplicates=7, inside=4)
+    return path
+
+
+def pair(srt, path, use_igrf=0, **kw):
+    o = dict(OPTS, **kw)
+    m = srt.scatteredinterpsetup(path, o["window_scale"], o["order"], o["exact"], o["local_window_scale"], scaled=o.get("scaled", 0),
+                                 yearday=2010001, milliseconds_day=0, use_igrf=use_igrf)
+    om = ol.OracleScattered(path, use_igrf=use_igrf, **o).impose_order(srt.scattered_samples(m)[:, :3])
+    return m, om
+
+
+def test_setup_through_the_c_abi(srt, sample_path):
+    m, om = pair(srt, sample_path)
+    he = common.HostEmuScattered(sample_path, **OPTS)
+    assert m.npoints == om.nkept == 3000 and m.maxnearest == om.maxnearest and m.radius == om.radius and m.nmono == 10
+    assert m.cells == he.cells and np.array_equal(srt.scattered_samples(m), he.records)
+    assert m.nspec == 4 and m.kernel_info(1000)["block"] <= 512
+    om.close()
+
+
+@pytest.mark.parametrize("use_igrf,order,exact,scaled", [(0, 2, 0, 0), (1, 2, 1, 0), (0, 3, 0, 0), (0, 1, 1, 1), (1, 0, 0, 0)])
+def test_plasma_parameters_bitwise(srt, sample_path, use_igrf, order, exact, scaled):
+    m, om = pair(srt, sample_path, use_igrf, order=order, exact=exact, scaled=scaled)
+    x = np.vstack([query_points(1500, seed=40 + order), [[0.5 * common.R_E, 0, 0], [np.inf, 0, 0], [np.nan, 1, 1], [9e7, 9e7, 9e7]]])
+    a, b = m.funcPlasmaParams(x)["raw"], om.plasma(x)
+    assert np.array_equal(a, b, equal_nan=True)
+    assert np.isfinite(a[:1500, 4:8]).all() and (a[:1500, 4] > 1.0).all()
+    om.close()
+
+
+@pytest.mark.parametrize("mode", ["thread", "team"])
+def test_rays_bitwise(srt, sample_path, mode, monkeypatch):
+    monkeypatch.setenv("SRT_KERNEL", mode)
+    pos0, dir0, w0 = common.launch_grid([1000.0, 3000.0, 9000.0], [20.0, 30.0, 40.0, 50.0], alt_km=3000.0)
+    for use_igrf, fixed in ((0, 0), (1, 0), (0, 1)):
+        m, om = pair(srt, sample_path, use_igrf)
+        prm = dict(common.C2, maxsteps=80, tmax=0.5, fixedstep=fixed)
+        res = srt.raytracer_run(m, pos0, dir0.copy(), w0, outputper=1, **prm)
+        steps = 0
+        for r in range(len(w0)):
+            o = om.trace(pos0[r], [0, 0, 0], w0[r], **prm)
+            g = res[r]
+            assert g.stopcond == o["stopcond"] and g.rows.shape == o["rows"].shape, (mode, use_igrf, fixed, r)
+            assert np.array_equal(g.rows, o["rows"], equal_nan=True), (mode, use_igrf, fixed, r)
+            steps += len(g.rows)
+        assert steps > 400
+        om.close()
+
+
+def test_in_its_own_order_the_product_stays_within_the_references_spread(srt, sample_path):
+    """no order imposed: the oracle in file order and under another insertion order, the GPU in its cell order"""
+    m, om = pair(srt, sample_path)
+    o1 = ol.OracleScattered(sample_path, **OPTS)
+    o2 = ol.OracleScattered(sample_path, perm=np.r_[np.random.default_rng(2).permutation(3000), 3000:3007], **OPTS)
+    x = query_points(500, seed=77)
+    a, b, c = m.funcPlasmaParams(x)["raw"], o1.plasma(x), o2.plasma(x)
+    mine = np.abs(a[:, 4:8] / b[:, 4:8] - 1.0).max()
+    own = np.abs(c[:, 4:8] / b[:, 4:8] - 1.0).max()
+    assert mine < 1e-9 and mine < 1e3 * max(own, 1e-15)
+    assert np.array_equal(a[:, 16:19], b[:, 16:19])
+    for o in (om, o1, o2):
+        o.close()
+
+
+def test_command_line_modelnum_4(srt, sample_path, tmp_path):
+    """the `raytracer` command with the driver's --scattered_interp_* options (driver:617-770): its output file is byte for
+    byte the driver's format applied to the oracle's rows"""
+    from test_gpu_cli import _cli, _oracle_text, _write_rays
+    m, om = pair(srt, sample_path)
+    pos0, dir0, w0 = common.launch_grid([2000.0, 6000.0], [25.0, 40.0], alt_km=3000.0)
+    rays = tmp_path / "rays.txt"
+    _write_rays(rays, pos0, dir0, w0)
+    params = dict(common.C2, maxsteps=40, tmax=0.5)
+    extra = ["--modelnum=4", "--interp_interpfile=%s" % sample_path, "--use_igrf=0", "--device=0",
+             "--scattered_interp_window_scale=%r" % OPTS["window_scale"], "--scattered_interp_order=%d" % OPTS["order"],
+             "--scattered_interp_exact=%d" % OPTS["exact"], "--scattered_interp_local_window_scale=%r" % OPTS["local_window_scale"]]
+    got = _cli(tmp_path, params, extra, rays)
+    want = _oracle_text(om, pos0, w0, params, 1, m.qs, m.ms, m.nus)
+    assert got == want
+    om.close()
