@@ -620,6 +620,24 @@ def measure_ts05(C, with_cpu):
     return out
 
 
+def measure_scattered(C):
+    """SURVEY.md 8(f) row f4, second half: modelnum 4 (scattered samples, moving least squares).  tools/scattered_bench.py in a
+    child process with a time limit, rank 0 only: the model's kernels had not run on a B200 when this was written (no GPU
+    minutes were left), so nothing they do -- fault, hang, wrong bits -- can reach this process or the line's parity gate;
+    its own counters (points_differing, rays_differing) say whether the GPU equals the CPU oracle there."""
+    if C.rank != 0:
+        return None
+    import subprocess
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "scattered_bench.py")], capture_output=True, text=True, timeout=300)
+        lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+        if not lines:
+            return {"error": "no result (exit code %d): %s" % (r.returncode, r.stderr.strip()[-300:])}
+        return json.loads(lines[-1])
+    except Exception as e:  # an extra must not take the line down
+        return {"error": repr(e)}
+
+
 def traffic_from_profiles(name, ki, accepted_per_launch):
     """DRAM bytes per launch of the trace kernel on this workload (dram__bytes_read.sum + dram__bytes_write.sum of a
     committed `ncu --set full` capture, profiles/traffic.json).  The captures run the workload's own launch set with
@@ -645,7 +663,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="c2 is the bench line; the others run as `extra`")
-    ap.add_argument("--extras", default="auto", help="auto (c3, c4_100k, c5, ts05, and c4 at 8 GPUs), none, or a comma list of workloads")
+    ap.add_argument("--extras", default="auto", help="auto (c3, c4_100k, c5, ts05, scattered at 1 GPU, and c4 at 8 GPUs), none, or a comma list of workloads")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -711,6 +729,10 @@ def main():
                 o = {"error": repr(e)}
             if C.rank == 0:
                 extras["ts05"] = o
+        if (args.extras == "auto" and C.world == 1) or "scattered" in names:
+            o = measure_scattered(C)
+            if C.rank == 0:
+                extras["scattered"] = o
     if C.rank == 0:
         m = main_out
         line = {"metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": C.world, "steps": args.steps, "warmup": args.warmup,

@@ -46,6 +46,9 @@ def test_compute_fails_loudly_without_gpu(built):
         m.funcPlasmaParams(pos0)
     with pytest.raises(srt.SrtError):
         srt.interpsetup(os.path.join(common.ROOT, "tests", "golden", "grid13.txt"), 2010001, 0, 1, 0)
+    with pytest.raises(srt.SrtError):  # modelnum 4 places its samples on the devices at set-up
+        srt.scatteredinterpsetup(os.path.join(common.ROOT, "tests", "golden", "grid13.txt"), 1.5, 2, 0, 3.0)
+    assert L.srt_model_scattered_samples(None, None, 0) == -3 and L.srt_model_scattered_info(None, None, None, None, None, None) == -3
 
 
 def test_argument_errors(built):
