@@ -107,6 +107,10 @@ def main(argv=None):
     ap.add_argument("--modelnum", type=int, default=0)
     ap.add_argument("--ngo_configfile", default="")
     ap.add_argument("--interp_interpfile", default="")
+    ap.add_argument("--scattered_interp_window_scale", type=float, default=0.0)  # modelnum 4 (dumpmodel.f95:152-160)
+    ap.add_argument("--scattered_interp_order", type=float, default=0.0)
+    ap.add_argument("--scattered_interp_exact", type=float, default=0.0)
+    ap.add_argument("--scattered_interp_local_window_scale", type=float, default=0.0)
     for k in ("yearday", "milliseconds_day", "use_tsyganenko", "use_igrf"):
         ap.add_argument("--" + k, type=int, default=0)  # unset options are 0 in the reference build (-finit-local-zero)
     TSY = ("Pdyn", "Dst", "ByIMF", "BzIMF", "W1", "W2", "W3", "W4", "W5", "W6")
@@ -121,8 +125,13 @@ def main(argv=None):
         model = srt.ngosetup(a.ngo_configfile, a.yearday, a.milliseconds_day, a.use_igrf, a.use_tsyganenko)
     elif a.modelnum == 3:
         model = srt.interpsetup(a.interp_interpfile, a.yearday, a.milliseconds_day, a.use_igrf, a.use_tsyganenko)
+    elif a.modelnum == 4:
+        import math
+        model = srt.scatteredinterpsetup(a.interp_interpfile, a.scattered_interp_window_scale, math.floor(a.scattered_interp_order),
+                                         math.floor(a.scattered_interp_exact), a.scattered_interp_local_window_scale, 0, a.yearday,
+                                         a.milliseconds_day, a.use_igrf, a.use_tsyganenko)
     else:
-        print("dumpmodel: modelnum %d is not supported (1 = Ngo, 3 = gridded interpolation)" % a.modelnum, file=sys.stderr)
+        print("dumpmodel: modelnum %d is not supported (1 = Ngo, 3 = gridded interpolation, 4 = scattered samples)" % a.modelnum, file=sys.stderr)
         return 2
     if a.use_tsyganenko == 1:
         pm = [getattr(a, "tsyganenko_" + k) for k in TSY]

@@ -247,3 +247,21 @@ def test_file_reader_follows_list_directed_rules(tmp_path):
     out = he.plasma(np.array([[2.15e7, 2e5, 2e5]]))
     assert out[0, 0] == -1.602e-19 and out[0, 1] == 1.602e-19 and out[0, 9] == 1.67e-27 and out[0, 6] == 0.0
     om.close()
+
+
+def test_with_the_ts05_external_field(sample_file):
+    """use_tsyganenko = 1 on modelnum 4 (adapter :352-360): the field block is the other adapters'; T04_s is the reference's
+    own source as translated into oracle/_ref"""
+    from test_ts05_cpu import PARMOD
+    if ol.ts05_ref(True) is None:
+        pytest.skip("oracle/_ref/libts05_ref_srtmath.so not built")
+    path = sample_file[0]
+    for use_igrf in (0, 1):
+        he = common.HostEmuScattered(path, use_igrf=use_igrf, msec=3600000, **OPTS).tsyganenko(PARMOD)
+        om = ol.OracleScattered(path, use_igrf=use_igrf, msec=3600000, **OPTS).impose_order(he.records[:, :3]).tsyganenko(PARMOD)
+        off = common.HostEmuScattered(path, use_igrf=use_igrf, msec=3600000, **OPTS)
+        x = query_points(150, seed=55)
+        a, b, c = he.plasma(x), om.plasma(x), off.plasma(x)
+        assert np.array_equal(a, b)
+        assert np.array_equal(a[:, :16], c[:, :16]) and not np.array_equal(a[:, 16:19], c[:, 16:19])
+        om.close()

@@ -111,3 +111,29 @@ def test_command_line_modelnum_4(srt, sample_path, tmp_path):
     want = _oracle_text(om, pos0, w0, params, 1, m.qs, m.ms, m.nus)
     assert got == want
     om.close()
+
+
+def test_with_the_ts05_external_field(srt, sample_path):
+    """use_tsyganenko = 1 on modelnum 4: evaluation kernel <2,2> / <2,3>, and a few rays through both trace kernels"""
+    from test_ts05_cpu import PARMOD
+    if ol.ts05_ref(True) is None:
+        pytest.skip("oracle/_ref/libts05_ref_srtmath.so not built")
+    o = OPTS
+    for use_igrf in (0, 1):
+        m = srt.scatteredinterpsetup(sample_path, o["window_scale"], o["order"], o["exact"], o["local_window_scale"], yearday=2010001,
+                                     milliseconds_day=3600000, use_igrf=use_igrf, use_tsyganenko=1).tsyganenko(*PARMOD[:4], W=PARMOD[4:])
+        om = ol.OracleScattered(sample_path, use_igrf=use_igrf, msec=3600000, **o).impose_order(srt.scattered_samples(m)[:, :3]).tsyganenko(PARMOD)
+        x = query_points(300, seed=56)
+        assert np.array_equal(m.funcPlasmaParams(x)["raw"], om.plasma(x))
+        pos0, dir0, w0 = common.launch_grid([3000.0], [25.0, 45.0], alt_km=3000.0)
+        prm = dict(common.C2, maxsteps=20, tmax=0.5)
+        for mode in ("thread", "team"):
+            os.environ["SRT_KERNEL"] = mode
+            try:
+                res = srt.raytracer_run(m, pos0, dir0.copy(), w0, outputper=1, **prm)
+            finally:
+                os.environ.pop("SRT_KERNEL", None)
+            for r in range(len(w0)):
+                want = om.trace(pos0[r], [0, 0, 0], w0[r], **prm)
+                assert res[r].stopcond == want["stopcond"] and np.array_equal(res[r].rows, want["rows"], equal_nan=True), (use_igrf, mode, r)
+        om.close()
