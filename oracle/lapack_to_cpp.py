@@ -541,6 +541,27 @@ void lapack_ref_csvd_hook(const double* m_re_im, double* vt_re_im) {
 }
 """
 
+# the three calls of fortran/blas.f95 that lsinterp (fortran/lsinterp_mod.f95:375-395) makes: SolveBlasSymmetric -> dposv 'U' with one
+# right-hand side, MatTransMatMultBlas -> dgemm 'T','N', MatVecMultBlas -> dgemv 'N'.  Column-major arrays, 0-based pointers.
+ENTRY_DPOSV = r"""
+extern "C" {
+int lapack_ref_dposv_upper(int n, double* a, double* b) {
+  int nrhs = 1, info = 0;
+  f_DPOSV(F_tmp<const char*>("U"), n, nrhs, a - 1, n, b - 1, n, info);
+  return info;
+}
+void lapack_ref_dgemm_tn(int m, int n, int k, double* a, double* b, double* c) {
+  double one = 1.0, zero = 0.0;
+  f_DGEMM(F_tmp<const char*>("T"), F_tmp<const char*>("N"), m, n, k, one, a - 1, k, b - 1, k, zero, c - 1, m);
+}
+void lapack_ref_dgemv_n(int m, int n, double* a, double* x, double* y) {
+  double one = 1.0, zero = 0.0;
+  int inc = 1;
+  f_DGEMV(F_tmp<const char*>("N"), m, n, one, a - 1, m, x - 1, inc, zero, y - 1, inc);
+}
+}
+"""
+
 
 def main(dst, srcs, absent):
     ABSENT.update(absent)
@@ -556,7 +577,7 @@ def main(dst, srcs, absent):
     stubs = "\n".join('template <class... A> int f_%s(A&&...) { fprintf(stderr, "lapack_ref: %s is on a branch a 3 x 3 call never takes\\n"); abort(); }' % (n, n)
                       for n in sorted(ABSENT))
     with open(dst, "w") as f:
-        f.write(PRELUDE + "\n" + stubs + "\n\n" + "\n".join(protos) + "\n\n" + "\n".join(texts) + ENTRY)
+        f.write(PRELUDE + "\n" + stubs + "\n\n" + "\n".join(protos) + "\n\n" + "\n".join(texts) + (ENTRY_DPOSV if "--entry=dposv" in sys.argv else ENTRY))
 
 
 if __name__ == "__main__":

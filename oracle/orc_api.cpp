@@ -78,6 +78,17 @@ long orc_scattered_search(void* mv, const double* x, double* recs, long cap) {
   }
   return (long)found.size();
 }
+// the three BLAS / LAPACK calls of lsinterp as restated (column-major): compared with the vendored lapack-3.2.1 itself, translated
+// into oracle/_ref/libdposv_ref.so
+int orc_dposv_upper(int n, double* a, double* b) {
+  std::vector<double> A(a, a + (size_t)n * n), B(b, b + n);
+  const int info = dposv_upper(n, A, B);
+  std::copy(A.begin(), A.end(), a);
+  std::copy(B.begin(), B.end(), b);
+  return info;
+}
+void orc_mat_trans_mat_mult(int m, int n, int k, const double* a, const double* b, double* c) { mat_trans_mat_mult(m, n, k, a, b, c); }
+void orc_mat_vec_mult(int m, int n, const double* a, const double* x, double* y) { mat_vec_mult(m, n, a, x, y); }
 long orc_scattered_impose_order(void* mv, long n, const double* pts) { return ((ScatteredModel*)(Model*)mv)->impose_order(n, pts); }
 int orc_scattered_interpolate(void* mv, const double* x, double* fi) { return ((ScatteredModel*)(Model*)mv)->interpolate(x, fi); }
 // lsinterp on neighbour arrays given in the caller's order: pts[I][3], vals[I][nval]

@@ -12,8 +12,11 @@
 // (adapter :141), so the order in which a query returns its neighbours, which sample is the tree's root (and gets the nearest
 // distance 0 from kdtree_nearest, see `root_quirk`), and which of several coincident samples survives are not defined by
 // the reference's source: no run of the reference reproduces another in the last bits.  This restatement takes the insertion
-// order as an argument.  Pinned: nothing reference-held exists for this model (no fixture, no test, Fortran uncompilable
-// here): parity unpinned beyond the statement-by-statement reading cited above.
+// order as an argument.  PARITY UNPINNED for the kd-tree and lsinterp statements: nothing reference-held exists for this model
+// (no fixture, no test) and its Fortran is outside what oracle/f90_to_cpp.py translates; they rest on the statement-by-statement
+// reading cited above and on a known answer (polynomial reproduction, tests/test_scattered_cpu.py).  PINNED: dposv_upper,
+// mat_trans_mat_mult, mat_vec_mult equal the reference's vendored lapack-3.2.1 as translated into oracle/_ref/libdposv_ref.so
+// (oracle/lapack_to_cpp.py --entry=dposv), bit for bit.
 #pragma once
 #include <algorithm>
 #include <memory>
@@ -180,6 +183,26 @@ inline int dposv_upper(int n, std::vector<double>& A, std::vector<double>& b) {
   return 0;
 }
 
+// MatTransMatMultBlas (blas.f95:96-110): C = A' B by dgemm 'T','N' (BLAS/SRC/dgemm.f: temp = temp + A(l,i)*B(l,j); C(i,j) = alpha*temp).
+// A is k x m, B is k x n, C is m x n, column-major.
+inline void mat_trans_mat_mult(int m, int n, int k, const double* A, const double* B, double* Cm) {
+  for (int j = 0; j < n; ++j)
+    for (int i = 0; i < m; ++i) {
+      double temp = 0.0;
+      for (int l = 0; l < k; ++l) temp = temp + A[(size_t)i * k + l] * B[(size_t)j * k + l];
+      Cm[(size_t)j * m + i] = 1.0 * temp;
+    }
+}
+// MatVecMultBlas (blas.f95:131-139): y = A x by dgemv 'N' (BLAS/SRC/dgemv.f: y = 0; per column with x(j) /= 0: y = y + (alpha*x(j))*A(:,j))
+inline void mat_vec_mult(int m, int n, const double* A, const double* x, double* y) {
+  for (int i = 0; i < m; ++i) y[i] = 0.0;
+  for (int j = 0; j < n; ++j)
+    if (x[j] != 0.0) {
+      const double temp = 1.0 * x[j];
+      for (int i = 0; i < m; ++i) y[i] = y[i] + temp * A[(size_t)j * m + i];
+    }
+}
+
 // lsinterp (lsinterp_mod.f95:255-449) on the neighbour arrays a radius query returned, in the order it returned them:
 // foundpoints [I][3], foundvals [I][nval] (the last value = nearest-neighbour distance).  fi[nval-1]; returns the status.
 inline int lsinterp_found(const double rin[3], const std::vector<const double*>& foundpoints, const std::vector<const double*>& foundvals,
@@ -231,22 +254,11 @@ inline int lsinterp_found(const double rin[3], const std::vector<const double*>&
     if (scaled == 1)
       for (int i = 0; i < I; ++i) col[i] = m_sqrt(k[i]) * col[i];
   }
-  // A = E' E: dgemm 'T','N' (BLAS/SRC/dgemm.f: temp = temp + A(l,i)*B(l,j))
   std::vector<double> A((size_t)J * J, 0.0);
-  for (int j = 0; j < J; ++j)
-    for (int i = 0; i < J; ++i) {
-      double temp = 0.0;
-      for (int l = 0; l < I; ++l) temp = temp + E[(size_t)i * I + l] * E[(size_t)j * I + l];
-      A[(size_t)j * J + i] = 1.0 * temp;
-    }
+  mat_trans_mat_mult(J, J, I, E.data(), E.data(), A.data());
   if (dposv_upper(J, A, c) != 0) return 1;  // (dposv works on tmpA and on b = c; x = b)
-  // tmp = E * aa(1:J): dgemv 'N'
   std::vector<double> tmp(I, 0.0);
-  for (int j = 0; j < J; ++j)
-    if (c[j] != 0.0) {
-      const double temp = 1.0 * c[j];
-      for (int i = 0; i < I; ++i) tmp[i] = tmp[i] + temp * E[(size_t)j * I + i];
-    }
+  mat_vec_mult(I, J, E.data(), c.data(), tmp.data());
   std::vector<double> aa(I);
   for (int i = 0; i < I; ++i) aa[i] = tmp[i] * dinv[i];
   if (scaled == 1)

@@ -265,3 +265,57 @@ def test_with_the_ts05_external_field(sample_file):
         assert np.array_equal(a, b)
         assert np.array_equal(a[:, :16], c[:, :16]) and not np.array_equal(a[:, 16:19], c[:, 16:19])
         om.close()
+
+
+def _dposv_ref():
+    import ctypes as C
+    path = os.path.join(common.ROOT, "oracle", "_ref", "libdposv_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libdposv_ref.so not built (the reference's lapack-3.2.1 is translated where /root/reference exists)")
+    return C.CDLL(path)
+
+
+def test_blas_and_lapack_calls_against_the_vendored_lapack():
+    """lsinterp's three library calls (blas.f95: dposv 'U', dgemm 'T','N', dgemv 'N') as the oracle restates them, against the
+    reference's own vendored lapack-3.2.1, translated statement by statement into oracle/_ref/libdposv_ref.so
+    (oracle/lapack_to_cpp.py): bit for bit, incl. matrices built like lsinterp's (monomials in metres), a matrix that is not
+    positive definite (same INFO, same partial factor) and zeros in the right-hand side (dtrsm / dgemv skip them)."""
+    import ctypes as C
+    R, L = _dposv_ref(), ol.lib()
+    vp, i = C.c_void_p, C.c_int
+    for lib_, names in ((R, ("lapack_ref_dposv_upper", "lapack_ref_dgemm_tn", "lapack_ref_dgemv_n")), (L, ("orc_dposv_upper", "orc_mat_trans_mat_mult", "orc_mat_vec_mult"))):
+        getattr(lib_, names[0]).argtypes = [i, vp, vp]
+        getattr(lib_, names[0]).restype = i
+        getattr(lib_, names[1]).argtypes = [i, i, i, vp, vp, vp]
+        getattr(lib_, names[2]).argtypes = [i, i, vp, vp, vp]
+    rng = np.random.default_rng(8)
+    p = lambda a: a.ctypes.data_as(vp)
+    cases = 0
+    for J in (1, 4, 10, 20):
+        for trial in range(12):
+            I = J + int(rng.integers(0, 60))
+            scale = 10.0 ** rng.uniform(0, 6)
+            E = np.asfortranarray(rng.normal(size=(I, J)) * scale ** rng.integers(0, 3, size=J)[None, :])
+            if trial == 0:
+                E[:, -1] = E[:, 0]  # singular: not positive definite (or barely), INFO > 0 on both sides or the same factor
+            A1, A2 = np.zeros((J, J), order="F"), np.zeros((J, J), order="F")
+            R.lapack_ref_dgemm_tn(J, J, I, p(E), p(E), p(A1))
+            L.orc_mat_trans_mat_mult(J, J, I, p(E), p(E), p(A2))
+            assert np.array_equal(A1, A2)
+            b1 = np.zeros(J); b1[0] = 1.0
+            if trial % 3 == 2:
+                b1 = rng.normal(size=J) * (rng.random(J) > 0.3)
+            b2 = b1.copy()
+            F1, F2 = A1.copy(order="F"), A2.copy(order="F")
+            i1, i2 = R.lapack_ref_dposv_upper(J, p(F1), p(b1)), L.orc_dposv_upper(J, p(F2), p(b2))
+            assert i1 == i2
+            assert np.array_equal(np.triu(F1), np.triu(F2), equal_nan=True)
+            if i1 == 0:
+                assert np.array_equal(b1, b2, equal_nan=True)
+            x = rng.normal(size=J) * (rng.random(J) > 0.2)
+            y1, y2 = np.full(I, 7.0), np.full(I, 7.0)
+            R.lapack_ref_dgemv_n(I, J, p(E), p(x), p(y1))
+            L.orc_mat_vec_mult(I, J, p(E), p(x), p(y2))
+            assert np.array_equal(y1, y2)
+            cases += 1
+    assert cases == 48
