@@ -319,3 +319,41 @@ def test_blas_and_lapack_calls_against_the_vendored_lapack():
             assert np.array_equal(y1, y2)
             cases += 1
     assert cases == 48
+
+
+def test_second_statement_in_numpy(sample_file, models):
+    """lsinterp said a second time, from the MATLAB lines its author left in the Fortran as comments (lsinterp_mod.f95:199-201:
+    `etainv = @(r) ((1+eps)./(exp(r.^2./h.^2)-1+eps)).*(.5+.5*cos(r*2*pi/s/2)).*(r<s)`; :388 `a = (Dinv)*E*(A\\c)`) and from
+    Levin's definition: the interpolant at x is the value at x of the polynomial of degree <= order that minimises
+    sum_i w_i (p(x_i) - f_i)^2 with w_i = 0.5 etainv(r_i).  Solved here by a weighted least-squares fit in coordinates scaled
+    by the radius (QR, not the normal equations), on brute-force neighbour sets: agreement to 1e-7 in the log-density."""
+    path = sample_file[0]
+    he = models[0]
+    rec, eps, worst = he.records, 5.0e-16, 0.0
+    for exact in (0, 1):
+        om = ol.OracleScattered(path, **dict(OPTS, exact=exact))
+        for x in query_points(40, seed=90 + exact):
+            d = rec[:, :3] - x
+            r = np.sqrt((d * d).sum(1))
+            nb = r < he.radius
+            d, r, vals, near = d[nb], r[nb], rec[nb, 3:7], rec[nb, 7]
+            cw = 0.5 + 0.5 * np.cos(r * 2 * np.pi / he.radius / 2)
+            h = OPTS["local_window_scale"] * (cw * near).sum() / cw.sum()
+            if exact:
+                eta = ((1 + eps) / (np.exp(r ** 2 / h ** 2) - 1 + eps)) * cw
+            else:
+                eta = np.exp(-((r + he.radius * eps) / (h / 4)) ** 1.1) * cw
+            keep = eta > 1e-16
+            if keep.sum() < 10:
+                keep[:] = True
+            s = d[keep] / he.radius
+            V = np.stack([s[:, 0] ** a * s[:, 1] ** b * s[:, 2] ** c for a in range(3) for b in range(3 - a) for c in range(3 - a - b)], axis=1)
+            sw = np.sqrt(0.5 * eta[keep])
+            coef = np.linalg.lstsq(V * sw[:, None], vals[keep] * sw[:, None], rcond=None)[0]
+            want = coef[0]  # the polynomial's value at the query point: every monomial but the constant vanishes there
+            st, fi = om.interpolate(x)
+            assert st == 0
+            worst = max(worst, np.abs(fi - want).max())
+        om.close()
+    print("lsinterp against the numpy second statement: largest difference of a log-density %.3g" % worst)
+    assert worst < 1e-7
