@@ -137,3 +137,28 @@ def test_with_the_ts05_external_field(srt, sample_path):
                 want = om.trace(pos0[r], [0, 0, 0], w0[r], **prm)
                 assert res[r].stopcond == want["stopcond"] and np.array_equal(res[r].rows, want["rows"], equal_nan=True), (use_igrf, mode, r)
         om.close()
+
+
+def test_degenerate_geometry_bitwise(srt, tmp_path):
+    """samples on a plane (singular normal equations: dposv INFO > 0 -> density 1), queries on samples (r = 0, exact window),
+    neighbourhoods cut below J by the weight threshold: the statuses 0, 1, 2 of lsinterp all occur (tests/test_scattered_cpu.py
+    ::test_degenerate_geometry_bitwise is the host side)"""
+    rng = np.random.default_rng(4)
+    n, base, span = 600, np.array([2.5, 0.3, 0.2]) * common.R_E, 0.4 * common.R_E
+    pos = base + np.c_[rng.random(n) - 0.5, rng.random(n) - 0.5, np.zeros(n)] * span
+    f = np.sin(pos[:, 0] / span) + 0.3 * np.cos(pos[:, 1] / span) + 20.0
+    path = str(tmp_path / "plane.txt")
+    with open(path, "w") as fh:
+        fh.write("2 0 0 0 0 0 0\n-1.602e-19 1.602e-19\n9.10938188e-31 1.6726e-27\n")
+        for p, v in zip(pos, f):
+            fh.write("%.17e %.17e %.17e %.17e %.17e\n" % (p[0], p[1], p[2], v, v - 1.0))
+    q = np.vstack([base + (rng.random((200, 3)) - 0.5) * span, pos[:20], pos[:10] + 1e-3])
+    ones = 0
+    for order, exact, lws in ((1, 0, 3.0), (2, 1, 3.0), (3, 0, 0.05), (2, 1, 0.02)):
+        m, om = pair(srt, path, 0, window_scale=3.0, order=order, exact=exact, local_window_scale=lws)
+        assert m.nspec == 2
+        a, b = m.funcPlasmaParams(q)["raw"], om.plasma(q)
+        assert np.array_equal(a, b, equal_nan=True), (order, exact, lws)
+        ones += int((a[:, 4] == 1.0).sum())
+        om.close()
+    assert ones > 0  # failed interpolations (exp(0)) were among them
