@@ -629,7 +629,7 @@ def measure_scattered(C):
         return None
     import subprocess
     try:
-        r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "scattered_bench.py")], capture_output=True, text=True, timeout=300)
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "scattered_bench.py")], capture_output=True, text=True, timeout=180)
         lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
         if not lines:
             return {"error": "no result (exit code %d): %s" % (r.returncode, r.stderr.strip()[-300:])}
