@@ -399,3 +399,109 @@ def test_degenerate_geometry_bitwise(tmp_path):
             om.close()
     print(sorted(seen))
     assert {s for _, s in seen} >= {0, 1}  # both the solved and the failed factorisation occur
+
+
+class ReferenceLsinterp:
+    """`lsinterp` of fortran/lsinterp_mod.f95 EXECUTED from the reference's own source text by oracle/f90_interp.py (with
+    tabular_monomials, etainv, coswindow of the same file and SolveBlasSymmetric / MatTransMatMultBlas / MatVecMultBlas of
+    fortran/blas.f95, interpreted too); dposv / dgemm / dgemv underneath are the reference's vendored lapack-3.2.1 as translated
+    into oracle/_ref/libdposv_ref.so; kdtree_search is a hook that returns the neighbour arrays the test supplies."""
+
+    def __init__(self):
+        import ctypes as C
+        import re
+        import sys
+        ref = "/root/reference/fortran"
+        if not os.path.exists(ref + "/lsinterp_mod.f95"):
+            pytest.skip("the reference's sources are not present on this machine")
+        sys.path.insert(0, os.path.join(common.ROOT, "oracle"))
+        import f90_interp as F
+        R = _dposv_ref()
+        vp, i = C.c_void_p, C.c_int
+        R.lapack_ref_dposv_upper.argtypes, R.lapack_ref_dposv_upper.restype = [i, vp, vp], i
+        R.lapack_ref_dgemm_tn.argtypes = [i, i, i, vp, vp, vp]
+        R.lapack_ref_dgemv_n.argtypes = [i, i, vp, vp, vp]
+        units = dict(F.parse_units(ref + "/lsinterp_mod.f95"))
+        blas = F.parse_units(ref + "/blas.f95")
+        for k in ("solveblassymmetric", "mattransmatmultblas", "matvecmultblas"):
+            units[k] = blas[k]
+        txt = open(ref + "/constants.f95").read().lower()
+        consts = {"pi": float(re.search(r"\bpi\s*=\s*([0-9.]+)_dp", txt).group(1)), "r_e": float(re.search(r"\br_e\s*=\s*([0-9.e+-]+)_dp", txt).group(1))}
+        self.found = None
+
+        def ptr(a):
+            assert isinstance(a, np.ndarray) and a.dtype == np.float64 and a.flags.f_contiguous
+            return a.ctypes.data
+
+        def dposv(v):
+            uplo, n, nrhs, a, lda, b, ldb, info = v
+            assert uplo == "u" and nrhs == 1 and lda == n and ldb == n
+            return [None] * 7 + [int(R.lapack_ref_dposv_upper(n, ptr(a), ptr(b)))]
+
+        def dgemm(v):
+            ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc = v
+            assert (ta, tb) == ("t", "n") and alpha == 1.0 and beta == 0.0 and lda == k and ldb == k and ldc == m
+            R.lapack_ref_dgemm_tn(m, n, k, ptr(a), ptr(b), ptr(c))
+            return [None] * 13
+
+        def dgemv(v):
+            t, m, n, alpha, a, lda, x, incx, beta, y, incy = v
+            assert t == "n" and alpha == 1.0 and beta == 0.0 and lda == m and incx == 1 and incy == 1
+            R.lapack_ref_dgemv_n(m, n, ptr(a), ptr(x), ptr(y))
+            return [None] * 11
+
+        self.I = F.Interp(units, consts, {"kdtree_search": lambda v: [None, None, None, self.found[0], self.found[1]],
+                                          "dposv": dposv, "dgemm": dgemm, "dgemv": dgemv})
+
+    def __call__(self, x, pts, vals, radius, order, exact, scaled, local_window_scale):
+        self.found = (np.asfortranarray(pts, dtype=np.float64), np.asfortranarray(vals, dtype=np.float64))
+        fi = np.full(vals.shape[1] - 1, np.nan)
+        _, fin = self.I.call("lsinterp", [np.array(x, dtype=np.float64), 0, float(radius), int(order), int(exact), int(scaled),
+                                          float(local_window_scale), fi, 0])
+        return int(fin[8]), np.asarray(fin[7])
+
+
+def test_lsinterp_against_the_references_own_source_text(sample_file, tmp_path):
+    """The pin of the moving-least-squares arithmetic: the oracle's restatement (built on glibc's libm, as a gfortran binary
+    here would be) == the reference's lsinterp_mod.f95 + blas.f95 executed statement by statement + its vendored LAPACK, bit
+    for bit, statuses included; every (order, exact, scaled), neighbourhoods of 10 to > 100 samples, and the degenerate plane
+    (singular normal equations -> status 1; too few neighbours -> status 2)."""
+    ref = ReferenceLsinterp()
+    path = sample_file[0]
+    checked, statuses = 0, set()
+    for order, exact, scaled in ((0, 0, 0), (1, 1, 0), (2, 0, 0), (2, 1, 0), (3, 0, 0), (3, 1, 1), (2, 0, 1)):
+        kw = dict(window_scale=1.8, order=order, exact=exact, local_window_scale=2.5, scaled=scaled)
+        he = common.HostEmuScattered(path, **kw)
+        om = ol.OracleScattered(path, libm=True, **kw)
+        for x in query_points(12, seed=100 + 10 * order + exact):
+            a = he.records[he.neighbours(x)]
+            st_r, fi_r = ref(x, a[:, :3], a[:, 3:8], he.radius, order, exact, scaled, 2.5)
+            st_o, fi_o = om.lsinterp_found(x, a[:, :3], a[:, 3:8])
+            assert st_r == st_o and np.array_equal(fi_r, fi_o[:4]), (order, exact, scaled, st_r, st_o, fi_r, fi_o)
+            checked += 1
+            statuses.add(st_r)
+        om.close()
+    rng = np.random.default_rng(4)
+    n, base, span = 600, np.array([2.5, 0.3, 0.2]) * R_E, 0.4 * R_E
+    pos = base + np.c_[rng.random(n) - 0.5, rng.random(n) - 0.5, np.zeros(n)] * span
+    f = np.sin(pos[:, 0] / span) + 0.3 * np.cos(pos[:, 1] / span) + 20.0
+    plane = str(tmp_path / "plane.txt")
+    with open(plane, "w") as fh:
+        fh.write("2 0 0 0 0 0 0\n-1.602e-19 1.602e-19\n9.10938188e-31 1.6726e-27\n")
+        for p, v in zip(pos, f):
+            fh.write("%.17e %.17e %.17e %.17e %.17e\n" % (p[0], p[1], p[2], v, v - 1.0))
+    for order, exact, lws in ((1, 0, 3.0), (2, 1, 3.0), (3, 0, 0.05)):
+        kw = dict(window_scale=3.0, order=order, exact=exact, local_window_scale=lws)
+        he = common.HostEmuScattered(plane, **kw)
+        om = ol.OracleScattered(plane, libm=True, **kw)
+        for x in np.vstack([base + (rng.random((8, 3)) - 0.5) * span, pos[:2], base + [0, 0, 5 * span]]):
+            a = he.records[he.neighbours(x)]
+            vals = np.c_[a[:, 3:5], a[:, 7]].reshape(-1, 3)
+            st_r, fi_r = ref(x, a[:, :3].reshape(-1, 3), vals, he.radius, order, exact, 0, lws)
+            st_o, fi_o = om.lsinterp_found(x, a[:, :3].reshape(-1, 3), vals)
+            assert st_r == st_o and np.array_equal(fi_r, fi_o[:2], equal_nan=True), (order, exact, lws, st_r, st_o, fi_r, fi_o)
+            checked += 1
+            statuses.add(st_r)
+        om.close()
+    print("lsinterp: %d queries equal to the executed reference text; statuses met: %s" % (checked, sorted(statuses)))
+    assert statuses == {0, 1, 2} and checked == 117
