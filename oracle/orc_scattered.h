@@ -12,11 +12,12 @@
 // (adapter :141), so the order in which a query returns its neighbours, which sample is the tree's root (and gets the nearest
 // distance 0 from kdtree_nearest, see `root_quirk`), and which of several coincident samples survives are not defined by
 // the reference's source: no run of the reference reproduces another in the last bits.  This restatement takes the insertion
-// order as an argument.  PARITY UNPINNED for the kd-tree and lsinterp statements: nothing reference-held exists for this model
-// (no fixture, no test) and its Fortran is outside what oracle/f90_to_cpp.py translates; they rest on the statement-by-statement
-// reading cited above and on a known answer (polynomial reproduction, tests/test_scattered_cpu.py).  PINNED: dposv_upper,
-// mat_trans_mat_mult, mat_vec_mult equal the reference's vendored lapack-3.2.1 as translated into oracle/_ref/libdposv_ref.so
-// (oracle/lapack_to_cpp.py --entry=dposv), bit for bit.
+// order as an argument.  PINNED: lsinterp_found (with tabular_monomials3, etainv, coswindow, pow_int) equals the reference's
+// own lsinterp_mod.f95 + blas.f95 executed statement by statement by oracle/f90_interp.py over the vendored lapack-3.2.1
+// (translated into oracle/_ref/libdposv_ref.so), bit for bit, statuses included (tests/test_scattered_cpu.py); dposv_upper,
+// mat_trans_mat_mult, mat_vec_mult equal that LAPACK directly.  PARITY UNPINNED: the kd-tree routines and `setup` (derived types
+// with recursive pointers: outside the interpreter and the translators); they rest on the statement-by-statement reading cited
+// above and on brute-force checks of what they compute (neighbour sets, nearest distances).
 #pragma once
 #include <algorithm>
 #include <memory>
