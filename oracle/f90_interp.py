@@ -16,7 +16,9 @@ What the interpreter fixes where a compiler has a choice (the same choices as or
     EXP, COS, SQRT are the C library's (glibc here, as for a gfortran binary on this machine): compare with the oracle built
     -DORC_LIBM;
   * a literal is the nearest double to its decimal text.
-Procedures that are not in the interpreted files (kdtree_search; the BLAS wrappers of blas.f95) are hooks the caller supplies.
+Derived types are objects with named components, pointers are references (NULL: None), `=>` binds a name to its target.
+Procedures that are not in the interpreted files (LAPACK / BLAS; kdtree_search when only lsinterp_mod.f95 is loaded) are hooks the
+caller supplies.
 """
 import math
 import re
@@ -24,11 +26,20 @@ import re
 import numpy as np
 
 TOKEN = re.compile(r"\s*(?:('[^']*'|\"[^\"]*\")|(\d+\.?\d*(?:[ed][+-]?\d+)?(?:_[a-z0-9]+)?|\.\d+(?:[ed][+-]?\d+)?(?:_[a-z0-9]+)?)|(\.(?:and|or|not|true|false|eq|ne|lt|le|gt|ge)\.)"
-                   r"|(\(/|/\)|\*\*|==|/=|<=|>=|[-+*/(),:<>=%])|([a-z][a-z0-9_]*))")
+                   r"|(\(/|/\)|\*\*|=>|==|/=|<=|>=|[-+*/(),:<>=%])|([a-z][a-z0-9_]*))")
 DOTOPS = {".eq.": "==", ".ne.": "/=", ".lt.": "<", ".le.": "<=", ".gt.": ">", ".ge.": ">="}
 
 
+_TOKENS = {}
+
+
 def tokenize(s):
+    if s not in _TOKENS:
+        _TOKENS[s] = _tokenize(s)
+    return list(_TOKENS[s])
+
+
+def _tokenize(s):
     out, i = [], 0
     s = s.strip()
     while i < len(s):
@@ -196,6 +207,13 @@ def _divide(a, b):
     return a / b if isinstance(a, np.ndarray) or isinstance(b, np.ndarray) else float(a) / float(b)
 
 
+class Obj:
+    """an object of a derived type: components by name (None: unallocated / disassociated)"""
+
+    def __init__(self):
+        self.attrs = {}
+
+
 class Stop(Exception):
     pass
 
@@ -336,11 +354,30 @@ class Interp:
         m = re.match(r"^allocate\s*\((.*)\)$", s)
         if m:
             for item in split_top(m.group(1)):
-                mm = re.match(r"\s*([a-z][a-z0-9_]*)\s*\((.*)\)\s*$", item)
-                shape = tuple(int(self.eval(t, env, u)) for t in split_top(mm.group(2)))
-                kind = DTYPES.get(u.types.get(mm.group(1), "real"), np.float64)
-                # (allocated storage is undefined: NaN for reals, so that a use before a definition shows)
-                env[mm.group(1)] = np.full(shape, np.nan, order="F") if kind is np.float64 else np.zeros(shape, dtype=kind, order="F")
+                mm = re.match(r"\s*([a-z][a-z0-9_]*)\s*(?:%\s*([a-z][a-z0-9_]*))?\s*(?:\((.*)\))?\s*$", item)
+                name, comp, dims = mm.groups()
+                if dims is None:  # a pointer to an object of a derived type
+                    new = Obj()
+                else:
+                    shape = tuple(int(self.eval(t, env, u)) for t in split_top(dims))
+                    kind = DTYPES.get(u.types.get(name, "real"), np.float64) if comp is None else np.float64
+                    # (allocated storage is undefined: NaN for reals, so that a use before a definition shows)
+                    new = np.full(shape, np.nan, order="F") if kind is np.float64 else np.zeros(shape, dtype=kind, order="F")
+                if comp is None:
+                    env[name] = new
+                else:
+                    env[name].attrs[comp] = new
+            return
+        m = re.match(r"^nullify\s*\(\s*([a-z][a-z0-9_]*)\s*(?:%\s*([a-z][a-z0-9_]*))?\s*\)$", s)
+        if m:
+            if m.group(2):
+                env[m.group(1)].attrs[m.group(2)] = None
+            else:
+                env.pop(m.group(1), None)
+            return
+        m = re.match(r"^call\s+move_alloc\s*\(\s*([a-z][a-z0-9_]*)\s*,\s*([a-z][a-z0-9_]*)\s*\)$", s)
+        if m:
+            env[m.group(2)] = env.pop(m.group(1))
             return
         m = re.match(r"^deallocate\s*\((.*)\)$", s)
         if m:
@@ -358,6 +395,9 @@ class Interp:
                 depth += 1
             elif t == ("op", ")") or t == ("op", "/)"):
                 depth -= 1
+            elif t == ("op", "=>") and depth == 0:  # pointer assignment: the name refers to the target itself
+                env[toks[0][1]] = _Parser(self, toks[i + 1:], env, u).expression()
+                return
             elif t == ("op", "=") and depth == 0:
                 eq = i
                 break
@@ -369,6 +409,15 @@ class Interp:
     def assign(self, lhs, value, env, u):
         name = lhs[0][1]
         kind = u.types.get(name)
+        if len(lhs) >= 3 and lhs[1] == ("op", "%"):
+            obj, comp = env[name], lhs[2][1]
+            if len(lhs) > 3:
+                obj.attrs[comp][_Parser(self, lhs[4:-1], env, u).subscripts()] = value
+            elif isinstance(obj.attrs.get(comp), np.ndarray) and (not isinstance(value, np.ndarray) or value.shape == obj.attrs[comp].shape):
+                obj.attrs[comp][...] = value
+            else:
+                obj.attrs[comp] = np.array(value, order="F") if isinstance(value, np.ndarray) else value
+            return
         if len(lhs) == 1:
             cur = env.get(name)
             if isinstance(cur, np.ndarray) and (not isinstance(value, np.ndarray) or value.shape == cur.shape):
@@ -402,8 +451,12 @@ class Interp:
             result, finals = (out, [None] * len(values)) if want_value else (None, out)
         else:
             raise NotImplementedError("procedure %s" % name)
-        for p, old, new in zip(plain, values, finals):
-            if p is None or new is None:
+        for t, p, old, new in zip(argtexts, plain, values, finals):
+            mc = re.fullmatch(r"\s*([a-z][a-z0-9_]*)\s*%\s*([a-z][a-z0-9_]*)\s*", t)
+            if mc and new is not None and new is not old:
+                env[mc.group(1)].attrs[mc.group(2)] = new  # e.g. a child pointer the callee allocated
+                continue
+            if p is None or new is None or (p in self.consts and p not in env):
                 continue
             if isinstance(old, np.ndarray) and isinstance(new, np.ndarray) and new.base is old:
                 continue  # the callee worked on a view of the caller's array
@@ -509,12 +562,17 @@ class _Parser:
         """the tokens of a subscript list (without the outer parentheses) -> numpy index, 1-based -> 0-based"""
         idx = []
         while self.p < len(self.t):
-            if self.peek() == ("op", ":"):
+            lo = None
+            if self.peek() != ("op", ":"):
+                lo = self.expression()
+            if self.peek() == ("op", ":"):  # a section lo:hi, either bound optional
                 self.take()
-                idx.append(slice(None))
+                hi = None
+                if self.peek()[0] is not None and self.peek() != ("op", ","):
+                    hi = self.expression()
+                idx.append(slice(None if lo is None else int(lo) - 1, None if hi is None else int(hi)))
             else:
-                v = self.expression()
-                idx.append(np.asarray(v) - 1 if isinstance(v, np.ndarray) else int(v) - 1)
+                idx.append(np.asarray(lo) - 1 if isinstance(lo, np.ndarray) else int(lo) - 1)
             if self.peek() == ("op", ","):
                 self.take()
             else:
@@ -561,6 +619,16 @@ class _Parser:
             return self.constructor()
         if k != "name":
             raise ValueError("unexpected %r in %r" % ((k, v), self.t))
+        if self.peek() == ("op", "%"):  # components of an object of a derived type
+            obj = self.env.get(v)
+            while self.peek() == ("op", "%"):
+                self.take()
+                comp = self.take()[1]
+                obj = obj.attrs.get(comp) if obj is not None else None
+            if self.peek() == ("op", "(") and isinstance(obj, np.ndarray):
+                self.take("(")
+                return self.index(obj)
+            return obj
         if self.peek() != ("op", "("):
             if v in self.env:
                 return self.env[v]
@@ -569,14 +637,25 @@ class _Parser:
             raise NameError("%s is used before it is defined (in %s)" % (v, self.u.name))
         self.take("(")
         if isinstance(self.env.get(v), np.ndarray):
-            args = self.arg_texts()
-            flat = []
-            for i, a in enumerate(args):
-                flat += a + ([("op", ",")] if i + 1 < len(args) else [])
-            got = self.env[v][self.sub(flat).subscripts()]
-            return got.item() if isinstance(got, np.ndarray) and got.ndim == 0 else (got.item() if isinstance(got, np.generic) else got)
+            return self.index(self.env[v])
         args = self.arg_texts()
         return self.function(v, args)
+
+    def index(self, arr):
+        """after '(' of a subscript list on `arr`"""
+        args = self.arg_texts()
+        flat = []
+        for i, a in enumerate(args):
+            flat += list(a) + ([("op", ",")] if i + 1 < len(args) else [])
+        got = arr[self.sub(flat).subscripts()]
+        return got.item() if isinstance(got, np.generic) or (isinstance(got, np.ndarray) and got.ndim == 0) else got
+
+    def designator(self):
+        """value of a variable that may be unallocated / disassociated / undefined: None then"""
+        try:
+            return self.expression()
+        except NameError:
+            return None
 
     def constructor(self):
         items = []
@@ -609,7 +688,9 @@ class _Parser:
     def function(self, name, args):
         ev = lambda a: self.sub(a).expression()
         if name == "allocated":
-            return isinstance(self.env.get(args[0][0][1]), np.ndarray)
+            return isinstance(self.sub(args[0]).designator(), np.ndarray)
+        if name == "associated":
+            return self.sub(args[0]).designator() is not None
         if name == "size":
             a = ev(args[0])
             return int(a.size) if len(args) == 1 else int(a.shape[int(ev(args[1])) - 1])

@@ -15,9 +15,10 @@
 // order as an argument.  PINNED: lsinterp_found (with tabular_monomials3, etainv, coswindow, pow_int) equals the reference's
 // own lsinterp_mod.f95 + blas.f95 executed statement by statement by oracle/f90_interp.py over the vendored lapack-3.2.1
 // (translated into oracle/_ref/libdposv_ref.so), bit for bit, statuses included (tests/test_scattered_cpu.py); dposv_upper,
-// mat_trans_mat_mult, mat_vec_mult equal that LAPACK directly.  PARITY UNPINNED: the kd-tree routines and `setup` (derived types
-// with recursive pointers: outside the interpreter and the translators); they rest on the statement-by-statement reading cited
-// above and on brute-force checks of what they compute (neighbour sets, nearest distances).
+// mat_trans_mat_mult, mat_vec_mult equal that LAPACK directly; the kd-tree (kdtree_add, kdtree_nearest, kdtree_find_ptr,
+// kdtree_search_core) and the insert / nearest-distance steps of setup equal the reference's kdtree_mod.f95 executed by the same
+// interpreter: same kept samples, same stored distances, same neighbours in the same order, the root quirk included.
+// UNPINNED: the READ loop of setup and the glue of funcPlasmaParams around lsinterp.
 #pragma once
 #include <algorithm>
 #include <memory>

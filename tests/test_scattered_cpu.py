@@ -505,3 +505,66 @@ def test_lsinterp_against_the_references_own_source_text(sample_file, tmp_path):
         om.close()
     print("lsinterp: %d queries equal to the executed reference text; statuses met: %s" % (checked, sorted(statuses)))
     assert statuses == {0, 1, 2} and checked == 117
+
+
+def test_kdtree_and_setup_against_the_references_own_source_text(tmp_path):
+    """The pin of the oracle's kd-tree: fortran/kdtree_mod.f95 (kdtree_add, kdtree_nearest, kdtree_find_ptr, kdtree_search and
+    its core) EXECUTED from the reference's text by oracle/f90_interp.py (derived type, pointers, recursion, move_alloc), driven
+    through the steps of the adapter's setup (scattered_interp_dens_model_adapter.f95:141-191: insert unless the nearest sample
+    already in the tree is at distance 0; then every sample's nearest other sample, written into the tree through the pointer
+    kdtree_find_ptr returns).  Same insertion order on both sides: the oracle's tree returns the same neighbours IN THE SAME
+    ORDER with the same stored distances, keeps and drops the same samples, finds the same maxnearest -- and the root sample's
+    distance is 0 in the reference's own text (the quirk the oracle restates and the product does not copy)."""
+    import sys
+    ref = "/root/reference/fortran/kdtree_mod.f95"
+    if not os.path.exists(ref):
+        pytest.skip("the reference's sources are not present on this machine")
+    sys.path.insert(0, os.path.join(common.ROOT, "oracle"))
+    sys.setrecursionlimit(max(sys.getrecursionlimit(), 20000))
+    import f90_interp as F
+    I = F.Interp(F.parse_units(ref), {}, {})
+    path = str(tmp_path / "small.txt")
+    pos, logn = common.write_scattered_file(path, 250, seed=12, duplicates=3, inside=2)
+    nspec, n = 4, len(pos)
+    perm = np.random.default_rng(6).permutation(n)
+    tree, kept, dropped = None, 0, 0
+    for i in perm:  # adapter :141-158
+        p = pos[i].copy()
+        _, fin = I.call("kdtree_nearest", [tree, p, 0, None, None])
+        best = fin[3]
+        if best is None or float(np.dot(best - p, best - p)) > 0.0:
+            _, fin = I.call("kdtree_add", [tree, p, np.r_[logn[i], 1.0], 0])
+            tree = fin[0]
+            kept += 1
+        else:
+            dropped += 1
+    maxnearest = 0.0
+    for i in range(n):  # adapter :160-191
+        p = pos[i].copy()
+        if (p[0] * p[0] + p[1] * p[1]) + p[2] * p[2] >= R_E * R_E:
+            _, fin = I.call("kdtree_nearest", [tree, p, 1, None, None])
+            best = fin[3]
+            _, fin = I.call("kdtree_find_ptr", [tree, p, None, None])
+            valptr = fin[3]
+            assert valptr is not None
+            d = best - p
+            dist = float(np.sqrt((d[0] * d[0] + d[1] * d[1]) + d[2] * d[2]))
+            valptr[-1] = dist
+            maxnearest = max(maxnearest, dist)
+    om = ol.OracleScattered(path, perm=perm, root_quirk=True, **OPTS)
+    assert (om.nkept, om.nduplicates) == (kept, dropped) == (250, 3)
+    assert om.maxnearest == maxnearest
+    assert tree.attrs["val"][-1] == 0.0 == om.root_nearest  # kdtree_nearest starts from best = root
+    radius = om.radius
+    total = 0
+    for x in query_points(40, seed=5, rmin=1.1, rmax=4.8):
+        _, fin = I.call("kdtree_search", [tree, np.array(x), float(radius), None, None])
+        fp, fv = fin[3], fin[4]
+        mine = om.search(x, nspec)
+        if fp is None or len(fp) == 0:
+            assert len(mine) == 0
+            continue
+        assert np.array_equal(np.c_[fp, fv], mine)  # same samples, same order, same values and stored distances
+        total += len(fp)
+    assert total > 300
+    om.close()
