@@ -18,7 +18,8 @@
 // mat_trans_mat_mult, mat_vec_mult equal that LAPACK directly; the kd-tree (kdtree_add, kdtree_nearest, kdtree_find_ptr,
 // kdtree_search_core) and the insert / nearest-distance steps of setup equal the reference's kdtree_mod.f95 executed by the same
 // interpreter: same kept samples, same stored distances, same neighbours in the same order, the root quirk included.
-// UNPINNED: the READ loop of setup and the glue of funcPlasmaParams around lsinterp.
+// The density part of funcPlasmaParams, executed as a whole from the reference's text on that tree, equals plasma() here.
+// UNPINNED: the READ loop of setup.
 #pragma once
 #include <algorithm>
 #include <memory>

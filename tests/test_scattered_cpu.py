@@ -568,3 +568,33 @@ def test_kdtree_and_setup_against_the_references_own_source_text(tmp_path):
         total += len(fp)
     assert total > 300
     om.close()
+    # ---- and the whole of funcPlasmaParams' density (adapter :214-262) from the reference's text: the adapter's statements,
+    # lsinterp, kdtree_search on the tree built above, the BLAS wrappers, the vendored LAPACK.  Field routines are stubbed
+    # (that block is the other adapters', pinned through the translated sources).
+    ref = ReferenceLsinterp()
+    adapter = F.parse_units("/root/reference/fortran/scattered_interp_dens_model_adapter.f95")
+    extra = dict(F.parse_units("/root/reference/fortran/kdtree_mod.f95"))
+    extra["funcplasmaparams"] = adapter["funcplasmaparams"]
+    ref.I.units.update(extra)
+    ref.I.trees.update({k: ref.I._structure(u.body) for k, u in extra.items()})
+    state = F.Obj()
+    state.attrs.update(dict(nspec=nspec, tree=tree, maxnearest=maxnearest, window_scale=OPTS["window_scale"], order=OPTS["order"], exact=OPTS["exact"],
+                            scaled=0, local_window_scale=OPTS["local_window_scale"], qs=np.array([-1.0, 1.0, 1.0, 1.0]), ms=np.array([1.0, 2.0, 3.0, 4.0]),
+                            itime=np.array([2010001, 0]), use_igrf=0, use_tsyganenko=0, pdyn=0.0, dst=0.0, byimf=0.0, bzimf=0.0,
+                            w1=0.0, w2=0.0, w3=0.0, w4=0.0, w5=0.0, w6=0.0))
+    datap = F.Obj()
+    datap.attrs["p"] = state
+    ref.I.hooks.update({"transfer": lambda v: datap, "sm_to_gsm_d": lambda v: [None, None, np.array(v[1])], "gsm_to_sm_d": lambda v: [None, None, np.array(v[1])],
+                        "tsy_recalc": lambda v: [None] * 5, "bmodel_cartesian": lambda v: np.zeros(3)})
+    om = ol.OracleScattered(path, perm=perm, root_quirk=True, libm=True, **OPTS)
+    xs = np.vstack([query_points(30, seed=9, rmin=1.1, rmax=4.8), [[0.3 * R_E, 0.2 * R_E, 0.0]], [[30 * R_E, 0.0, 0.0]]])
+    want = om.plasma(xs)[:, 4:8]
+    interpolated = 0
+    for x, w in zip(xs, want):
+        ns = np.full(nspec, np.nan)
+        _, fin = ref.I.call("funcplasmaparams", [np.array(x), np.zeros(nspec), ns, np.zeros(nspec), np.zeros(nspec), np.zeros(3), 0])
+        assert np.array_equal(fin[2], w), (x, fin[2], w)
+        assert np.array_equal(fin[1], state.attrs["qs"]) and np.array_equal(fin[3], state.attrs["ms"]) and not fin[4].any()
+        interpolated += int(w[0] != 1.0 and w[0] != 0.0)
+    assert interpolated >= 15 and (want[-2] == 0.0).all() and (want[-1] == 1.0).all()  # inside the Earth: 0; nothing in reach: exp(0)
+    om.close()
