@@ -19,7 +19,8 @@
 // kdtree_search_core) and the insert / nearest-distance steps of setup equal the reference's kdtree_mod.f95 executed by the same
 // interpreter: same kept samples, same stored distances, same neighbours in the same order, the root quirk included.
 // The density part of funcPlasmaParams, executed as a whole from the reference's text on that tree, equals plasma() here.
-// UNPINNED: the READ loop of setup.
+// The READ loop of setup: the PRODUCT's reader is compared with libgfortran executing those READs (tests/test_formats_gfortran.py);
+// the reader of this file (ListReader of orc_models.h) knows clean files only.
 #pragma once
 #include <algorithm>
 #include <memory>

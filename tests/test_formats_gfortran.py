@@ -297,3 +297,29 @@ def test_config_cards_against_the_runtime(gf, built, tmp_path, name):
         assert da == 1 and sa[1] > 0
     if name.startswith("newray"):
         assert da >= 7
+
+
+def test_scattered_sample_file_against_the_runtime(gf, built, tmp_path):
+    """the READ statements of the scattered adapter's setup (scattered_interp_dens_model_adapter.f95:88-110: 7 items, nspec,
+    nspec, then `read(infile,*,iostat=reason) pos, dat%Ns` until a READ fails) run by libgfortran == what the product's set-up
+    (csrc/srt_scattered_setup.h) takes from the same file: the same number of samples, the same values, the list ending at the
+    same record (a word that is not a number; the record after it is never read)."""
+    path = str(tmp_path / "odd.txt")
+    with open(path, "w") as fh:
+        fh.write("2, 0 0 0 0 0 0\n-1.602D-19 1.602d-19\n9.1e-31,\n1.67e-27\n")
+        for i in range(30):
+            fh.write("%.6e,%.6e\n%.6e %.3f %.3f trailing words are dropped with the record\n" % (2e7 + 1e5 * i, 1e5 * (i % 5), 2e5 * (i % 3), 20.0 + 0.01 * i, 19.0))
+        fh.write("oops 1 2 3 4\n3e7 0 0 1 1\n")
+    counts = np.array([7, 2, 2] + [5] * 40, dtype=np.int32)
+    gf.gfio_read_counts.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    out, status = np.full(int(counts.sum()), -777.0), np.zeros(len(counts), dtype=np.int32)
+    done = gf.gfio_read_counts(path.encode(), counts.ctypes.data, len(counts), out.ctypes.data, status.ctypes.data)
+    assert done == 33 and status[33] > 0  # header, qs, ms, 30 samples; the 31st READ meets `oops`
+    samples = out[11:11 + 5 * 30].reshape(30, 5)
+    he = common.HostEmuScattered(path, window_scale=30.0, order=1, exact=0, local_window_scale=3.0)
+    assert he.npts == 30
+    rec = he.records[np.lexsort(he.records[:, :3].T[::-1])]
+    ref = samples[np.lexsort(samples[:, :3].T[::-1])]
+    assert np.array_equal(rec[:, :5].view(np.uint64), ref.view(np.uint64)) and not rec[:, 5:7].any()
+    o = he.plasma(np.array([[2.15e7, 2e5, 2e5]]))
+    assert np.array_equal(o[0, 0:2], out[7:9]) and np.array_equal(o[0, 8:10], out[9:11])  # qs, ms as libgfortran read them
