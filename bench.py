@@ -20,7 +20,9 @@ roofline: FP64 (non-tensor) pipe.  achieved = algorithmic flop-equivalents (SURV
           rate measured live by srt_fp64_peak().
 extra   = the other BASELINE configs on the same box in the same run (fewer sweeps): C3 (100 k rays, tricubic grid +
           IGRF), a C4-shaped 100 k-ray lattice (strong scaling: sharded over the N ranks) and, at N = 8, the full
-          1 M-ray C4; each with value, e2e and roofline.
+          1 M-ray C4; each with value, e2e and roofline.  Also c5 (damping along the config-3 rays), ts05 (the C2 launch set
+          with the TS05 external field) and, at N = 1, scattered (modelnum 4: tools/scattered_bench.py in a child process
+          with a time limit, its own mismatch counters, no roofline yet -- its kernels had not run on a B200 when it was added).
 parity  = rays of the timed sweeps traced by the CPU oracle as well (the cpu_baseline leg) and compared with the
           GPU summaries bit for bit: parity_checked_rays / parity_mismatches (non-zero exits 1).
 """
