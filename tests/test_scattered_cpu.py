@@ -598,3 +598,34 @@ def test_kdtree_and_setup_against_the_references_own_source_text(tmp_path):
         interpolated += int(w[0] != 1.0 and w[0] != 0.0)
     assert interpolated >= 15 and (want[-2] == 0.0).all() and (want[-1] == 1.0).all()  # inside the Earth: 0; nothing in reach: exp(0)
     om.close()
+
+
+def test_cell_list_finds_the_brute_force_set_for_any_geometry(tmp_path):
+    """the walk over the cell list against brute force over the records, for sample counts from 1 to 800, search radii from a
+    fraction of the sample spacing to many times the bounding box (one cell), anisotropic boxes, and queries inside, on the
+    faces of, and far outside the box: the same samples, each once"""
+    rng = np.random.default_rng(17)
+    case = 0
+    for n in (1, 2, 7, 60, 800):
+        for ws in (0.3, 1.0, 6.0, 80.0):
+            for shape in ((1.0, 1.0, 1.0), (1.0, 0.02, 0.3)):
+                case += 1
+                pos = np.array([2.0, 1.0, 0.5]) * R_E + (rng.random((n, 3)) - 0.5) * np.array(shape) * 0.5 * R_E
+                path = str(tmp_path / ("c%d.txt" % case))
+                with open(path, "w") as fh:
+                    fh.write("1 0 0 0 0 0 0\n-1.602e-19\n9.1e-31\n")
+                    for p in pos:
+                        fh.write("%.17e %.17e %.17e 20.0\n" % tuple(p))
+                he = common.HostEmuScattered(path, window_scale=ws, order=1, exact=0, local_window_scale=3.0)
+                assert he.npts == n
+                rec = he.records
+                lo, hi = rec[:, :3].min(0), rec[:, :3].max(0)
+                q = np.vstack([lo + (hi - lo) * rng.random((12, 3)), lo, hi, lo - he.radius * 0.999, hi + he.radius * 1.001,
+                               lo + (hi - lo) * rng.random((4, 3)) * 40.0 - 20.0 * (hi - lo), rec[:3, :3]])
+                for x in q:
+                    got = he.neighbours(x)
+                    d = rec[:, :3] - x
+                    want = np.nonzero((d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2] < he.radius * he.radius)[0]
+                    assert len(got) == len(set(got.tolist())) and np.array_equal(np.sort(got), want), (n, ws, shape, x)
+                    assert np.array_equal(got, np.sort(got))  # the walk's order is the records' order
+    assert case == 40
